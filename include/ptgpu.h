@@ -1,0 +1,174 @@
+/*
+ * include/ptgpu.h -- C ABI of the B200-native likelihood engine behind
+ * pt::pll::Partition (matsengrp/pt, NNI-scoring hot path).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.
+ * Every entry point names the libpll call it replaces in the reference's
+ * wrapper (PTPLL = /root/reference/lib/libptpll/src, LIBPLL =
+ * /root/reference/lib/libptpll/lib/pll-modules/libs/libpll/src).
+ *
+ * Index spaces are libpll's (LIBPLL/parse_utree.y:250-340) so host trees need
+ * no change:  clv_index in [0, tips + clv_buffers)  (tips first),
+ *             scaler_index in {-1} U [0, scale_buffers),
+ *             matrix_index in [0, prob_matrices).
+ * Extra clv/scale buffers (for directional CLVs, see ptgpu_score_nni_batch)
+ * are simply requested at create time.
+ *
+ * Layouts in HBM (one engine = one alignment on one device):
+ *   tips     uint8  [tips][sites]             4-bit state masks (A=1,C=2,G=4,T=8)
+ *   clv      double [clv_buffers][sites][cats][4]
+ *   scalers  uint32 [scale_buffers][sites]    counts of 2^256 rescalings
+ *   pmatrix  double [prob_matrices][cats][4][4]   row = parent state
+ *   sumtable double [sites][cats][4]
+ *
+ * Threading: a handle is used by one host thread at a time (as a
+ * pll_partition_t is, PTPLL/pll_partition.hpp:26-33); many handles may be
+ * used concurrently.  Each handle owns one CUDA stream.
+ *
+ * Errors: every function returns PTGPU_OK (0) or a negative code; a
+ * thread-local message is available from ptgpu_last_error() (libpll:
+ * PLL_FAILURE + thread-local pll_errno/pll_errmsg, LIBPLL/pll.c:24-25).
+ * There is NO CPU fallback: without a CUDA device every call fails loudly.
+ */
+#ifndef PTGPU_H
+#define PTGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTGPU_OK 0
+#define PTGPU_ERR_CUDA (-1)      /* CUDA runtime failure (message has details) */
+#define PTGPU_ERR_ARG (-2)       /* bad index / size / null pointer */
+#define PTGPU_ERR_STATE (-3)     /* illegal tip state, model not set, ... */
+#define PTGPU_ERR_NOT_FINITE (-4)/* d1/d2 not finite (PTPLL/pll_partition.cpp:443-449) */
+
+#define PTGPU_SCALE_BUFFER_NONE (-1) /* == PLL_SCALE_BUFFER_NONE */
+
+typedef struct ptgpu_engine ptgpu_engine;
+
+/* Same field order and types as pll_operation_t (LIBPLL/pll.h:249-259), so a
+   pll_operation_t array can be passed with a cast. */
+typedef struct ptgpu_operation
+{
+  unsigned int parent_clv_index;
+  int parent_scaler_index;
+  unsigned int child1_clv_index;
+  unsigned int child1_matrix_index;
+  int child1_scaler_index;
+  unsigned int child2_clv_index;
+  unsigned int child2_matrix_index;
+  int child2_scaler_index;
+} ptgpu_operation_t;
+
+/* One NNI candidate = the two CLV updates that face each other across the
+   central edge after the swap, plus the start length of that edge.  The
+   parent_* fields of p/q are ignored: the two new CLVs never leave the chip. */
+typedef struct ptgpu_nni_candidate
+{
+  ptgpu_operation_t p;
+  ptgpu_operation_t q;
+  double length0;
+} ptgpu_nni_candidate_t;
+
+const char *ptgpu_last_error(void);
+int ptgpu_device_count(void);
+
+/* pll_partition_create (LIBPLL/pll.c:399-818) as called by
+   PTPLL/pll_partition.cpp:47-57: 4 states, 1 rate matrix, per-site scalers. */
+int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites,
+                 unsigned int rate_cats, unsigned int prob_matrices,
+                 unsigned int scale_buffers, int device, ptgpu_engine **out);
+void ptgpu_destroy(ptgpu_engine *e); /* pll_partition_destroy */
+
+/* pll_set_frequencies + pll_set_subst_params + pll_set_category_rates
+   (LIBPLL/models.c:366-400) followed by pll_update_eigen (:251-331).  The
+   4x4 symmetric eigenproblem is solved on the host, once per model, and the
+   result is kept as kernel constants.  subst = ac ag at cg ct gt. */
+int ptgpu_set_model(ptgpu_engine *e, const double freqs[4], const double subst[6],
+                    const double *category_rates);
+/* read back what the kernels use (test hook) */
+int ptgpu_get_eigen(ptgpu_engine *e, double evecs[16], double inv_evecs[16],
+                    double evals[4]);
+
+/* pll_set_tip_states(partition, tip, pll_map_nt, sequence)
+   (LIBPLL/pll.c:941-964, LIBPLL/maps.c:46-64): IUPAC nucleotide codes, gap/N/? =
+   fully ambiguous; an unknown character is PTGPU_ERR_STATE. */
+int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index,
+                         const char *sequence);
+
+/* pll_update_prob_matrices (LIBPLL/models.c:333-364) */
+int ptgpu_update_prob_matrices(ptgpu_engine *e, const unsigned int *matrix_indices,
+                               const double *branch_lengths, unsigned int count);
+
+/* pll_update_partials (LIBPLL/partials.c:177-213): ops run in list order. */
+int ptgpu_update_partials(ptgpu_engine *e, const ptgpu_operation_t *ops,
+                          unsigned int count);
+
+/* pll_compute_edge_loglikelihood (LIBPLL/likelihood.c:478-513); persite_lnl
+   may be NULL, else `sites` doubles on the host. */
+int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_index,
+                                     int parent_scaler_index,
+                                     unsigned int child_clv_index,
+                                     int child_scaler_index,
+                                     unsigned int matrix_index,
+                                     double *persite_lnl, double *lnl_out);
+
+/* pll_update_sumtable (LIBPLL/derivatives.c:164-234) into the engine-owned
+   device sumtable (PTPLL keeps one scratch sumtable per partition too). */
+int ptgpu_update_sumtable(ptgpu_engine *e, unsigned int parent_clv_index,
+                          unsigned int child_clv_index, int parent_scaler_index,
+                          int child_scaler_index);
+
+/* pll_compute_likelihood_derivatives (LIBPLL/derivatives.c:243-312): first
+   and second derivative of -lnL at branch_length from the current sumtable. */
+int ptgpu_compute_likelihood_derivatives(ptgpu_engine *e, double branch_length,
+                                         double *d_f, double *dd_f);
+
+/* The body of Partition::OptimizeBranch (PTPLL/pll_partition.cpp:408-488)
+   as one device-resident loop: sumtable, <= max_iter Newton steps with the
+   reference's stopping rules, then the edge's P matrix at the new length.
+   map_lambda = 0 outside MAP mode (10 in MAP mode).  *iterations (optional)
+   receives the number of derivative evaluations. */
+int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
+                          int parent_scaler_index, unsigned int child_clv_index,
+                          int child_scaler_index, unsigned int matrix_index,
+                          double length0, unsigned int max_iter, double epsilon,
+                          double map_lambda, double *length_out, int *iterations);
+
+/* Batched SingleBranchOptimizer::EvaluateMove
+   (src/move_tester/single_branch_optimizer.cpp:23-64) for `count` candidates
+   of one parent tree: for each, the two CLV updates across the swapped edge,
+   the sumtable, Newton on the central branch from length0, and the
+   log-likelihood at the optimum.  Nothing in the engine's CLV / scaler /
+   P-matrix state is modified.  status_out[i] is PTGPU_OK or
+   PTGPU_ERR_NOT_FINITE. */
+int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
+                          unsigned int count, unsigned int max_iter,
+                          double epsilon, double map_lambda, double *length_out,
+                          double *lnl_out, int *status_out);
+
+/* test / debug hooks: host copies of device state */
+int ptgpu_get_clv(ptgpu_engine *e, unsigned int clv_index, double *out);
+int ptgpu_set_clv(ptgpu_engine *e, unsigned int clv_index, const double *in);
+int ptgpu_get_scaler(ptgpu_engine *e, int scaler_index, unsigned int *out);
+int ptgpu_get_pmatrix(ptgpu_engine *e, unsigned int matrix_index, double *out);
+int ptgpu_set_pmatrix(ptgpu_engine *e, unsigned int matrix_index, const double *in);
+int ptgpu_get_sumtable(ptgpu_engine *e, double *out);
+
+/* counters since create: [0] kernel launches, [1] CLV site-updates,
+   [2] Newton derivative passes (site sweeps), [3] NNI candidates scored */
+int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[4]);
+
+/* the engine's stream (a cudaStream_t) so callers can order their own CUDA
+   events / work against it */
+void *ptgpu_stream(ptgpu_engine *e);
+int ptgpu_synchronize(ptgpu_engine *e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTGPU_H */

@@ -1,0 +1,699 @@
+// pt_b200/csrc/engine.cu -- the C ABI of include/ptgpu.h over the sm_100a kernels.
+//
+// One ptgpu_engine = one alignment resident in the HBM of one device, with the
+// same index spaces as a pll_partition_t.  There is no CPU
+// fallback anywhere in this file: every entry point either runs CUDA kernels
+// or returns an error.
+#include "../../include/ptgpu.h"
+
+#include "gtr_model.hpp"
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace ptgpu;
+
+static_assert(sizeof(ptgpu_operation_t) == sizeof(DevOp), "op layout");
+static_assert(sizeof(ptgpu_nni_candidate_t) == sizeof(DevCand), "candidate layout");
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...)
+{
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                        \
+  do                                                                                    \
+  {                                                                                     \
+    cudaError_t err__ = (call);                                                         \
+    if (err__ != cudaSuccess)                                                           \
+      return fail(PTGPU_ERR_CUDA, "%s failed: %s (%s:%d)", #call,                       \
+                  cudaGetErrorString(err__), __FILE__, __LINE__);                       \
+  } while (0)
+
+// host staging area in pinned, device-mapped memory: small inputs go up and
+// scalar results come back without extra cudaMemcpy calls
+struct Staging
+{
+  static constexpr size_t kBytes = 1 << 20;
+  unsigned char *host = nullptr;
+  unsigned char *dev = nullptr;
+};
+
+} // namespace
+
+struct ptgpu_engine
+{
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  unsigned int tips = 0, clv_buffers = 0, sites = 0, cats = 0, prob_matrices = 0,
+               scale_buffers = 0;
+  unsigned int ntiles = 0;
+  bool model_set = false;
+  DevState dev{};
+  ModelConst model{};
+  uint8_t *d_tips = nullptr;
+  double *d_sumtable = nullptr;
+  double *d_persite = nullptr;      // per-site lnL scratch (allocated on first use)
+  double *d_partials = nullptr;     // [ntiles * 2] tile partials of single-edge reductions
+  unsigned int *d_counter = nullptr;
+  NewtonState *d_state = nullptr;   // single-branch Newton state
+  unsigned int *d_idx1 = nullptr;   // one matrix index (optimize_branch)
+  // batch scratch (grown on demand)
+  double *d_bsum = nullptr;
+  unsigned int *d_bsclr = nullptr;
+  NewtonState *d_bstate = nullptr;
+  double *d_bpartials = nullptr;
+  DevCand *d_bcands = nullptr;
+  size_t bcap = 0;
+  // op / matrix upload buffers
+  DevOp *d_ops = nullptr;
+  size_t ops_cap = 0;
+  unsigned int *d_midx = nullptr;
+  double *d_mlen = nullptr;
+  size_t mcap = 0;
+  Staging stg;
+  int coop_blocks_per_sm = 0;
+  int sm_count = 0;
+  unsigned long long counters[4] = {0, 0, 0, 0};
+};
+
+namespace {
+
+int check_clv(const ptgpu_engine *e, unsigned int idx, const char *what)
+{
+  if (idx >= e->tips + e->clv_buffers)
+    return fail(PTGPU_ERR_ARG, "%s: clv index %u out of range [0,%u)", what, idx,
+                e->tips + e->clv_buffers);
+  return PTGPU_OK;
+}
+int check_scaler(const ptgpu_engine *e, int idx, const char *what)
+{
+  if (idx != PTGPU_SCALE_BUFFER_NONE && (idx < 0 || (unsigned int)idx >= e->scale_buffers))
+    return fail(PTGPU_ERR_ARG, "%s: scaler index %d out of range", what, idx);
+  return PTGPU_OK;
+}
+int check_matrix(const ptgpu_engine *e, unsigned int idx, const char *what)
+{
+  if (idx >= e->prob_matrices)
+    return fail(PTGPU_ERR_ARG, "%s: matrix index %u out of range [0,%u)", what, idx,
+                e->prob_matrices);
+  return PTGPU_OK;
+}
+int check_op(const ptgpu_engine *e, const ptgpu_operation_t &op, bool need_parent)
+{
+  int rc;
+  if (need_parent)
+  {
+    if (op.parent_clv_index < e->tips)
+      return fail(PTGPU_ERR_ARG, "operation writes tip clv %u", op.parent_clv_index);
+    if ((rc = check_clv(e, op.parent_clv_index, "op.parent"))) return rc;
+    if ((rc = check_scaler(e, op.parent_scaler_index, "op.parent"))) return rc;
+  }
+  if ((rc = check_clv(e, op.child1_clv_index, "op.child1"))) return rc;
+  if ((rc = check_clv(e, op.child2_clv_index, "op.child2"))) return rc;
+  if ((rc = check_scaler(e, op.child1_scaler_index, "op.child1"))) return rc;
+  if ((rc = check_scaler(e, op.child2_scaler_index, "op.child2"))) return rc;
+  if ((rc = check_matrix(e, op.child1_matrix_index, "op.child1"))) return rc;
+  if ((rc = check_matrix(e, op.child2_matrix_index, "op.child2"))) return rc;
+  return PTGPU_OK;
+}
+
+// dispatch on the compile-time category count
+#define DISPATCH_CATS(e, CALL)                                                          \
+  switch ((e)->cats)                                                                    \
+  {                                                                                     \
+    case 1: { constexpr int C = 1; CALL; break; }                                       \
+    case 2: { constexpr int C = 2; CALL; break; }                                       \
+    case 4: { constexpr int C = 4; CALL; break; }                                       \
+    case 8: { constexpr int C = 8; CALL; break; }                                       \
+    default: return fail(PTGPU_ERR_ARG, "unsupported rate category count %u", (e)->cats); \
+  }
+
+template <int C>
+int coop_occupancy(int *out)
+{
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, newton_kernel<C>, kSitesPerPass * C, 0));
+  return PTGPU_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *ptgpu_last_error(void) { return g_err.c_str(); }
+
+int ptgpu_device_count(void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites,
+                 unsigned int rate_cats, unsigned int prob_matrices,
+                 unsigned int scale_buffers, int device, ptgpu_engine **out)
+{
+  if (!out) return fail(PTGPU_ERR_ARG, "ptgpu_create: out is null");
+  *out = nullptr;
+  if (tips < 3 || sites == 0 || clv_buffers == 0 || prob_matrices == 0)
+    return fail(PTGPU_ERR_ARG, "ptgpu_create: empty partition (tips=%u sites=%u)", tips, sites);
+  if (!(rate_cats == 1 || rate_cats == 2 || rate_cats == 4 || rate_cats == 8))
+    return fail(PTGPU_ERR_ARG, "ptgpu_create: rate_cats must be 1, 2, 4 or 8 (got %u)", rate_cats);
+  int ndev = 0;
+  CU(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev)
+    return fail(PTGPU_ERR_ARG, "ptgpu_create: device %d not present (%d devices)", device, ndev);
+  CU(cudaSetDevice(device));
+
+  ptgpu_engine *e = new ptgpu_engine;
+  e->device = device;
+  e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
+  e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
+  e->ntiles = (sites + kTileSites - 1) / kTileSites;
+  const size_t clv_stride = (size_t)sites * rate_cats * 4;
+#define CU_NEW(call)                                                                    \
+  do { cudaError_t err__ = (call); if (err__ != cudaSuccess) { int rc__ = fail(PTGPU_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(err__)); ptgpu_destroy(e); return rc__; } } while (0)
+  CU_NEW(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  CU_NEW(cudaMalloc(&e->d_tips, (size_t)tips * sites));
+  CU_NEW(cudaMemsetAsync(e->d_tips, 0, (size_t)tips * sites, e->stream));
+  CU_NEW(cudaMalloc(&e->dev.clv, clv_stride * clv_buffers * sizeof(double)));
+  CU_NEW(cudaMalloc(&e->dev.scalers, (size_t)std::max(1u, scale_buffers) * sites * sizeof(unsigned int)));
+  CU_NEW(cudaMemsetAsync(e->dev.scalers, 0, (size_t)std::max(1u, scale_buffers) * sites * sizeof(unsigned int), e->stream));
+  CU_NEW(cudaMalloc(&e->dev.pmat, (size_t)prob_matrices * rate_cats * 16 * sizeof(double)));
+  CU_NEW(cudaMemsetAsync(e->dev.pmat, 0, (size_t)prob_matrices * rate_cats * 16 * sizeof(double), e->stream));
+  CU_NEW(cudaMalloc(&e->d_sumtable, clv_stride * sizeof(double)));
+  CU_NEW(cudaMalloc(&e->d_partials, (size_t)e->ntiles * 2 * sizeof(double)));
+  CU_NEW(cudaMalloc(&e->d_counter, sizeof(unsigned int)));
+  CU_NEW(cudaMemsetAsync(e->d_counter, 0, sizeof(unsigned int), e->stream));
+  CU_NEW(cudaMalloc(&e->d_state, sizeof(NewtonState)));
+  CU_NEW(cudaMalloc(&e->d_idx1, sizeof(unsigned int)));
+  CU_NEW(cudaHostAlloc(&e->stg.host, Staging::kBytes, cudaHostAllocMapped));
+  CU_NEW(cudaHostGetDevicePointer((void **)&e->stg.dev, e->stg.host, 0));
+  e->dev.tips = e->d_tips;
+  e->dev.n_tips = tips;
+  e->dev.sites = sites;
+  e->dev.clv_stride = clv_stride;
+  CU_NEW(cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, device));
+  {
+    int rc = PTGPU_OK, occ = 0;
+    switch (rate_cats)
+    {
+      case 1: rc = coop_occupancy<1>(&occ); break;
+      case 2: rc = coop_occupancy<2>(&occ); break;
+      case 4: rc = coop_occupancy<4>(&occ); break;
+      default: rc = coop_occupancy<8>(&occ); break;
+    }
+    if (rc) { ptgpu_destroy(e); return rc; }
+    if (occ < 1) { ptgpu_destroy(e); return fail(PTGPU_ERR_CUDA, "newton kernel does not fit an SM"); }
+    e->coop_blocks_per_sm = occ;
+  }
+  CU_NEW(cudaStreamSynchronize(e->stream));
+#undef CU_NEW
+  *out = e;
+  return PTGPU_OK;
+}
+
+void ptgpu_destroy(ptgpu_engine *e)
+{
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  cudaFree(e->d_tips); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
+  cudaFree(e->d_sumtable); cudaFree(e->d_persite); cudaFree(e->d_partials); cudaFree(e->d_counter);
+  cudaFree(e->d_state); cudaFree(e->d_idx1);
+  cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials);
+  cudaFree(e->d_bcands); cudaFree(e->d_ops); cudaFree(e->d_midx); cudaFree(e->d_mlen);
+  if (e->stg.host) cudaFreeHost(e->stg.host);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int ptgpu_set_model(ptgpu_engine *e, const double freqs[4], const double subst[6],
+                    const double *category_rates)
+{
+  if (!e || !freqs || !subst || !category_rates) return fail(PTGPU_ERR_ARG, "ptgpu_set_model: null argument");
+  ModelConst &m = e->model;
+  gtr_eigensystem(freqs, subst, m.evecs, m.inv_evecs, m.evals);
+  for (int i = 0; i < 4; ++i) m.freqs[i] = freqs[i];
+  for (int j = 0; j < 4; ++j)
+    for (int k = 0; k < 4; ++k) m.tt_inv[j * 4 + k] = m.inv_evecs[k * 4 + j] * freqs[k];
+  for (unsigned int c = 0; c < kMaxCats; ++c) m.rates[c] = c < e->cats ? category_rates[c] : 0.0;
+  m.rate_weight = 1.0 / e->cats;
+  m.log_scale_thr = std::log(1.0 / std::ldexp(1.0, 256));
+  e->model_set = true;
+  return PTGPU_OK;
+}
+
+int ptgpu_get_eigen(ptgpu_engine *e, double evecs[16], double inv_evecs[16], double evals[4])
+{
+  if (!e || !e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  memcpy(evecs, e->model.evecs, sizeof e->model.evecs);
+  memcpy(inv_evecs, e->model.inv_evecs, sizeof e->model.inv_evecs);
+  memcpy(evals, e->model.evals, sizeof e->model.evals);
+  return PTGPU_OK;
+}
+
+int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *sequence)
+{
+  if (!e || !sequence) return fail(PTGPU_ERR_ARG, "ptgpu_set_tip_states: null argument");
+  if (tip_index >= e->tips) return fail(PTGPU_ERR_ARG, "tip index %u out of range", tip_index);
+  std::vector<uint8_t> masks(e->sites);
+  for (unsigned int i = 0; i < e->sites; ++i)
+  {
+    const unsigned char ch = (unsigned char)sequence[i];
+    const unsigned int mk = ch ? nucleotide_mask(ch) : 0;
+    if (!mk) return fail(PTGPU_ERR_STATE, "Illegal state code in tip \"%c\" (site %u)", ch ? ch : '?', i);
+    masks[i] = (uint8_t)mk;
+  }
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(e->d_tips + (size_t)tip_index * e->sites, masks.data(), e->sites,
+                     cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// staging layout: [0, 4096) scalar results written by kernels through the
+// mapped pointer; [4096, 1 MiB) small uploads (ops, matrix lists, candidates)
+constexpr size_t kUploadOff = 4096;
+
+template <typename T>
+int ensure(T **ptr, size_t *cap, size_t need)
+{
+  if (need <= *cap) return PTGPU_OK;
+  if (*ptr) CU(cudaFree(*ptr));
+  *ptr = nullptr;
+  *cap = 0;
+  size_t n = std::max<size_t>(need, 64);
+  CU(cudaMalloc(ptr, n * sizeof(T)));
+  *cap = n;
+  return PTGPU_OK;
+}
+
+// host -> device copy of a small descriptor array on the engine's stream.
+// Arrays that fit go through the pinned staging area (truly asynchronous);
+// the stream is drained first so the area is never overwritten in flight.
+int upload(ptgpu_engine *e, void *dst, const void *src, size_t bytes)
+{
+  if (bytes <= Staging::kBytes - kUploadOff)
+  {
+    CU(cudaStreamSynchronize(e->stream));
+    memcpy(e->stg.host + kUploadOff, src, bytes);
+    CU(cudaMemcpyAsync(dst, e->stg.host + kUploadOff, bytes, cudaMemcpyHostToDevice, e->stream));
+  }
+  else
+  {
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+  }
+  return PTGPU_OK;
+}
+
+template <int C>
+int launch_pmatrix(ptgpu_engine *e, const unsigned int *d_idx, const double *d_len, unsigned int count)
+{
+  const unsigned int threads = 128, blocks = (count * C + threads - 1) / threads;
+  pmatrix_kernel<C><<<blocks, threads, 0, e->stream>>>(e->dev, e->model, d_idx, d_len, count);
+  CU(cudaGetLastError());
+  e->counters[0]++;
+  return PTGPU_OK;
+}
+
+template <int C>
+int launch_newton(ptgpu_engine *e, NewtonArgs &a)
+{
+  const unsigned int work = std::max(1u, a.B * a.ntiles);
+  const unsigned int maxg = (unsigned int)(e->coop_blocks_per_sm * e->sm_count);
+  const unsigned int grid = std::min(work, maxg);
+  void *params[] = {&a};
+  CU(cudaLaunchCooperativeKernel((void *)newton_kernel<C>, dim3(grid), dim3(kSitesPerPass * C),
+                                 params, 0, e->stream));
+  e->counters[0]++;
+  return PTGPU_OK;
+}
+
+int run_newton(ptgpu_engine *e, NewtonArgs &a)
+{
+  DISPATCH_CATS(e, return launch_newton<C>(e, a));
+  return PTGPU_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int ptgpu_update_prob_matrices(ptgpu_engine *e, const unsigned int *matrix_indices,
+                               const double *branch_lengths, unsigned int count)
+{
+  if (!e || (count && (!matrix_indices || !branch_lengths)))
+    return fail(PTGPU_ERR_ARG, "ptgpu_update_prob_matrices: null argument");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  if (!count) return PTGPU_OK;
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    int rc = check_matrix(e, matrix_indices[i], "update_prob_matrices");
+    if (rc) return rc;
+    if (!(branch_lengths[i] >= 0))
+      return fail(PTGPU_ERR_ARG, "negative or NaN branch length %g", branch_lengths[i]);
+  }
+  CU(cudaSetDevice(e->device));
+  int rc;
+  size_t cap2 = e->mcap;
+  if ((rc = ensure(&e->d_midx, &e->mcap, count))) return rc;
+  if ((rc = ensure(&e->d_mlen, &cap2, count))) return rc;
+  if ((rc = upload(e, e->d_midx, matrix_indices, count * sizeof(unsigned int)))) return rc;
+  if ((rc = upload(e, e->d_mlen, branch_lengths, count * sizeof(double)))) return rc;
+  DISPATCH_CATS(e, rc = launch_pmatrix<C>(e, e->d_midx, e->d_mlen, count));
+  return rc;
+}
+
+int ptgpu_update_partials(ptgpu_engine *e, const ptgpu_operation_t *ops, unsigned int count)
+{
+  if (!e || (count && !ops)) return fail(PTGPU_ERR_ARG, "ptgpu_update_partials: null argument");
+  if (!count) return PTGPU_OK;
+  int rc;
+  for (unsigned int i = 0; i < count; ++i)
+    if ((rc = check_op(e, ops[i], true))) return rc;
+  CU(cudaSetDevice(e->device));
+  if ((rc = ensure(&e->d_ops, &e->ops_cap, count))) return rc;
+  if ((rc = upload(e, e->d_ops, ops, count * sizeof(DevOp)))) return rc;
+  DISPATCH_CATS(e, (partials_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
+  CU(cudaGetLastError());
+  e->counters[0]++;
+  e->counters[1] += (unsigned long long)count * e->sites;
+  return PTGPU_OK;
+}
+
+int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_index,
+                                     int parent_scaler_index, unsigned int child_clv_index,
+                                     int child_scaler_index, unsigned int matrix_index,
+                                     double *persite_lnl, double *lnl_out)
+{
+  if (!e || !lnl_out) return fail(PTGPU_ERR_ARG, "ptgpu_compute_edge_loglikelihood: null argument");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  int rc;
+  if ((rc = check_clv(e, parent_clv_index, "edge_lnl.parent"))) return rc;
+  if ((rc = check_clv(e, child_clv_index, "edge_lnl.child"))) return rc;
+  if ((rc = check_scaler(e, parent_scaler_index, "edge_lnl.parent"))) return rc;
+  if ((rc = check_scaler(e, child_scaler_index, "edge_lnl.child"))) return rc;
+  if ((rc = check_matrix(e, matrix_index, "edge_lnl"))) return rc;
+  CU(cudaSetDevice(e->device));
+  double *d_persite = nullptr;
+  if (persite_lnl)
+  {
+    if (!e->d_persite) CU(cudaMalloc(&e->d_persite, (size_t)e->sites * sizeof(double)));
+    d_persite = e->d_persite;
+  }
+  double *result = (double *)e->stg.dev;
+  DISPATCH_CATS(e, (edge_lnl_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
+                       e->dev, e->model, parent_clv_index, parent_scaler_index, child_clv_index,
+                       child_scaler_index, matrix_index, d_persite, e->d_partials, e->d_counter, result)));
+  CU(cudaGetLastError());
+  e->counters[0]++;
+  if (persite_lnl)
+    CU(cudaMemcpyAsync(persite_lnl, d_persite, (size_t)e->sites * sizeof(double),
+                       cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  *lnl_out = *(volatile double *)e->stg.host;
+  return PTGPU_OK;
+}
+
+int ptgpu_update_sumtable(ptgpu_engine *e, unsigned int parent_clv_index,
+                          unsigned int child_clv_index, int parent_scaler_index,
+                          int child_scaler_index)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_update_sumtable: null engine");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  int rc;
+  if ((rc = check_clv(e, parent_clv_index, "sumtable.parent"))) return rc;
+  if ((rc = check_clv(e, child_clv_index, "sumtable.child"))) return rc;
+  (void)parent_scaler_index; (void)child_scaler_index; // per-site scalers do not enter the sumtable
+  CU(cudaSetDevice(e->device));
+  DISPATCH_CATS(e, (sumtable_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
+                       e->dev, e->model, parent_clv_index, child_clv_index, e->d_sumtable)));
+  CU(cudaGetLastError());
+  e->counters[0]++;
+  return PTGPU_OK;
+}
+
+static int newton_single(ptgpu_engine *e, double len0, unsigned int max_iter, double eps,
+                         double lambda, NewtonState *out)
+{
+  NewtonState init{};
+  init.len = len0;
+  int rc;
+  if ((rc = upload(e, e->d_state, &init, sizeof init))) return rc;
+  NewtonArgs a{};
+  a.m = e->model;
+  a.sumtables = e->d_sumtable;
+  a.entry_stride = 0;
+  a.sclr = nullptr;
+  a.st = e->d_state;
+  a.partials = e->d_partials;
+  a.sites = e->sites; a.B = 1; a.ntiles = e->ntiles; a.max_iter = max_iter;
+  a.eps = eps; a.lambda = lambda; a.want_lnl = 0;
+  if ((rc = run_newton(e, a))) return rc;
+  e->counters[2] += max_iter; // upper bound; exact count is returned in state.iters
+  (void)out;
+  return PTGPU_OK;
+}
+
+int ptgpu_compute_likelihood_derivatives(ptgpu_engine *e, double branch_length, double *d_f,
+                                         double *dd_f)
+{
+  if (!e || !d_f || !dd_f) return fail(PTGPU_ERR_ARG, "ptgpu_compute_likelihood_derivatives: null argument");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  CU(cudaSetDevice(e->device));
+  int rc;
+  if ((rc = newton_single(e, branch_length, 1, 0.0, 0.0, nullptr))) return rc;
+  NewtonState *hs = (NewtonState *)(e->stg.host + 64);
+  CU(cudaMemcpyAsync(hs, e->d_state, sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  *d_f = hs->d1;
+  *dd_f = hs->d2;
+  return PTGPU_OK;
+}
+
+int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
+                          int parent_scaler_index, unsigned int child_clv_index,
+                          int child_scaler_index, unsigned int matrix_index, double length0,
+                          unsigned int max_iter, double epsilon, double map_lambda,
+                          double *length_out, int *iterations)
+{
+  if (!e || !length_out) return fail(PTGPU_ERR_ARG, "ptgpu_optimize_branch: null argument");
+  int rc;
+  if ((rc = check_matrix(e, matrix_index, "optimize_branch"))) return rc;
+  if ((rc = ptgpu_update_sumtable(e, parent_clv_index, child_clv_index, parent_scaler_index,
+                                  child_scaler_index)))
+    return rc;
+  if ((rc = newton_single(e, length0, max_iter, epsilon, map_lambda, nullptr))) return rc;
+  // UpdateBranchLength (PTPLL/pll_partition.cpp:395-406): the edge's P matrix at
+  // the new length, straight from the device-resident state
+  *(unsigned int *)(e->stg.host + 128) = matrix_index;
+  CU(cudaMemcpyAsync(e->d_idx1, e->stg.host + 128, sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+  DISPATCH_CATS(e, rc = launch_pmatrix<C>(e, e->d_idx1, &e->d_state->len, 1));
+  if (rc) return rc;
+  NewtonState *hs = (NewtonState *)(e->stg.host + 64);
+  CU(cudaMemcpyAsync(hs, e->d_state, sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  *length_out = hs->len;
+  if (iterations) *iterations = hs->iters;
+  if (hs->status == 1) return fail(PTGPU_ERR_NOT_FINITE, "d1 is not finite");
+  if (hs->status == 2) return fail(PTGPU_ERR_NOT_FINITE, "d2 is not finite");
+  return PTGPU_OK;
+}
+
+int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
+                          unsigned int count, unsigned int max_iter, double epsilon,
+                          double map_lambda, double *length_out, double *lnl_out,
+                          int *status_out)
+{
+  if (!e || (count && (!cands || !length_out || !lnl_out)))
+    return fail(PTGPU_ERR_ARG, "ptgpu_score_nni_batch: null argument");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  if (!count) return PTGPU_OK;
+  int rc;
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    if ((rc = check_op(e, cands[i].p, false))) return rc;
+    if ((rc = check_op(e, cands[i].q, false))) return rc;
+    if (!(cands[i].length0 >= 0)) return fail(PTGPU_ERR_ARG, "candidate %u: bad start length", i);
+  }
+  CU(cudaSetDevice(e->device));
+  const size_t stride = e->dev.clv_stride;
+  // candidates are processed in chunks whose sumtables fit the scratch budget
+  size_t free_b = 0, total_b = 0;
+  CU(cudaMemGetInfo(&free_b, &total_b));
+  const size_t per_cand = stride * sizeof(double) + (size_t)e->sites * sizeof(unsigned int) +
+                          (size_t)e->ntiles * 2 * sizeof(double) + sizeof(NewtonState) + sizeof(DevCand);
+  size_t have = e->bcap * per_cand;
+  size_t budget = std::max(have, (size_t)((free_b + have) * 0.8));
+  size_t chunk = std::min<size_t>(count, std::max<size_t>(1, budget / per_cand));
+  if (chunk > e->bcap)
+  {
+    cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials); cudaFree(e->d_bcands);
+    e->d_bsum = nullptr; e->d_bsclr = nullptr; e->d_bstate = nullptr; e->d_bpartials = nullptr; e->d_bcands = nullptr;
+    e->bcap = 0;
+    CU(cudaMalloc(&e->d_bsum, chunk * stride * sizeof(double)));
+    CU(cudaMalloc(&e->d_bsclr, chunk * (size_t)e->sites * sizeof(unsigned int)));
+    CU(cudaMalloc(&e->d_bstate, chunk * sizeof(NewtonState)));
+    CU(cudaMalloc(&e->d_bpartials, chunk * (size_t)e->ntiles * 2 * sizeof(double)));
+    CU(cudaMalloc(&e->d_bcands, chunk * sizeof(DevCand)));
+    e->bcap = chunk;
+  }
+  std::vector<NewtonState> hst(chunk);
+  for (unsigned int base = 0; base < count; base += (unsigned int)chunk)
+  {
+    const unsigned int nb = (unsigned int)std::min<size_t>(chunk, count - base);
+    for (unsigned int i = 0; i < nb; ++i)
+    {
+      hst[i] = NewtonState{};
+      hst[i].len = cands[base + i].length0;
+    }
+    if ((rc = upload(e, e->d_bcands, cands + base, nb * sizeof(DevCand)))) return rc;
+    if ((rc = upload(e, e->d_bstate, hst.data(), nb * sizeof(NewtonState)))) return rc;
+    DISPATCH_CATS(e, (nni_prepare_kernel<C><<<dim3(e->ntiles, nb), kSitesPerPass * C, 0, e->stream>>>(
+                         e->dev, e->model, e->d_bcands, e->d_bsum, stride, e->d_bsclr)));
+    CU(cudaGetLastError());
+    e->counters[0]++;
+    NewtonArgs a{};
+    a.m = e->model;
+    a.sumtables = e->d_bsum;
+    a.entry_stride = stride;
+    a.sclr = e->d_bsclr;
+    a.st = e->d_bstate;
+    a.partials = e->d_bpartials;
+    a.sites = e->sites; a.B = nb; a.ntiles = e->ntiles; a.max_iter = max_iter;
+    a.eps = epsilon; a.lambda = map_lambda; a.want_lnl = 1;
+    if ((rc = run_newton(e, a))) return rc;
+    CU(cudaMemcpyAsync(hst.data(), e->d_bstate, nb * sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    for (unsigned int i = 0; i < nb; ++i)
+    {
+      length_out[base + i] = hst[i].len;
+      lnl_out[base + i] = hst[i].lnl;
+      if (status_out) status_out[base + i] = hst[i].status ? PTGPU_ERR_NOT_FINITE : PTGPU_OK;
+      e->counters[2] += (unsigned long long)hst[i].iters;
+    }
+    e->counters[3] += nb;
+  }
+  return PTGPU_OK;
+}
+
+int ptgpu_get_clv(ptgpu_engine *e, unsigned int clv_index, double *out)
+{
+  if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_clv: null argument");
+  int rc = check_clv(e, clv_index, "get_clv");
+  if (rc) return rc;
+  CU(cudaSetDevice(e->device));
+  if (clv_index < e->tips)
+  {
+    std::vector<uint8_t> m(e->sites);
+    CU(cudaMemcpyAsync(m.data(), e->d_tips + (size_t)clv_index * e->sites, e->sites, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    for (unsigned int s = 0; s < e->sites; ++s)
+      for (unsigned int c = 0; c < e->cats; ++c)
+        for (int j = 0; j < 4; ++j) out[((size_t)s * e->cats + c) * 4 + j] = (m[s] >> j) & 1 ? 1.0 : 0.0;
+    return PTGPU_OK;
+  }
+  CU(cudaMemcpyAsync(out, e->dev.clv + (size_t)(clv_index - e->tips) * e->dev.clv_stride,
+                     e->dev.clv_stride * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+int ptgpu_set_clv(ptgpu_engine *e, unsigned int clv_index, const double *in)
+{
+  if (!e || !in) return fail(PTGPU_ERR_ARG, "ptgpu_set_clv: null argument");
+  int rc = check_clv(e, clv_index, "set_clv");
+  if (rc) return rc;
+  if (clv_index < e->tips) return fail(PTGPU_ERR_ARG, "set_clv: %u is a tip", clv_index);
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(e->dev.clv + (size_t)(clv_index - e->tips) * e->dev.clv_stride, in,
+                     e->dev.clv_stride * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+int ptgpu_get_scaler(ptgpu_engine *e, int scaler_index, unsigned int *out)
+{
+  if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_scaler: null argument");
+  if (scaler_index < 0 || (unsigned int)scaler_index >= e->scale_buffers)
+    return fail(PTGPU_ERR_ARG, "get_scaler: index %d out of range", scaler_index);
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(out, e->dev.scalers + (size_t)scaler_index * e->sites,
+                     (size_t)e->sites * sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+int ptgpu_get_pmatrix(ptgpu_engine *e, unsigned int matrix_index, double *out)
+{
+  if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_pmatrix: null argument");
+  int rc = check_matrix(e, matrix_index, "get_pmatrix");
+  if (rc) return rc;
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(out, e->dev.pmat + (size_t)matrix_index * e->cats * 16,
+                     (size_t)e->cats * 16 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+int ptgpu_set_pmatrix(ptgpu_engine *e, unsigned int matrix_index, const double *in)
+{
+  if (!e || !in) return fail(PTGPU_ERR_ARG, "ptgpu_set_pmatrix: null argument");
+  int rc = check_matrix(e, matrix_index, "set_pmatrix");
+  if (rc) return rc;
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(e->dev.pmat + (size_t)matrix_index * e->cats * 16, in,
+                     (size_t)e->cats * 16 * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+int ptgpu_get_sumtable(ptgpu_engine *e, double *out)
+{
+  if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_sumtable: null argument");
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(out, e->d_sumtable, e->dev.clv_stride * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[4])
+{
+  if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_counters: null argument");
+  for (int i = 0; i < 4; ++i) out[i] = e->counters[i];
+  return PTGPU_OK;
+}
+
+void *ptgpu_stream(ptgpu_engine *e) { return e ? (void *)e->stream : nullptr; }
+
+int ptgpu_synchronize(ptgpu_engine *e)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_synchronize: null engine");
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamSynchronize(e->stream));
+  return PTGPU_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,709 @@
+// pt_b200/csrc/kernels.cuh -- sm_100a device code of the likelihood engine.
+//
+// Work decomposition shared by every kernel here: one thread owns one
+// (site, rate-category) pair, i.e. one 4-double (32-byte) CLV entry.  A CTA
+// covers 64 consecutive sites x C categories per pass and PASSES passes per
+// tile, so a warp reads 32 consecutive 32-byte entries = 1 KB contiguous with
+// one LDG.E.256 per thread (fully coalesced), and the C lanes of one site sit
+// next to each other in a warp so per-site reductions over categories are
+// width-C shuffles.  All arithmetic that must match libpll's AVX path bit for
+// bit uses __dmul_rn/__dadd_rn (never contracted to FMA) in the reference's
+// summation order (note N1).
+//
+// Reference citations: LIBPLL = lib/libptpll/lib/pll-modules/libs/libpll/src,
+// PTPLL = lib/libptpll/src (under /root/reference).
+#pragma once
+
+#include <cooperative_groups.h>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ptgpu {
+
+namespace cg = cooperative_groups;
+
+constexpr int kSitesPerPass = 64;  // sites covered by a CTA in one pass
+constexpr int kPasses = 4;         // passes per tile
+constexpr int kTileSites = kSitesPerPass * kPasses;  // 256 sites per tile
+constexpr int kMaxCats = 8;
+
+// Device view of one engine (passed by value; lives in the constant bank).
+struct DevState
+{
+  const uint8_t *tips;   // [n_tips][sites]
+  double *clv;           // [clv_buffers][sites][C][4]
+  unsigned int *scalers; // [scale_buffers][sites]
+  double *pmat;          // [prob_matrices][C][16]
+  unsigned int n_tips;
+  unsigned int sites;
+  size_t clv_stride;     // doubles per CLV buffer
+};
+
+// Model constants (kernel parameter => constant bank, broadcast reads).
+struct ModelConst
+{
+  double evecs[16];     // eigenvecs[j*4+k]                  (LIBPLL/models.c:290-318)
+  double inv_evecs[16];
+  double tt_inv[16];    // tt_inv[j*4+k] = inv_evecs[k*4+j]*freqs[k] (LIBPLL/core_derivatives_avx.c:86-95)
+  double evals[4];
+  double freqs[4];
+  double rates[kMaxCats];
+  double rate_weight;   // 1/C                               (LIBPLL/pll.c:742-748)
+  double log_scale_thr; // host log(2^-256)                  (LIBPLL/core_likelihood_avx.c:1250)
+};
+
+struct DevOp // == ptgpu_operation_t
+{
+  unsigned int parent_clv;
+  int parent_scaler;
+  unsigned int c1_clv;
+  unsigned int c1_mat;
+  int c1_scaler;
+  unsigned int c2_clv;
+  unsigned int c2_mat;
+  int c2_scaler;
+};
+
+struct DevCand // == ptgpu_nni_candidate_t
+{
+  DevOp p;
+  DevOp q;
+  double length0;
+};
+
+// Newton state of one branch (PTPLL/pll_partition.cpp:419-481)
+struct NewtonState
+{
+  double len;
+  double d1;
+  double d2;
+  double lnl;
+  int iters;
+  int done;             // 0 running, 1 finished
+  int maybe_decreasing;
+  int status;           // 0 ok, 1 d1 not finite, 2 d2 not finite
+};
+
+// ---------------------------------------------------------------- helpers
+
+#define PT_SCALE_FACTOR 1.157920892373161954235709850086879078532699846656405640394575840079131296399360e77 /* 2^256 */
+#define PT_SCALE_THRESHOLD (1.0 / PT_SCALE_FACTOR)
+
+__device__ __forceinline__ void ld256(const double *p, double v[4])
+{
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+               : "l"(p));
+}
+
+// streaming read of data nobody re-reads soon (sumtable sweeps)
+__device__ __forceinline__ void ld256_stream(const double *p, double v[4])
+{
+  asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+               : "l"(p));
+}
+
+__device__ __forceinline__ void st256(double *p, const double v[4])
+{
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]),
+               "d"(v[2]), "d"(v[3])
+               : "memory");
+}
+
+// (a0 b0 + a1 b1) + (a2 b2 + a3 b3), every product and sum rounded separately
+__device__ __forceinline__ double dot4(const double *a, const double b[4])
+{
+  return __dadd_rn(__dadd_rn(__dmul_rn(a[0], b[0]), __dmul_rn(a[1], b[1])),
+                   __dadd_rn(__dmul_rn(a[2], b[2]), __dmul_rn(a[3], b[3])));
+}
+
+// One (site, cat) entry of CLV `clv_index`: tips are expanded from their 4-bit
+// mask to the 0.0/1.0 vector libpll stores (LIBPLL/pll.c:920-925).
+template <int C>
+__device__ __forceinline__ void load_entry(const DevState &s, unsigned int clv_index,
+                                           unsigned int site, int cat, double v[4])
+{
+  if (clv_index < s.n_tips)
+  {
+    const unsigned int m = s.tips[(size_t)clv_index * s.sites + site];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = ((m >> j) & 1u) ? 1.0 : 0.0;
+  }
+  else
+  {
+    ld256(s.clv + (size_t)(clv_index - s.n_tips) * s.clv_stride +
+              ((size_t)site * C + cat) * 4,
+          v);
+  }
+}
+
+__device__ __forceinline__ unsigned int load_scaler(const DevState &s, int scaler_index,
+                                                    unsigned int site)
+{
+  return scaler_index < 0 ? 0u : s.scalers[(size_t)scaler_index * s.sites + site];
+}
+
+// AND of a predicate over the C lanes that hold one site
+template <int C>
+__device__ __forceinline__ bool site_all(bool pred)
+{
+  unsigned int b = pred ? 1u : 0u;
+#pragma unroll
+  for (int d = 1; d < C; d <<= 1) b &= __shfl_xor_sync(0xffffffffu, b, d, C);
+  return b != 0;
+}
+
+// x_i = dot4(M[i], child) for the four rows of a staged 4x4 matrix, then the
+// elementwise product of the two children's vectors: one libpll CLV entry
+// (LIBPLL/core_partials_avx.c:418-476).
+__device__ __forceinline__ void combine_entry(const double *lm, const double *rm,
+                                              const double l[4], const double r[4],
+                                              double p[4])
+{
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    p[i] = __dmul_rn(dot4(lm + 4 * i, l), dot4(rm + 4 * i, r));
+}
+
+// deterministic CTA-wide sum of one double per thread; result valid in thread 0
+template <int THREADS>
+__device__ __forceinline__ double block_sum(double v, double *smem /* >= THREADS/32 */)
+{
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, d));
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) smem[w] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (threadIdx.x < 32)
+  {
+    t = (threadIdx.x < THREADS / 32) ? smem[threadIdx.x] : 0.0;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) t = __dadd_rn(t, __shfl_down_sync(0xffffffffu, t, d));
+  }
+  __syncthreads();
+  return t;
+}
+
+// ------------------------------------------------------------ kernel 2
+// P(t) = I + (V^-1 o expm1(lambda r t)) V per branch and category
+// (LIBPLL/core_pmatrix_avx.c:42-310).  One thread per (branch, category).
+// lengths/indices live in device memory so that the Newton kernel's result
+// can feed this kernel without a host round trip.
+template <int C>
+__global__ void pmatrix_kernel(DevState s, ModelConst m, const unsigned int *idx,
+                               const double *len, unsigned int count)
+{
+  const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count * C) return;
+  const unsigned int b = t / C, c = t % C;
+  const double bl = len[b];
+  double *pm = s.pmat + ((size_t)idx[b] * C + c) * 16;
+  if (bl == 0.0)
+  {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) pm[i] = (i % 5 == 0) ? 1.0 : 0.0;
+    return;
+  }
+  double e[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    e[k] = expm1(__dmul_rn(__dmul_rn(m.evals[k], m.rates[c]), bl));
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+  {
+    double w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) w[k] = __dmul_rn(m.inv_evecs[i * 4 + k], e[k]);
+    double row[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+      const double a = __dadd_rn(__dmul_rn(w[0], m.evecs[0 + j]), __dmul_rn(w[1], m.evecs[4 + j]));
+      const double b2 = __dadd_rn(__dmul_rn(w[2], m.evecs[8 + j]), __dmul_rn(w[3], m.evecs[12 + j]));
+      row[j] = __dadd_rn(__dadd_rn(a, b2), (i == j) ? 1.0 : 0.0);
+    }
+    st256(pm + 4 * i, row);
+  }
+}
+
+// ------------------------------------------------------------ kernel 1
+// Streaming CLV update: every thread walks the whole operation list for the
+// (site, category) entries it owns (LIBPLL/partials.c:177-213 runs the same
+// list one op at a time over all sites).  Entries of different sites never
+// interact, and an entry written by op i is re-read by op j > i only by the
+// thread that wrote it, so no inter-thread synchronisation is needed beyond
+// staging each op's two P matrices in shared memory.
+template <int C>
+__global__ void __launch_bounds__(kSitesPerPass *C)
+    partials_kernel(DevState s, const DevOp *__restrict__ ops, unsigned int nops)
+{
+  __shared__ double mats[2][2][C * 16];
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = blockIdx.x * kTileSites + threadIdx.x / C;
+
+  for (unsigned int o = 0; o < nops; ++o)
+  {
+    const DevOp op = ops[o];
+    double *lm = mats[o & 1][0], *rm = mats[o & 1][1];
+    for (int i = threadIdx.x; i < C * 16; i += blockDim.x)
+    {
+      lm[i] = s.pmat[(size_t)op.c1_mat * C * 16 + i];
+      rm[i] = s.pmat[(size_t)op.c2_mat * C * 16 + i];
+    }
+    __syncthreads(); // double-buffered: one barrier per op is enough
+
+    double l[kPasses][4], r[kPasses][4];
+    unsigned int sc[kPasses];
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps)
+    {
+      const unsigned int site = min(site0 + ps * kSitesPerPass, s.sites - 1);
+      load_entry<C>(s, op.c1_clv, site, cat, l[ps]);
+      load_entry<C>(s, op.c2_clv, site, cat, r[ps]);
+      sc[ps] = load_scaler(s, op.c1_scaler, site) + load_scaler(s, op.c2_scaler, site);
+    }
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps)
+    {
+      const unsigned int site = site0 + ps * kSitesPerPass;
+      double p[4];
+      combine_entry(lm + cat * 16, rm + cat * 16, l[ps], r[ps], p);
+      // per-site scaling (LIBPLL/core_partials_avx.c:491-527): ordered "<"
+      bool small = (p[0] < PT_SCALE_THRESHOLD) & (p[1] < PT_SCALE_THRESHOLD) &
+                   (p[2] < PT_SCALE_THRESHOLD) & (p[3] < PT_SCALE_THRESHOLD);
+      small = site_all<C>(small) && op.parent_scaler >= 0;
+      if (small)
+      {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) p[i] = __dmul_rn(p[i], PT_SCALE_FACTOR);
+      }
+      if (site < s.sites)
+      {
+        st256(s.clv + (size_t)(op.parent_clv - s.n_tips) * s.clv_stride +
+                  ((size_t)site * C + cat) * 4,
+              p);
+        if (cat == 0 && op.parent_scaler >= 0)
+          s.scalers[(size_t)op.parent_scaler * s.sites + site] = sc[ps] + (small ? 1u : 0u);
+      }
+    }
+    __syncwarp(); // scaler word written by lane cat 0, re-read by its C-lane group
+  }
+}
+
+// Fixed-order finish shared by the reduction kernels: every CTA drops its
+// per-tile partial(s) into `partials[tile*NV + v]`; the last CTA to arrive
+// sums all tiles in a fixed tree, so the result depends only on `sites`,
+// never on launch geometry, SM count or timing.
+template <int THREADS, int NV>
+__device__ __forceinline__ void finish_tiles(const double (&mine)[NV], double *partials,
+                                             unsigned int ntiles, unsigned int *counter,
+                                             double *result, double *smem)
+{
+  __shared__ bool last;
+  if (threadIdx.x == 0)
+  {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) partials[(size_t)blockIdx.x * NV + v] = mine[v];
+    __threadfence();
+    last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+  {
+    double acc = 0.0;
+    for (unsigned int t = threadIdx.x; t < ntiles; t += THREADS)
+      acc = __dadd_rn(acc, __ldcg(partials + (size_t)t * NV + v));
+    acc = block_sum<THREADS>(acc, smem);
+    if (threadIdx.x == 0) result[v] = acc;
+  }
+  if (threadIdx.x == 0) *counter = 0u; // re-arm for the next launch on this stream
+}
+
+// ------------------------------------------------------------ kernel 3a
+// Edge log-likelihood (LIBPLL/core_likelihood_avx.c:1080-1266).
+// grid = number of tiles; result[0] = lnL; persite may be null.
+template <int C>
+__global__ void __launch_bounds__(kSitesPerPass *C)
+    edge_lnl_kernel(DevState s, ModelConst m, unsigned int pclv, int pscaler,
+                    unsigned int cclv, int cscaler, unsigned int matrix, double *persite,
+                    double *partials, unsigned int *counter, double *result)
+{
+  constexpr int T = kSitesPerPass * C;
+  __shared__ double pm[C * 16];
+  __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = blockIdx.x * kTileSites + threadIdx.x / C;
+  for (int i = threadIdx.x; i < C * 16; i += T) pm[i] = s.pmat[(size_t)matrix * C * 16 + i];
+  __syncthreads();
+
+  double p[kPasses][4], c[kPasses][4];
+  unsigned int sc[kPasses];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = min(site0 + ps * kSitesPerPass, s.sites - 1);
+    load_entry<C>(s, pclv, site, cat, p[ps]);
+    load_entry<C>(s, cclv, site, cat, c[ps]);
+    sc[ps] = load_scaler(s, pscaler, site) + load_scaler(s, cscaler, site);
+  }
+  double acc = 0.0;
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = site0 + ps * kSitesPerPass;
+    double f[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      f[i] = __dmul_rn(__dmul_rn(m.freqs[i], dot4(pm + cat * 16 + 4 * i, c[ps])), p[ps][i]);
+    const double tk = __dadd_rn(__dadd_rn(f[0], f[1]), __dadd_rn(f[2], f[3]));
+    // terma += tk * w only for tk > 0, categories in order (:1225-1241)
+    double term = (tk > 0.0) ? __dmul_rn(tk, m.rate_weight) : 0.0;
+    double terma = term; // lane cat 0 ends up with ((t0 + t1) + t2) + ...
+#pragma unroll
+    for (int k = 1; k < C; ++k)
+      terma = __dadd_rn(terma, __shfl_down_sync(0xffffffffu, term, k, C));
+    if (cat == 0 && site < s.sites)
+    {
+      double lk = log(terma);
+      if (sc[ps]) lk = __dadd_rn(lk, __dmul_rn((double)sc[ps], m.log_scale_thr));
+      if (persite) persite[site] = lk;
+      acc = __dadd_rn(acc, lk);
+    }
+  }
+  const double mine[1] = {block_sum<T>(acc, red)};
+  finish_tiles<T, 1>(mine, partials, gridDim.x, counter, result, red);
+}
+
+// ------------------------------------------------------------ kernel 3b
+// Sumtable (LIBPLL/core_derivatives_avx.c:25-207): per entry
+//   sum_j = dot4(tt_inv[j], clvp) * dot4(evecs[j], clvc)
+template <int C>
+__device__ __forceinline__ void sumtable_entry(const ModelConst &m, const double p[4],
+                                               const double c[4], double out[4])
+{
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    out[j] = __dmul_rn(dot4(m.tt_inv + 4 * j, p), dot4(m.evecs + 4 * j, c));
+}
+
+template <int C>
+__global__ void __launch_bounds__(kSitesPerPass *C)
+    sumtable_kernel(DevState s, ModelConst m, unsigned int pclv, unsigned int cclv,
+                    double *sumtable)
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = blockIdx.x * kTileSites + threadIdx.x / C;
+  double p[kPasses][4], c[kPasses][4];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = min(site0 + ps * kSitesPerPass, s.sites - 1);
+    load_entry<C>(s, pclv, site, cat, p[ps]);
+    load_entry<C>(s, cclv, site, cat, c[ps]);
+  }
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = site0 + ps * kSitesPerPass;
+    double out[4];
+    sumtable_entry<C>(m, p[ps], c[ps], out);
+    if (site < s.sites) st256(sumtable + ((size_t)site * C + cat) * 4, out);
+  }
+}
+
+// ------------------------------------------------------------ kernel 4
+// Derivatives of -lnL from the sumtable and the Newton-Raphson control loop.
+
+// diag[(c*4+j)*3 + {0,1,2}] = {e, (lambda r) e, (lambda r)^2 e}, e = exp(lambda_j r_c t)
+// (LIBPLL/core_derivatives.c:560-575; prop_invar = 0 so ki = r_c / 1.0)
+template <int C>
+__device__ __forceinline__ void fill_diag(const ModelConst &m, double len, double *diag)
+{
+  if (threadIdx.x < C * 4)
+  {
+    const int c = threadIdx.x / 4, j = threadIdx.x % 4;
+    const double ki = m.rates[c] / (1.0 - 0.0);
+    const double lr = __dmul_rn(m.evals[j], ki);
+    const double e = exp(__dmul_rn(lr, len));
+    diag[threadIdx.x * 3 + 0] = e;
+    diag[threadIdx.x * 3 + 1] = __dmul_rn(lr, e);
+    diag[threadIdx.x * 3 + 2] = __dmul_rn(__dmul_rn(__dmul_rn(lr, m.evals[j]), ki), e);
+  }
+}
+
+// One tile of the site sweep.  out[0] += -L'/L terms, out[1] += second
+// derivative terms, out[2] += log-likelihood terms (only if WITH_LNL).
+// Per-site arithmetic follows LIBPLL/core_derivatives_avx.c:1003-1156: sites
+// below `full` (= sites/4*4) use the reciprocal form of the 4-site vector
+// step, the remaining sites the scalar tail with true divisions.
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *sumtable,
+                                           const unsigned int *sclr, unsigned int sites,
+                                           unsigned int tile, const double *diag,
+                                           double out[3])
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  const unsigned int full = sites / 4 * 4;
+  double sv[kPasses][4];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = min(site0 + ps * kSitesPerPass, sites - 1);
+    ld256_stream(sumtable + ((size_t)site * C + cat) * 4, sv[ps]);
+  }
+  const double *dg = diag + cat * 12;
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = site0 + ps * kSitesPerPass;
+    double ck[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+    {
+      double a = __dadd_rn(0.0, __dmul_rn(sv[ps][0], dg[0 * 3 + q]));
+      a = __dadd_rn(a, __dmul_rn(sv[ps][1], dg[1 * 3 + q]));
+      a = __dadd_rn(a, __dmul_rn(sv[ps][2], dg[2 * 3 + q]));
+      ck[q] = __dadd_rn(a, __dmul_rn(sv[ps][3], dg[3 * 3 + q]));
+    }
+    double lk[3] = {ck[0], ck[1], ck[2]};
+    double term = 0.0, terma = 0.0;
+    if (WITH_LNL)
+    {
+      term = (ck[0] > 0.0) ? __dmul_rn(ck[0], m.rate_weight) : 0.0;
+      terma = term;
+    }
+#pragma unroll
+    for (int k = 1; k < C; ++k)
+    {
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        lk[q] = __dadd_rn(lk[q], __shfl_down_sync(0xffffffffu, ck[q], k, C));
+      if (WITH_LNL) terma = __dadd_rn(terma, __shfl_down_sync(0xffffffffu, term, k, C));
+    }
+    if (cat == 0 && site < sites)
+    {
+      if (site < full)
+      {
+        const double recip = __ddiv_rn(1.0, lk[0]);
+        const double a = __dmul_rn(lk[1], recip);
+        const double b = __dadd_rn(__dmul_rn(a, a), -__dmul_rn(lk[2], recip));
+        out[0] = __dadd_rn(out[0], -a);
+        out[1] = __dadd_rn(out[1], b);
+      }
+      else
+      {
+        const double a = -__ddiv_rn(lk[1], lk[0]);
+        const double b = __dadd_rn(__dmul_rn(a, a), -__ddiv_rn(lk[2], lk[0]));
+        out[0] = __dadd_rn(out[0], a);
+        out[1] = __dadd_rn(out[1], b);
+      }
+      if (WITH_LNL)
+      {
+        double l = log(terma);
+        const unsigned int sc = sclr ? sclr[site] : 0u;
+        if (sc) l = __dadd_rn(l, __dmul_rn((double)sc, m.log_scale_thr));
+        out[2] = __dadd_rn(out[2], l);
+      }
+    }
+  }
+}
+
+struct NewtonArgs
+{
+  ModelConst m;
+  const double *sumtables;  // [B][entry_stride]
+  size_t entry_stride;      // doubles between consecutive entries' sumtables
+  const unsigned int *sclr; // [B][sites] summed scaler counts, or null (=> 0)
+  NewtonState *st;          // [B]
+  double *partials;         // [B][ntiles][2]
+  unsigned int sites, B, ntiles, max_iter;
+  double eps, lambda;
+  int want_lnl;
+};
+
+// Persistent cooperative kernel: the whole Newton-Raphson loop of
+// Partition::OptimizeBranch (PTPLL/pll_partition.cpp:419-481) for B branches
+// at once.  Each iteration = one sweep of every still-running branch's
+// sumtable (tiles spread over all CTAs), a grid barrier, a fixed-order
+// reduction + the scalar update done by one CTA per branch, a grid barrier.
+template <int C>
+__global__ void __launch_bounds__(kSitesPerPass *C) newton_kernel(NewtonArgs a)
+{
+  constexpr int T = kSitesPerPass * C;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double diag[C * 12];
+  __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  const unsigned int nwork = a.B * a.ntiles;
+
+  for (unsigned int it = 0; it < a.max_iter; ++it)
+  {
+    for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
+    {
+      const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+      if (__ldcg(&a.st[e].done)) continue;
+      __syncthreads();
+      fill_diag<C>(a.m, __ldcg(&a.st[e].len), diag);
+      __syncthreads();
+      double out[3] = {0.0, 0.0, 0.0};
+      sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+                           tile, diag, out);
+      const double s1 = block_sum<T>(out[0], red);
+      const double s2 = block_sum<T>(out[1], red);
+      if (threadIdx.x == 0)
+      {
+        a.partials[(size_t)w * 2 + 0] = s1;
+        a.partials[(size_t)w * 2 + 1] = s2;
+      }
+    }
+    grid.sync();
+    for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+    {
+      if (__ldcg(&a.st[e].done)) continue;
+      double a1 = 0.0, a2 = 0.0;
+      for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
+      {
+        a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.ntiles + t) * 2 + 0));
+        a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.ntiles + t) * 2 + 1));
+      }
+      a1 = block_sum<T>(a1, red);
+      a2 = block_sum<T>(a2, red);
+      if (threadIdx.x == 0)
+      {
+        NewtonState st;
+        st.len = __ldcg(&a.st[e].len);
+        st.lnl = 0.0;
+        st.iters = __ldcg(&a.st[e].iters);
+        st.done = 0;
+        st.maybe_decreasing = __ldcg(&a.st[e].maybe_decreasing);
+        st.status = 0;
+        double d1 = a1, d2 = a2;
+        if (a.lambda != 0.0) d1 = __dadd_rn(d1, a.lambda);
+        st.d1 = d1;
+        st.d2 = d2;
+        st.iters += 1;
+        if (!isfinite(d1)) { st.status = 1; st.done = 1; }
+        else if (!isfinite(d2)) { st.status = 2; st.done = 1; }
+        else if (fabs(d1) < a.eps) st.done = 1;
+        else
+        {
+          const double step = __ddiv_rn(d1, d2);
+          st.len = (d2 < 0.0) ? __dadd_rn(st.len, step) : __dadd_rn(st.len, -step);
+          if (st.len < 0.0)
+          {
+            st.len = a.eps;
+            if (st.maybe_decreasing) st.done = 1;
+            st.maybe_decreasing = 1;
+          }
+        }
+        if (st.iters >= (int)a.max_iter) st.done = 1;
+        a.st[e] = st;
+      }
+    }
+    grid.sync();
+    int active = 0;
+    for (unsigned int e = threadIdx.x; e < a.B; e += T) active |= !__ldcg(&a.st[e].done);
+    if (!__syncthreads_or(active)) break;
+  }
+
+  if (!a.want_lnl) return;
+  // log-likelihood at the final length, from the same sumtable
+  for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
+  {
+    const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+    __syncthreads();
+    fill_diag<C>(a.m, __ldcg(&a.st[e].len), diag);
+    __syncthreads();
+    double out[3] = {0.0, 0.0, 0.0};
+    sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                        a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, diag,
+                        out);
+    const double s = block_sum<T>(out[2], red);
+    if (threadIdx.x == 0) a.partials[(size_t)w * 2] = s;
+  }
+  grid.sync();
+  for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+  {
+    double acc = 0.0;
+    for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
+      acc = __dadd_rn(acc, __ldcg(a.partials + ((size_t)e * a.ntiles + t) * 2));
+    acc = block_sum<T>(acc, red);
+    if (threadIdx.x == 0) a.st[e].lnl = acc;
+  }
+}
+
+// ------------------------------------------------- NNI candidate preparation
+// For candidate b (blockIdx.y) and one tile of sites: the two CLV updates that
+// face each other across the swapped edge (kept in registers, never written),
+// their per-site scaler counts, and the sumtable entries of the central edge.
+// Reads 4 neighbour CLVs (or tip masks) + their scaler words; writes the
+// candidate's sumtable (32 B per entry) and one summed scaler word per site.
+template <int C>
+__global__ void __launch_bounds__(kSitesPerPass *C)
+    nni_prepare_kernel(DevState s, ModelConst m, const DevCand *__restrict__ cands,
+                       double *sumtables, size_t entry_stride, unsigned int *sclr)
+{
+  constexpr int T = kSitesPerPass * C;
+  __shared__ double mats[4][C * 16];
+  const unsigned int b = blockIdx.y;
+  const DevCand cd = cands[b];
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = blockIdx.x * kTileSites + threadIdx.x / C;
+  for (int i = threadIdx.x; i < C * 16; i += T)
+  {
+    mats[0][i] = s.pmat[(size_t)cd.p.c1_mat * C * 16 + i];
+    mats[1][i] = s.pmat[(size_t)cd.p.c2_mat * C * 16 + i];
+    mats[2][i] = s.pmat[(size_t)cd.q.c1_mat * C * 16 + i];
+    mats[3][i] = s.pmat[(size_t)cd.q.c2_mat * C * 16 + i];
+  }
+  __syncthreads();
+  double *out = sumtables + (size_t)b * entry_stride;
+
+#pragma unroll 2
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site_raw = site0 + ps * kSitesPerPass;
+    const unsigned int site = min(site_raw, s.sites - 1);
+    double x1[4], x2[4], y1[4], y2[4];
+    load_entry<C>(s, cd.p.c1_clv, site, cat, x1);
+    load_entry<C>(s, cd.p.c2_clv, site, cat, x2);
+    load_entry<C>(s, cd.q.c1_clv, site, cat, y1);
+    load_entry<C>(s, cd.q.c2_clv, site, cat, y2);
+    unsigned int cnt = load_scaler(s, cd.p.c1_scaler, site) + load_scaler(s, cd.p.c2_scaler, site) +
+                       load_scaler(s, cd.q.c1_scaler, site) + load_scaler(s, cd.q.c2_scaler, site);
+    double pp[4], qq[4];
+    combine_entry(mats[0] + cat * 16, mats[1] + cat * 16, x1, x2, pp);
+    combine_entry(mats[2] + cat * 16, mats[3] + cat * 16, y1, y2, qq);
+    bool sp = (pp[0] < PT_SCALE_THRESHOLD) & (pp[1] < PT_SCALE_THRESHOLD) &
+              (pp[2] < PT_SCALE_THRESHOLD) & (pp[3] < PT_SCALE_THRESHOLD);
+    bool sq = (qq[0] < PT_SCALE_THRESHOLD) & (qq[1] < PT_SCALE_THRESHOLD) &
+              (qq[2] < PT_SCALE_THRESHOLD) & (qq[3] < PT_SCALE_THRESHOLD);
+    sp = site_all<C>(sp);
+    sq = site_all<C>(sq);
+    if (sp)
+    {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pp[i] = __dmul_rn(pp[i], PT_SCALE_FACTOR);
+    }
+    if (sq)
+    {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) qq[i] = __dmul_rn(qq[i], PT_SCALE_FACTOR);
+    }
+    cnt += (sp ? 1u : 0u) + (sq ? 1u : 0u);
+    double sum[4];
+    sumtable_entry<C>(m, pp, qq, sum);
+    if (site_raw < s.sites)
+    {
+      st256(out + ((size_t)site * C + cat) * 4, sum);
+      if (cat == 0) sclr[(size_t)b * s.sites + site] = cnt;
+    }
+  }
+}
+
+} // namespace ptgpu

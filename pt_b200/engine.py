@@ -1,0 +1,211 @@
+"""ctypes front-end of the C ABI in include/ptgpu.h (pt_b200/lib/libptgpu.so).
+
+Plumbing only: every method is one C-ABI call on host buffers.  There is no
+Python or CPU implementation behind it -- if the CUDA library is missing or no
+device is present, construction fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libptgpu.so")
+
+PTGPU_OK = 0
+PTGPU_ERR_CUDA = -1
+PTGPU_ERR_ARG = -2
+PTGPU_ERR_STATE = -3
+PTGPU_ERR_NOT_FINITE = -4
+
+# == ptgpu_operation_t == pll_operation_t (libpll pll.h:249-259)
+OP_DTYPE = np.dtype([
+    ("parent_clv_index", np.uint32), ("parent_scaler_index", np.int32),
+    ("child1_clv_index", np.uint32), ("child1_matrix_index", np.uint32),
+    ("child1_scaler_index", np.int32),
+    ("child2_clv_index", np.uint32), ("child2_matrix_index", np.uint32),
+    ("child2_scaler_index", np.int32)])
+CAND_DTYPE = np.dtype([("p", OP_DTYPE), ("q", OP_DTYPE), ("length0", np.float64)])
+assert OP_DTYPE.itemsize == 32 and CAND_DTYPE.itemsize == 72
+
+_dp = C.POINTER(C.c_double)
+_up = C.POINTER(C.c_uint)
+_lib = None
+
+
+class PtGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"ptgpu error {code}: {msg}")
+        self.code = code
+
+
+def load_library():
+    """dlopen the engine; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(the engine has no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    L.ptgpu_last_error.restype = C.c_char_p
+    L.ptgpu_stream.restype = C.c_void_p
+    L.ptgpu_stream.argtypes = [C.c_void_p]
+    L.ptgpu_destroy.argtypes = [C.c_void_p]
+    L.ptgpu_destroy.restype = None
+    _lib = L
+    return L
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def ops_array(rows):
+    """list of 8-int rows (pll_operation_t field order) -> structured array"""
+    a = np.asarray(rows, dtype=np.int64).reshape(-1, 8)
+    out = np.zeros(len(a), dtype=OP_DTYPE)
+    for k, name in enumerate(OP_DTYPE.names):
+        out[name] = a[:, k]
+    return out
+
+
+class Engine:
+    """One alignment resident on one B200 (a ptgpu_engine handle)."""
+
+    def __init__(self, tips, clv_buffers, sites, rate_cats, prob_matrices, scale_buffers,
+                 device=0):
+        self.lib = load_library()
+        self.h = C.c_void_p()
+        self.tips, self.clv_buffers, self.sites, self.cats = tips, clv_buffers, sites, rate_cats
+        self.prob_matrices, self.scale_buffers = prob_matrices, scale_buffers
+        self._chk(self.lib.ptgpu_create(C.c_uint(tips), C.c_uint(clv_buffers), C.c_uint(sites),
+                                        C.c_uint(rate_cats), C.c_uint(prob_matrices),
+                                        C.c_uint(scale_buffers), C.c_int(device),
+                                        C.byref(self.h)))
+
+    def _chk(self, rc):
+        if rc != PTGPU_OK:
+            raise PtGpuError(rc, self.lib.ptgpu_last_error().decode())
+
+    def close(self):
+        if self.h:
+            self.lib.ptgpu_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- model / data -----------------------------------------------------
+    def set_model(self, freqs, subst, rates):
+        f = np.ascontiguousarray(freqs, dtype=np.float64)
+        s = np.ascontiguousarray(subst, dtype=np.float64)
+        r = np.ascontiguousarray(rates, dtype=np.float64)
+        assert len(f) == 4 and len(s) == 6 and len(r) == self.cats
+        self._chk(self.lib.ptgpu_set_model(self.h, _d(f), _d(s), _d(r)))
+
+    def eigen(self):
+        ev = np.empty(16); iv = np.empty(16); el = np.empty(4)
+        self._chk(self.lib.ptgpu_get_eigen(self.h, _d(ev), _d(iv), _d(el)))
+        return ev, iv, el
+
+    def set_tip_states(self, tip, seq):
+        b = seq.encode() if isinstance(seq, str) else bytes(seq)
+        if len(b) != self.sites:
+            raise ValueError("sequence length does not match the partition")
+        self._chk(self.lib.ptgpu_set_tip_states(self.h, C.c_uint(tip), b))
+
+    # --- hot path -----------------------------------------------------------
+    def update_prob_matrices(self, indices, lengths):
+        i = np.ascontiguousarray(indices, dtype=np.uint32)
+        l = np.ascontiguousarray(lengths, dtype=np.float64)
+        self._chk(self.lib.ptgpu_update_prob_matrices(self.h, i.ctypes.data_as(_up), _d(l),
+                                                      C.c_uint(len(i))))
+
+    def update_partials(self, ops):
+        o = np.ascontiguousarray(ops, dtype=OP_DTYPE)
+        self._chk(self.lib.ptgpu_update_partials(self.h, o.ctypes.data_as(C.c_void_p),
+                                                 C.c_uint(len(o))))
+
+    def edge_loglikelihood(self, pclv, pscaler, cclv, cscaler, matrix, persite=False):
+        out = C.c_double()
+        ps = np.empty(self.sites) if persite else None
+        self._chk(self.lib.ptgpu_compute_edge_loglikelihood(
+            self.h, C.c_uint(pclv), C.c_int(pscaler), C.c_uint(cclv), C.c_int(cscaler),
+            C.c_uint(matrix), None if ps is None else _d(ps), C.byref(out)))
+        return (out.value, ps) if persite else out.value
+
+    def update_sumtable(self, pclv, cclv, pscaler=-1, cscaler=-1):
+        self._chk(self.lib.ptgpu_update_sumtable(self.h, C.c_uint(pclv), C.c_uint(cclv),
+                                                 C.c_int(pscaler), C.c_int(cscaler)))
+
+    def derivatives(self, length):
+        d1 = C.c_double(); d2 = C.c_double()
+        self._chk(self.lib.ptgpu_compute_likelihood_derivatives(
+            self.h, C.c_double(length), C.byref(d1), C.byref(d2)))
+        return d1.value, d2.value
+
+    def optimize_branch(self, pclv, pscaler, cclv, cscaler, matrix, length0, max_iter=32,
+                        eps=1e-6, map_lambda=0.0):
+        out = C.c_double(); it = C.c_int()
+        self._chk(self.lib.ptgpu_optimize_branch(
+            self.h, C.c_uint(pclv), C.c_int(pscaler), C.c_uint(cclv), C.c_int(cscaler),
+            C.c_uint(matrix), C.c_double(length0), C.c_uint(max_iter), C.c_double(eps),
+            C.c_double(map_lambda), C.byref(out), C.byref(it)))
+        return out.value, it.value
+
+    def score_nni_batch(self, cands, max_iter=32, eps=1e-6, map_lambda=0.0):
+        c = np.ascontiguousarray(cands, dtype=CAND_DTYPE)
+        n = len(c)
+        lens = np.empty(n); lnl = np.empty(n); st = np.zeros(n, dtype=np.int32)
+        self._chk(self.lib.ptgpu_score_nni_batch(
+            self.h, c.ctypes.data_as(C.c_void_p), C.c_uint(n), C.c_uint(max_iter),
+            C.c_double(eps), C.c_double(map_lambda), _d(lens), _d(lnl),
+            st.ctypes.data_as(C.POINTER(C.c_int))))
+        return lens, lnl, st
+
+    # --- test hooks -----------------------------------------------------------
+    def get_clv(self, idx):
+        out = np.empty(self.sites * self.cats * 4)
+        self._chk(self.lib.ptgpu_get_clv(self.h, C.c_uint(idx), _d(out)))
+        return out
+
+    def set_clv(self, idx, data):
+        a = np.ascontiguousarray(data, dtype=np.float64)
+        assert a.size == self.sites * self.cats * 4
+        self._chk(self.lib.ptgpu_set_clv(self.h, C.c_uint(idx), _d(a)))
+
+    def get_scaler(self, idx):
+        out = np.empty(self.sites, dtype=np.uint32)
+        self._chk(self.lib.ptgpu_get_scaler(self.h, C.c_int(idx), out.ctypes.data_as(_up)))
+        return out
+
+    def get_pmatrix(self, idx):
+        out = np.empty(self.cats * 16)
+        self._chk(self.lib.ptgpu_get_pmatrix(self.h, C.c_uint(idx), _d(out)))
+        return out
+
+    def set_pmatrix(self, idx, data):
+        a = np.ascontiguousarray(data, dtype=np.float64)
+        assert a.size == self.cats * 16
+        self._chk(self.lib.ptgpu_set_pmatrix(self.h, C.c_uint(idx), _d(a)))
+
+    def get_sumtable(self):
+        out = np.empty(self.sites * self.cats * 4)
+        self._chk(self.lib.ptgpu_get_sumtable(self.h, _d(out)))
+        return out
+
+    def counters(self):
+        out = (C.c_ulonglong * 4)()
+        self._chk(self.lib.ptgpu_get_counters(self.h, out))
+        return dict(launches=out[0], site_updates=out[1], newton_passes=out[2], candidates=out[3])
+
+    def stream(self):
+        return self.lib.ptgpu_stream(self.h)
+
+    def synchronize(self):
+        self._chk(self.lib.ptgpu_synchronize(self.h))
