@@ -1,0 +1,446 @@
+#!/usr/bin/env python
+"""bench.py -- NNI candidates scored/s (and CLV site-updates/s) on N B200s.
+
+Workload (BASELINE.json configs[2]/[3] shape, the one the north_star target is
+quoted on): synthetic 64 taxa x 1,000,000 sites, GTR+Gamma4 (DS1's model).
+One STEP = one pass of the hot path over one parent tree:
+    P matrices of all 2n-3 branches            (kernel 2)
+    all 3(n-2) directional CLVs                (kernel 1, one launch)
+    every NNI candidate of Wanderer::QueueMoves (2(n-2) = 124) scored with
+    SingleBranchOptimizer semantics            (prepare + cooperative Newton)
+`value`  = candidates/s with the alignment resident in HBM, CUDA events on the
+           engine's stream, max over ranks.
+`e2e`    = the same metric through the C ABI starting from the raw alignment in
+           pinned HOST memory: the step additionally uploads and encodes the n
+           tip sequences (H2D inside the timed region) and reads the results back.
+N > 1: candidate-parallel: alignment and model replicated, every
+rank scores the candidates of its own parent tree, no data-path collective
+(weak scaling); only the timing max goes through NCCL.
+`--impl reference`: the UNMODIFIED reference (oracle/_ref/libpllref.so, built in
+place from /root/reference by oracle/Makefile.ref) timed on the host cores with
+the identical call sequence of SingleBranchOptimizer::EvaluateMove, one private
+partition per thread, on a bounded site sample, scaled to the full site count.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from pytree import Tree, cand_array, random_tree_newick  # noqa: E402
+
+# DS1's GTR+G4 model (tests/golden/data/ds1/RAxML_info.DS1:72,75)
+FREQS = np.array([0.234, 0.257, 0.280, 0.229])
+SUBST = np.array([0.584812, 1.048321, 0.673188, 1.823979, 3.468817, 1.0])
+SEED_TREE, SEED_ALN = 20260001, 20260002
+
+
+def golden_rates():
+    """Gamma(alpha = 0.134946) mean rates exactly as the reference computes them
+    (committed golden vector; pll_compute_gamma_cats, libpll gamma.c:220-292)"""
+    with open(os.path.join(ROOT, "tests", "golden", "ds1_golden.json")) as f:
+        g = json.load(f)
+    return np.array([float.fromhex(x) for x in g["rates"]])
+
+
+RATES = golden_rates()
+
+
+def gtr_pmats(t):
+    """numpy P(t r_c) for data simulation only (not on any measured path)"""
+    pi = FREQS
+    r = SUBST / SUBST[5]
+    q = np.zeros((4, 4))
+    k = 0
+    for i in range(4):
+        for j in range(i + 1, 4):
+            q[i, j] = r[k] * pi[j]
+            q[j, i] = r[k] * pi[i]
+            k += 1
+    q -= np.diag(q.sum(1))
+    q /= -(pi * np.diag(q)).sum()
+    w, v = np.linalg.eig(q)
+    vi = np.linalg.inv(v)
+    return np.stack([(v * np.exp(w * t * rc)) @ vi for rc in RATES]).real
+
+
+def simulate(tree, sites, rng):
+    """alignment simulated down `tree` under GTR+G4, 2% gaps; returns {label: bytes}"""
+    cat = rng.integers(0, 4, sites)
+    state = {}
+    root = tree.root
+    state[id(root)] = rng.choice(4, sites, p=FREQS / FREQS.sum()).astype(np.uint8)
+    out = {}
+    stack = [(x.back, state[id(root)]) for x in (root, root.next, root.next.next)]
+    while stack:
+        node, parent = stack.pop()
+        cum = np.cumsum(gtr_pmats(node.length), axis=2)
+        u = rng.random(sites)
+        child = (u[:, None] > cum[cat, parent]).sum(1).astype(np.uint8).clip(0, 3)
+        if node.is_tip:
+            sym = np.frombuffer(b"ACGT", dtype=np.uint8)[child].copy()
+            sym[rng.random(sites) < 0.02] = ord("-")
+            out[node.label] = sym
+        else:
+            stack.append((node.next.back, child))
+            stack.append((node.next.next.back, child))
+    return out
+
+
+def parent_tree(taxa, rank):
+    """base tree (seed 20260001) moved `rank` random NNIs away: rank r's parent tree"""
+    rng = np.random.default_rng(SEED_TREE)
+    t = Tree(random_tree_newick(taxa, rng))
+    walk = np.random.default_rng(SEED_TREE + 17)
+    for _ in range(rank):
+        inner = [n for n in t.nodes[t.tip_count:] if not n.back.is_tip]
+        t.nni(inner[int(walk.integers(len(inner)))], int(walk.integers(1, 3)))
+    return t
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region"""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.rows, self._stop_evt = device, [], threading.Event()
+
+    def run(self):
+        try:
+            p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                  "-lms", "200", "-i", str(self.device)], stdout=subprocess.PIPE,
+                                 stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            return
+        while not self._stop_evt.is_set():
+            line = p.stdout.readline()
+            if not line:
+                break
+            self.rows.append([x.strip() for x in line.split(",")])
+        p.terminate()
+
+    def stop(self):
+        self._stop_evt.set()
+        sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) > 8:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                    "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None,
+                    sm_max_mhz=max(mx) if mx else None, reasons=sorted(reasons),
+                    samples=len(sm))
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def op_bytes(ops, tips, sites):
+    """algorithmic HBM bytes of a streaming op list: child = 1 B/site if tip mask,
+    else 128 B CLV + 4 B scaler; parent write 128 + 4 (compact tips)"""
+    b = 0
+    for op in ops:
+        for c in (op[2], op[5]):
+            b += 1 if c < tips else 132
+        b += 132
+    return b * sites
+
+
+# --------------------------------------------------------------------------
+# reference arm / CPU baseline: the unmodified reference through libpllref.so
+# --------------------------------------------------------------------------
+class RefWorker:
+    """one private reference partition + the SingleBranchOptimizer::EvaluateMove
+    call sequence for every candidate of one tree
+    (src/move_tester/single_branch_optimizer.cpp:23-64)"""
+
+    def __init__(self, R, newick, labels, seqs):
+        self.p = R.open_mem(newick, labels, seqs, FREQS, SUBST, RATES)
+        self.cands = Tree(newick).nni_candidates()
+
+    def run_pass(self):
+        p = self.p
+        t0 = time.perf_counter()
+        p.traversal_update(p.root, True)
+        for (pidx, kind, _, _, l0) in self.cands:
+            p.nni(pidx, kind)
+            p.invalidate_edge(pidx)
+            p.traversal_update(pidx, False)
+            p.optimize_branch(pidx)
+            p.loglikelihood(pidx)
+            p.update_branch_length(pidx, l0)
+            p.nni(pidx, kind)
+            p.invalidate_edge(pidx)
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.p.close()
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_baseline_single(taxa, sites_full, aln_sample, tree, sample_sites):
+    from oracle.pyoracle import RefLib, have_ref
+    if not have_ref():
+        return None
+    R = RefLib()
+    labels = tree.labels()
+    seqs = [bytes(aln_sample[l][:sample_sites]) for l in labels]
+    w = RefWorker(R, tree.newick(), labels, seqs)
+    times = [w.run_pass() for _ in range(3)]
+    ncand = len(w.cands)
+    w.close()
+    best = min(times[1:])
+    return dict(value=ncand / best * sample_sites / sites_full, unit="candidates/s", cores=1,
+                kind="reference",
+                sample=f"{ncand} candidates x {sample_sites} of {sites_full} sites, 1 thread, "
+                       f"best of 2 passes ({best:.2f} s), scaled by sites ratio",
+                raw_candidates_per_s_at_sample=ncand / best)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle.pyoracle import RefLib, have_ref
+    if not have_ref():
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "oracle/_ref/libpllref.so missing (build() needs /root/reference)"}))
+        return
+    T = host_cores()
+    sample = int(min(20000, max(2000, 16e9 / T / (2 * args.taxa * 128 * 4))))
+    sample = min(sample, args.sites)
+    base = parent_tree(args.taxa, 0)
+    aln = simulate(base, sample, np.random.default_rng(SEED_ALN))
+    R = RefLib()
+    trees = [parent_tree(args.taxa, r) for r in range(T)]
+    workers = [RefWorker(R, t.newick(), t.labels(), [bytes(aln[l]) for l in t.labels()])
+               for t in trees]
+    ncand = sum(len(w.cands) for w in workers)
+    step_s = []
+    with ThreadPoolExecutor(T) as ex:
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            list(ex.map(lambda w: w.run_pass(), workers))
+            dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                step_s.append(dt)
+    for w in workers:
+        w.close()
+    total = sum(step_s)
+    value = ncand * len(step_s) / total * sample / args.sites
+    line = dict(metric="nni_candidates_scored_per_s", value=value, unit="candidates/s",
+                impl="reference", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * total / len(step_s), higher_is_better=True, scaling="weak",
+                vs_baseline=None, dtype="f64", data="synthetic",
+                config=dict(workload=f"synthetic {args.taxa} taxa x {args.sites} sites GTR+G4, "
+                                     f"all {ncand // T} NNI candidates of one tree per thread, "
+                                     "SingleBranchOptimizer (radius 0)",
+                            taxa=args.taxa, sites=args.sites, rate_cats=4),
+                cpu_baseline=dict(value=value, unit="candidates/s", cores=T, kind="reference",
+                                  sample=f"{T} threads x one tree ({ncand // T} candidates) x {sample} "
+                                         f"of {args.sites} sites per step, scaled by sites ratio"),
+                e2e=dict(value=value, unit="candidates/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    from pt_b200.engine import Engine, ops_array
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    n, S = args.taxa, args.sites
+    base = parent_tree(n, 0)
+    aln = simulate(base, S, np.random.default_rng(SEED_ALN))
+    tree = parent_tree(n, rank)
+    labels = tree.labels()
+    # raw alignment in pinned host memory (what a caller hands to the C ABI)
+    host_aln = torch.empty((n, S), dtype=torch.uint8).pin_memory()
+    for i, tip in enumerate(tree.nodes[:n]):
+        host_aln[tip.clv_index].copy_(torch.from_numpy(aln[tip.label]))
+    nbuf = 3 * (n - 2)
+    e = Engine(n, nbuf, S, 4, 2 * n - 3, nbuf, device=local)
+    e.set_model(FREQS, SUBST, RATES)
+
+    def upload_tips():
+        for t in range(n):
+            e.set_tip_states_ptr(t, host_aln[t].data_ptr())
+
+    upload_tips()
+    br = tree.branches()
+    midx = np.array(list(br.keys()), dtype=np.uint32)
+    mlen = np.array(list(br.values()), dtype=np.float64)
+    plan_rows = tree.directional_plan()
+    plan = ops_array(plan_rows)
+    cand_rows = tree.nni_candidates()
+    cands = cand_array(cand_rows)
+    ncand = len(cands)
+
+    def step():
+        e.update_prob_matrices(midx, mlen)
+        e.update_partials(plan)
+        return e.score_nni_batch(cands)
+
+    for _ in range(args.warmup):
+        lens, lnls, status = step()
+    assert not status.any() and np.all(np.isfinite(lnls))
+
+    stream = torch.cuda.ExternalStream(e.stream(), device=torch.device("cuda", local))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e.set_profiling(True)
+    e.kernel_times(reset=True)
+    c0 = e.counters()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    kt = e.kernel_times(reset=True)
+    c1 = e.counters()
+    e.set_profiling(False)
+
+    # end to end: raw alignment in pinned host memory -> scores on the host
+    t_e2e = []
+    for i in range(1 + args.steps):
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        upload_tips()
+        out = step()
+        torch.cuda.synchronize()
+        if i:
+            t_e2e.append(time.perf_counter() - t0)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e_s = sum(t_e2e)
+
+    if dist:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+    if rank != 0:
+        if dist:
+            dist.destroy_process_group()
+        return
+
+    steps = args.steps
+    value = world * ncand * steps / (ms * 1e-3)
+    launches = c1["launches"] - c0["launches"]
+    site_updates = c1["site_updates"] - c0["site_updates"]
+    passes = c1["newton_passes"] - c0["newton_passes"]
+    peak, peak_kind = measured_peak()
+    child_bytes = sum((1 if c < n else 132) for row in cand_rows for c in (row[2][2], row[2][5], row[3][2], row[3][5]))
+    algo = dict(
+        partials=op_bytes(plan_rows, n, S),                                  # per launch
+        nni_prepare=(child_bytes + ncand * 132) * S,                          # per launch
+        newton=(passes / steps) * S * 128 + ncand * S * 132,                  # per launch
+    )
+    kernels = {}
+    for k, bytes_per_launch in algo.items():
+        tot_ms, nl = kt[k]
+        if nl:
+            per = tot_ms / nl
+            kernels[k] = dict(ms_per_launch=per, launches_per_step=nl / steps,
+                              share_of_step=tot_ms / ms,
+                              achieved_gbs=bytes_per_launch / (per * 1e-3) / 1e9,
+                              algorithmic_bytes_per_launch=int(bytes_per_launch))
+    dom = max(kernels, key=lambda k: kernels[k]["share_of_step"])
+    roof = dict(bound="hbm", kernel=dom, achieved=kernels[dom]["achieved_gbs"], peak=peak,
+                unit="GB/s", frac=kernels[dom]["achieved_gbs"] / peak, peak_source=peak_kind,
+                traffic=None)
+    h2d = n * S + midx.nbytes + mlen.nbytes + plan.nbytes + cands.nbytes
+    d2h = ncand * (8 + 8 + 4)
+    line = dict(
+        metric="nni_candidates_scored_per_s", value=value, unit="candidates/s",
+        n_gpus=world, steps=steps, warmup=args.warmup, ms_per_step=ms / steps,
+        higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+        config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]/[3] shape): "
+                             f"per step all {ncand} NNI candidates of one parent tree per GPU, "
+                             "SingleBranchOptimizer (radius 0) semantics, incl. P matrices and "
+                             "all directional CLVs", taxa=n, sites=S, rate_cats=4,
+                    candidates_per_step_per_gpu=ncand, parallelism=f"candidate-parallel x{world}",
+                    l2="inputs (>20 GB of CLVs per step) far exceed the 126 MB L2; no flush needed"),
+        clv_site_updates_per_s=world * site_updates / (kt["partials"][0] * 1e-3) if kt["partials"][0] else None,
+        newton_iterations_per_candidate=passes / steps / ncand,
+        gpu_launches=int(launches), kernels=kernels, roofline=roof, clocks=clocks,
+        e2e=dict(value=world * ncand * len(t_e2e) / e2e_s, unit="candidates/s",
+                 h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h),
+                 note="raw alignment in pinned host memory uploaded + encoded every step"),
+        lnl_checksum=float(np.sum(lnls)),
+    )
+    if world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline_single(n, S, aln, tree, min(S, args.cpu_sample_sites))
+        if cb:
+            line["cpu_baseline"] = cb
+    print(json.dumps(line))
+    if dist:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--taxa", type=int, default=64)
+    ap.add_argument("--sites", type=int, default=1000000)
+    ap.add_argument("--cpu-sample-sites", type=int, default=100000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -96,7 +96,9 @@ int ptgpu_get_eigen(ptgpu_engine *e, double evecs[16], double inv_evecs[16],
 
 /* pll_set_tip_states(partition, tip, pll_map_nt, sequence)
    (LIBPLL/pll.c:941-964, LIBPLL/maps.c:46-64): IUPAC nucleotide codes, gap/N/? =
-   fully ambiguous; an unknown character is PTGPU_ERR_STATE. */
+   fully ambiguous; an unknown character is PTGPU_ERR_STATE.  `sequence` is a
+   host buffer of `sites` characters; they are copied as they are and encoded
+   to state masks by a kernel (pass pinned memory for an asynchronous copy). */
 int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index,
                          const char *sequence);
 
@@ -162,6 +164,21 @@ int ptgpu_get_sumtable(ptgpu_engine *e, double *out);
 /* counters since create: [0] kernel launches, [1] CLV site-updates,
    [2] Newton derivative passes (site sweeps), [3] NNI candidates scored */
 int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[4]);
+
+/* Optional per-kernel timing with CUDA events on the engine's stream (used by
+   bench.py for the roofline figures; off by default).  Kinds index the arrays
+   of ptgpu_get_kernel_times, which drains pending events (synchronises). */
+#define PTGPU_KERNEL_PMATRIX 0
+#define PTGPU_KERNEL_PARTIALS 1
+#define PTGPU_KERNEL_EDGE_LNL 2
+#define PTGPU_KERNEL_SUMTABLE 3
+#define PTGPU_KERNEL_NEWTON 4
+#define PTGPU_KERNEL_NNI_PREPARE 5
+#define PTGPU_KERNEL_TIP_ENCODE 6
+#define PTGPU_KERNEL_KINDS 7
+int ptgpu_set_profiling(ptgpu_engine *e, int on);
+int ptgpu_get_kernel_times(ptgpu_engine *e, double ms_out[PTGPU_KERNEL_KINDS],
+                           unsigned long long launches_out[PTGPU_KERNEL_KINDS], int reset);
 
 /* the engine's stream (a cudaStream_t) so callers can order their own CUDA
    events / work against it */

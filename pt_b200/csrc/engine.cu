@@ -68,6 +68,7 @@ struct ptgpu_engine
   DevState dev{};
   ModelConst model{};
   uint8_t *d_tips = nullptr;
+  uint8_t *d_raw = nullptr;         // raw characters of the tip being encoded
   double *d_sumtable = nullptr;
   double *d_persite = nullptr;      // per-site lnL scratch (allocated on first use)
   double *d_partials = nullptr;     // [ntiles * 2] tile partials of single-edge reductions
@@ -91,7 +92,41 @@ struct ptgpu_engine
   int coop_blocks_per_sm = 0;
   int sm_count = 0;
   unsigned long long counters[4] = {0, 0, 0, 0};
+  // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
+  bool profiling = false;
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> pending;
+  std::vector<cudaEvent_t> event_pool;
+  double kernel_ms[PTGPU_KERNEL_KINDS] = {};
+  unsigned long long kernel_launches[PTGPU_KERNEL_KINDS] = {};
 };
+
+namespace {
+// RAII bracket around one kernel launch: counts it and, when profiling is on,
+// records a start/stop event pair on the engine's stream.
+struct LaunchScope
+{
+  ptgpu_engine *e;
+  int kind;
+  cudaEvent_t a = nullptr, b = nullptr;
+  static cudaEvent_t take(ptgpu_engine *e)
+  {
+    cudaEvent_t ev = nullptr;
+    if (!e->event_pool.empty()) { ev = e->event_pool.back(); e->event_pool.pop_back(); }
+    else cudaEventCreate(&ev);
+    return ev;
+  }
+  LaunchScope(ptgpu_engine *eng, int k) : e(eng), kind(k)
+  {
+    e->counters[0]++;
+    e->kernel_launches[kind]++;
+    if (e->profiling) { a = take(e); b = take(e); cudaEventRecord(a, e->stream); }
+  }
+  ~LaunchScope()
+  {
+    if (a) { cudaEventRecord(b, e->stream); e->pending.push_back({kind, {a, b}}); }
+  }
+};
+} // namespace
 
 namespace {
 
@@ -234,11 +269,13 @@ void ptgpu_destroy(ptgpu_engine *e)
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
-  cudaFree(e->d_tips); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
+  cudaFree(e->d_tips); cudaFree(e->d_raw); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
   cudaFree(e->d_sumtable); cudaFree(e->d_persite); cudaFree(e->d_partials); cudaFree(e->d_counter);
   cudaFree(e->d_state); cudaFree(e->d_idx1);
   cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials);
   cudaFree(e->d_bcands); cudaFree(e->d_ops); cudaFree(e->d_midx); cudaFree(e->d_mlen);
+  for (auto &p : e->pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
+  for (auto ev : e->event_pool) cudaEventDestroy(ev);
   if (e->stg.host) cudaFreeHost(e->stg.host);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
@@ -273,18 +310,36 @@ int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *se
 {
   if (!e || !sequence) return fail(PTGPU_ERR_ARG, "ptgpu_set_tip_states: null argument");
   if (tip_index >= e->tips) return fail(PTGPU_ERR_ARG, "tip index %u out of range", tip_index);
-  std::vector<uint8_t> masks(e->sites);
-  for (unsigned int i = 0; i < e->sites; ++i)
-  {
-    const unsigned char ch = (unsigned char)sequence[i];
-    const unsigned int mk = ch ? nucleotide_mask(ch) : 0;
-    if (!mk) return fail(PTGPU_ERR_STATE, "Illegal state code in tip \"%c\" (site %u)", ch ? ch : '?', i);
-    masks[i] = (uint8_t)mk;
-  }
+  static const TipLut lut = [] {
+    TipLut t;
+    for (int c = 0; c < 256; ++c) t.m[c] = (uint8_t)nucleotide_mask((unsigned char)c);
+    t.m[0] = 0;
+    return t;
+  }();
   CU(cudaSetDevice(e->device));
-  CU(cudaMemcpyAsync(e->d_tips + (size_t)tip_index * e->sites, masks.data(), e->sites,
-                     cudaMemcpyHostToDevice, e->stream));
+  if (!e->d_raw) CU(cudaMalloc(&e->d_raw, e->sites));
+  // the characters are encoded on the device: one H2D copy of the raw bytes
+  // (asynchronous when the caller's buffer is pinned) and one byte-map kernel
+  unsigned int *bad_h = (unsigned int *)(e->stg.host + 192);
+  unsigned int *bad_d = (unsigned int *)(e->stg.dev + 192);
   CU(cudaStreamSynchronize(e->stream));
+  *bad_h = 0xffffffffu;
+  CU(cudaMemcpyAsync(e->d_raw, sequence, e->sites, cudaMemcpyHostToDevice, e->stream));
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_TIP_ENCODE);
+    const unsigned int blocks = std::min<unsigned int>((e->sites + 255) / 256, 4u * (unsigned int)e->sm_count);
+    tip_encode_kernel<<<blocks, 256, 0, e->stream>>>((const unsigned char *)e->d_raw,
+                                                     e->d_tips + (size_t)tip_index * e->sites,
+                                                     e->sites, lut, bad_d);
+  }
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(e->stream));
+  const unsigned int bad = *(volatile unsigned int *)bad_h;
+  if (bad != 0xffffffffu)
+  {
+    const unsigned char ch = (unsigned char)sequence[bad];
+    return fail(PTGPU_ERR_STATE, "Illegal state code in tip \"%c\" (site %u)", ch ? ch : '?', bad);
+  }
   return PTGPU_OK;
 }
 
@@ -332,9 +387,11 @@ template <int C>
 int launch_pmatrix(ptgpu_engine *e, const unsigned int *d_idx, const double *d_len, unsigned int count)
 {
   const unsigned int threads = 128, blocks = (count * C + threads - 1) / threads;
-  pmatrix_kernel<C><<<blocks, threads, 0, e->stream>>>(e->dev, e->model, d_idx, d_len, count);
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_PMATRIX);
+    pmatrix_kernel<C><<<blocks, threads, 0, e->stream>>>(e->dev, e->model, d_idx, d_len, count);
+  }
   CU(cudaGetLastError());
-  e->counters[0]++;
   return PTGPU_OK;
 }
 
@@ -345,9 +402,11 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   const unsigned int maxg = (unsigned int)(e->coop_blocks_per_sm * e->sm_count);
   const unsigned int grid = std::min(work, maxg);
   void *params[] = {&a};
-  CU(cudaLaunchCooperativeKernel((void *)newton_kernel<C>, dim3(grid), dim3(kSitesPerPass * C),
-                                 params, 0, e->stream));
-  e->counters[0]++;
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
+    CU(cudaLaunchCooperativeKernel((void *)newton_kernel<C>, dim3(grid), dim3(kSitesPerPass * C),
+                                   params, 0, e->stream));
+  }
   return PTGPU_OK;
 }
 
@@ -396,9 +455,11 @@ int ptgpu_update_partials(ptgpu_engine *e, const ptgpu_operation_t *ops, unsigne
   CU(cudaSetDevice(e->device));
   if ((rc = ensure(&e->d_ops, &e->ops_cap, count))) return rc;
   if ((rc = upload(e, e->d_ops, ops, count * sizeof(DevOp)))) return rc;
-  DISPATCH_CATS(e, (partials_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_PARTIALS);
+    DISPATCH_CATS(e, (partials_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
+  }
   CU(cudaGetLastError());
-  e->counters[0]++;
   e->counters[1] += (unsigned long long)count * e->sites;
   return PTGPU_OK;
 }
@@ -424,11 +485,13 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
     d_persite = e->d_persite;
   }
   double *result = (double *)e->stg.dev;
-  DISPATCH_CATS(e, (edge_lnl_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
-                       e->dev, e->model, parent_clv_index, parent_scaler_index, child_clv_index,
-                       child_scaler_index, matrix_index, d_persite, e->d_partials, e->d_counter, result)));
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_EDGE_LNL);
+    DISPATCH_CATS(e, (edge_lnl_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
+                         e->dev, e->model, parent_clv_index, parent_scaler_index, child_clv_index,
+                         child_scaler_index, matrix_index, d_persite, e->d_partials, e->d_counter, result)));
+  }
   CU(cudaGetLastError());
-  e->counters[0]++;
   if (persite_lnl)
     CU(cudaMemcpyAsync(persite_lnl, d_persite, (size_t)e->sites * sizeof(double),
                        cudaMemcpyDeviceToHost, e->stream));
@@ -448,10 +511,12 @@ int ptgpu_update_sumtable(ptgpu_engine *e, unsigned int parent_clv_index,
   if ((rc = check_clv(e, child_clv_index, "sumtable.child"))) return rc;
   (void)parent_scaler_index; (void)child_scaler_index; // per-site scalers do not enter the sumtable
   CU(cudaSetDevice(e->device));
-  DISPATCH_CATS(e, (sumtable_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
-                       e->dev, e->model, parent_clv_index, child_clv_index, e->d_sumtable)));
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_SUMTABLE);
+    DISPATCH_CATS(e, (sumtable_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
+                         e->dev, e->model, parent_clv_index, child_clv_index, e->d_sumtable)));
+  }
   CU(cudaGetLastError());
-  e->counters[0]++;
   return PTGPU_OK;
 }
 
@@ -571,10 +636,12 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     }
     if ((rc = upload(e, e->d_bcands, cands + base, nb * sizeof(DevCand)))) return rc;
     if ((rc = upload(e, e->d_bstate, hst.data(), nb * sizeof(NewtonState)))) return rc;
-    DISPATCH_CATS(e, (nni_prepare_kernel<C><<<dim3(e->ntiles, nb), kSitesPerPass * C, 0, e->stream>>>(
-                         e->dev, e->model, e->d_bcands, e->d_bsum, stride, e->d_bsclr)));
+    {
+      LaunchScope ls(e, PTGPU_KERNEL_NNI_PREPARE);
+      DISPATCH_CATS(e, (nni_prepare_kernel<C><<<dim3(e->ntiles, nb), kSitesPerPass * C, 0, e->stream>>>(
+                           e->dev, e->model, e->d_bcands, e->d_bsum, stride, e->d_bsclr)));
+    }
     CU(cudaGetLastError());
-    e->counters[0]++;
     NewtonArgs a{};
     a.m = e->model;
     a.sumtables = e->d_bsum;
@@ -683,6 +750,37 @@ int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[4])
 {
   if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_counters: null argument");
   for (int i = 0; i < 4; ++i) out[i] = e->counters[i];
+  return PTGPU_OK;
+}
+
+int ptgpu_set_profiling(ptgpu_engine *e, int on)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_set_profiling: null engine");
+  e->profiling = on != 0;
+  return PTGPU_OK;
+}
+
+int ptgpu_get_kernel_times(ptgpu_engine *e, double ms_out[PTGPU_KERNEL_KINDS],
+                           unsigned long long launches_out[PTGPU_KERNEL_KINDS], int reset)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_get_kernel_times: null engine");
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamSynchronize(e->stream));
+  for (auto &p : e->pending)
+  {
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, p.second.first, p.second.second));
+    e->kernel_ms[p.first] += ms;
+    e->event_pool.push_back(p.second.first);
+    e->event_pool.push_back(p.second.second);
+  }
+  e->pending.clear();
+  for (int k = 0; k < PTGPU_KERNEL_KINDS; ++k)
+  {
+    if (ms_out) ms_out[k] = e->kernel_ms[k];
+    if (launches_out) launches_out[k] = e->kernel_launches[k];
+    if (reset) { e->kernel_ms[k] = 0; e->kernel_launches[k] = 0; }
+  }
   return PTGPU_OK;
 }
 

@@ -186,6 +186,24 @@ __device__ __forceinline__ double block_sum(double v, double *smem /* >= THREADS
   return t;
 }
 
+// Tip encoding: raw alignment characters -> 4-bit state masks through a
+// 256-entry table (pll_map_nt semantics, LIBPLL/maps.c:46-64); the position
+// of the first illegal character (if any) is reported through *bad.
+struct TipLut { uint8_t m[256]; };
+__global__ void tip_encode_kernel(const unsigned char *__restrict__ raw, uint8_t *out,
+                                  unsigned int n, TipLut lut, unsigned int *bad)
+{
+  __shared__ uint8_t t[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) t[i] = lut.m[i];
+  __syncthreads();
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    const uint8_t mk = t[raw[i]];
+    if (!mk) atomicMin(bad, i);
+    out[i] = mk;
+  }
+}
+
 // ------------------------------------------------------------ kernel 2
 // P(t) = I + (V^-1 o expm1(lambda r t)) V per branch and category
 // (LIBPLL/core_pmatrix_avx.c:42-310).  One thread per (branch, category).

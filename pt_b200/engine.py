@@ -119,6 +119,10 @@ class Engine:
             raise ValueError("sequence length does not match the partition")
         self._chk(self.lib.ptgpu_set_tip_states(self.h, C.c_uint(tip), b))
 
+    def set_tip_states_ptr(self, tip, host_ptr):
+        """same call, `host_ptr` = address of `sites` characters (e.g. pinned memory)"""
+        self._chk(self.lib.ptgpu_set_tip_states(self.h, C.c_uint(tip), C.c_void_p(host_ptr)))
+
     # --- hot path -----------------------------------------------------------
     def update_prob_matrices(self, indices, lengths):
         i = np.ascontiguousarray(indices, dtype=np.uint32)
@@ -209,3 +213,16 @@ class Engine:
 
     def synchronize(self):
         self._chk(self.lib.ptgpu_synchronize(self.h))
+
+    KERNEL_KINDS = ("pmatrix", "partials", "edge_lnl", "sumtable", "newton", "nni_prepare",
+                    "tip_encode")
+
+    def set_profiling(self, on=True):
+        self._chk(self.lib.ptgpu_set_profiling(self.h, C.c_int(int(on))))
+
+    def kernel_times(self, reset=True):
+        """{kind: (total ms, launches)} measured with CUDA events on the engine's stream"""
+        ms = (C.c_double * 7)()
+        n = (C.c_ulonglong * 7)()
+        self._chk(self.lib.ptgpu_get_kernel_times(self.h, ms, n, C.c_int(int(reset))))
+        return {k: (ms[i], int(n[i])) for i, k in enumerate(self.KERNEL_KINDS)}
