@@ -64,6 +64,8 @@ struct ptgpu_engine
   unsigned int tips = 0, clv_buffers = 0, sites = 0, cats = 0, prob_matrices = 0,
                scale_buffers = 0;
   unsigned int ntiles = 0;
+  unsigned int nheavy = 0; // tiles of the register-heavy CLV kernels (kHeavyTile sites)
+  unsigned int chunk_tiles = 1, nchunks = 0; // Newton reduction units (functions of `sites` only)
   bool model_set = false;
   DevState dev{};
   ModelConst model{};
@@ -221,6 +223,9 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
+  e->nheavy = (sites + kHeavyTile - 1) / kHeavyTile;
+  e->chunk_tiles = std::min(8u, std::max(1u, e->ntiles / 128u));
+  e->nchunks = (e->ntiles + e->chunk_tiles - 1) / e->chunk_tiles;
   const size_t clv_stride = (size_t)sites * rate_cats * 4;
 #define CU_NEW(call)                                                                    \
   do { cudaError_t err__ = (call); if (err__ != cudaSuccess) { int rc__ = fail(PTGPU_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(err__)); ptgpu_destroy(e); return rc__; } } while (0)
@@ -398,7 +403,7 @@ int launch_pmatrix(ptgpu_engine *e, const unsigned int *d_idx, const double *d_l
 template <int C>
 int launch_newton(ptgpu_engine *e, NewtonArgs &a)
 {
-  const unsigned int work = std::max(1u, a.B * a.ntiles);
+  const unsigned int work = std::max(1u, a.B * a.nchunks);
   const unsigned int maxg = (unsigned int)(e->coop_blocks_per_sm * e->sm_count);
   const unsigned int grid = std::min(work, maxg);
   void *params[] = {&a};
@@ -457,7 +462,7 @@ int ptgpu_update_partials(ptgpu_engine *e, const ptgpu_operation_t *ops, unsigne
   if ((rc = upload(e, e->d_ops, ops, count * sizeof(DevOp)))) return rc;
   {
     LaunchScope ls(e, PTGPU_KERNEL_PARTIALS);
-    DISPATCH_CATS(e, (partials_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
+    DISPATCH_CATS(e, (partials_kernel<C><<<e->nheavy, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
   }
   CU(cudaGetLastError());
   e->counters[1] += (unsigned long long)count * e->sites;
@@ -534,7 +539,7 @@ static int newton_single(ptgpu_engine *e, double len0, unsigned int max_iter, do
   a.sclr = nullptr;
   a.st = e->d_state;
   a.partials = e->d_partials;
-  a.sites = e->sites; a.B = 1; a.ntiles = e->ntiles; a.max_iter = max_iter;
+  a.sites = e->sites; a.B = 1; a.ntiles = e->ntiles; a.chunk_tiles = e->chunk_tiles; a.nchunks = e->nchunks; a.max_iter = max_iter;
   a.eps = eps; a.lambda = lambda; a.want_lnl = 0;
   if ((rc = run_newton(e, a))) return rc;
   e->counters[2] += max_iter; // upper bound; exact count is returned in state.iters
@@ -638,8 +643,8 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     if ((rc = upload(e, e->d_bstate, hst.data(), nb * sizeof(NewtonState)))) return rc;
     {
       LaunchScope ls(e, PTGPU_KERNEL_NNI_PREPARE);
-      DISPATCH_CATS(e, (nni_prepare_kernel<C><<<dim3(e->ntiles, nb), kSitesPerPass * C, 0, e->stream>>>(
-                           e->dev, e->model, e->d_bcands, e->d_bsum, stride, e->d_bsclr)));
+      DISPATCH_CATS(e, (nni_prepare_kernel<C><<<e->nheavy * nb, kHeavySites * C, 0, e->stream>>>(
+                           e->dev, e->model, e->d_bcands, nb, e->d_bsum, stride, e->d_bsclr)));
     }
     CU(cudaGetLastError());
     NewtonArgs a{};
@@ -649,7 +654,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     a.sclr = e->d_bsclr;
     a.st = e->d_bstate;
     a.partials = e->d_bpartials;
-    a.sites = e->sites; a.B = nb; a.ntiles = e->ntiles; a.max_iter = max_iter;
+    a.sites = e->sites; a.B = nb; a.ntiles = e->ntiles; a.chunk_tiles = e->chunk_tiles; a.nchunks = e->nchunks; a.max_iter = max_iter;
     a.eps = epsilon; a.lambda = map_lambda; a.want_lnl = 1;
     if ((rc = run_newton(e, a))) return rc;
     CU(cudaMemcpyAsync(hst.data(), e->d_bstate, nb * sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));

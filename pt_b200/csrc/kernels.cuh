@@ -26,6 +26,11 @@ constexpr int kSitesPerPass = 64;  // sites covered by a CTA in one pass
 constexpr int kPasses = 4;         // passes per tile
 constexpr int kTileSites = kSitesPerPass * kPasses;  // 256 sites per tile
 constexpr int kMaxCats = 8;
+// The two CLV-producing kernels keep P matrices in registers (32 doubles per
+// thread) and amortise them over kHeavyPasses sites, so they run smaller CTAs.
+constexpr int kHeavySites = 32;   // sites covered by a CTA in one pass
+constexpr int kHeavyPasses = 4;   // passes per tile
+constexpr int kHeavyTile = kHeavySites * kHeavyPasses; // 128 sites per tile
 
 // Device view of one engine (passed by value; lives in the constant bank).
 struct DevState
@@ -100,6 +105,14 @@ __device__ __forceinline__ void ld256(const double *p, double v[4])
 __device__ __forceinline__ void ld256_stream(const double *p, double v[4])
 {
   asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+               : "l"(p));
+}
+
+// read-only path (P-matrix rows: never written while a kernel that uses this runs)
+__device__ __forceinline__ void ld256_nc(const double *p, double v[4])
+{
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
                : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
                : "l"(p));
 }
@@ -251,59 +264,67 @@ __global__ void pmatrix_kernel(DevState s, ModelConst m, const unsigned int *idx
 // (site, category) entries it owns (LIBPLL/partials.c:177-213 runs the same
 // list one op at a time over all sites).  Entries of different sites never
 // interact, and an entry written by op i is re-read by op j > i only by the
-// thread that wrote it, so no inter-thread synchronisation is needed beyond
-// staging each op's two P matrices in shared memory.
+// thread that wrote it, so the kernel has no block-level barrier at all: warps
+// free-run through the list.  Because a CTA owns a fixed tile of sites, the
+// children an op reads were written by the same SM a few ops earlier and are
+// normally still in L2 -- only tips and first touches come from HBM.
+// P-matrix rows cost LSU bandwidth like any other load (32 bytes returned to
+// every lane), so each thread loads the two 4x4 matrices of its category once
+// per op into registers and reuses them for kHeavyPasses sites.
 template <int C>
-__global__ void __launch_bounds__(kSitesPerPass *C)
+__device__ __forceinline__ void load_matrix(const double *pm, double m[16])
+{
+#pragma unroll
+  for (int i = 0; i < 4; ++i) ld256_nc(pm + 4 * i, m + 4 * i);
+}
+
+template <int C>
+__global__ void __launch_bounds__(kHeavySites *C)
     partials_kernel(DevState s, const DevOp *__restrict__ ops, unsigned int nops)
 {
-  __shared__ double mats[2][2][C * 16];
   const int cat = threadIdx.x % C;
-  const unsigned int site0 = blockIdx.x * kTileSites + threadIdx.x / C;
+  const unsigned int site0 = blockIdx.x * kHeavyTile + threadIdx.x / C;
 
   for (unsigned int o = 0; o < nops; ++o)
   {
     const DevOp op = ops[o];
-    double *lm = mats[o & 1][0], *rm = mats[o & 1][1];
-    for (int i = threadIdx.x; i < C * 16; i += blockDim.x)
+    double lm[16], rm[16];
+    load_matrix<C>(s.pmat + ((size_t)op.c1_mat * C + cat) * 16, lm);
+    load_matrix<C>(s.pmat + ((size_t)op.c2_mat * C + cat) * 16, rm);
+    double *dst = s.clv + (size_t)(op.parent_clv - s.n_tips) * s.clv_stride;
+#pragma unroll 1
+    for (int half = 0; half < kHeavyPasses; half += 2)
     {
-      lm[i] = s.pmat[(size_t)op.c1_mat * C * 16 + i];
-      rm[i] = s.pmat[(size_t)op.c2_mat * C * 16 + i];
-    }
-    __syncthreads(); // double-buffered: one barrier per op is enough
-
-    double l[kPasses][4], r[kPasses][4];
-    unsigned int sc[kPasses];
+      double l[2][4], r[2][4], p[2][4];
+      unsigned int sc[2];
 #pragma unroll
-    for (int ps = 0; ps < kPasses; ++ps)
-    {
-      const unsigned int site = min(site0 + ps * kSitesPerPass, s.sites - 1);
-      load_entry<C>(s, op.c1_clv, site, cat, l[ps]);
-      load_entry<C>(s, op.c2_clv, site, cat, r[ps]);
-      sc[ps] = load_scaler(s, op.c1_scaler, site) + load_scaler(s, op.c2_scaler, site);
-    }
-#pragma unroll
-    for (int ps = 0; ps < kPasses; ++ps)
-    {
-      const unsigned int site = site0 + ps * kSitesPerPass;
-      double p[4];
-      combine_entry(lm + cat * 16, rm + cat * 16, l[ps], r[ps], p);
-      // per-site scaling (LIBPLL/core_partials_avx.c:491-527): ordered "<"
-      bool small = (p[0] < PT_SCALE_THRESHOLD) & (p[1] < PT_SCALE_THRESHOLD) &
-                   (p[2] < PT_SCALE_THRESHOLD) & (p[3] < PT_SCALE_THRESHOLD);
-      small = site_all<C>(small) && op.parent_scaler >= 0;
-      if (small)
+      for (int j = 0; j < 2; ++j)
       {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) p[i] = __dmul_rn(p[i], PT_SCALE_FACTOR);
+        const unsigned int site = min(site0 + (half + j) * kHeavySites, s.sites - 1);
+        load_entry<C>(s, op.c1_clv, site, cat, l[j]);
+        load_entry<C>(s, op.c2_clv, site, cat, r[j]);
+        sc[j] = load_scaler(s, op.c1_scaler, site) + load_scaler(s, op.c2_scaler, site);
       }
-      if (site < s.sites)
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
       {
-        st256(s.clv + (size_t)(op.parent_clv - s.n_tips) * s.clv_stride +
-                  ((size_t)site * C + cat) * 4,
-              p);
-        if (cat == 0 && op.parent_scaler >= 0)
-          s.scalers[(size_t)op.parent_scaler * s.sites + site] = sc[ps] + (small ? 1u : 0u);
+        combine_entry(lm, rm, l[j], r[j], p[j]);
+        const unsigned int site = site0 + (half + j) * kHeavySites;
+        // per-site scaling (LIBPLL/core_partials_avx.c:491-527): ordered "<"
+        bool small = (p[j][0] < PT_SCALE_THRESHOLD) & (p[j][1] < PT_SCALE_THRESHOLD) &
+                     (p[j][2] < PT_SCALE_THRESHOLD) & (p[j][3] < PT_SCALE_THRESHOLD);
+        small = site_all<C>(small) && op.parent_scaler >= 0;
+        if (small)
+        {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) p[j][i] = __dmul_rn(p[j][i], PT_SCALE_FACTOR);
+        }
+        if (site < s.sites)
+        {
+          st256(dst + ((size_t)site * C + cat) * 4, p[j]);
+          if (cat == 0 && op.parent_scaler >= 0)
+            s.scalers[(size_t)op.parent_scaler * s.sites + site] = sc[j] + (small ? 1u : 0u);
+        }
       }
     }
     __syncwarp(); // scaler word written by lane cat 0, re-read by its C-lane group
@@ -437,97 +458,140 @@ __global__ void __launch_bounds__(kSitesPerPass *C)
 // ------------------------------------------------------------ kernel 4
 // Derivatives of -lnL from the sumtable and the Newton-Raphson control loop.
 
-// diag[(c*4+j)*3 + {0,1,2}] = {e, (lambda r) e, (lambda r)^2 e}, e = exp(lambda_j r_c t)
-// (LIBPLL/core_derivatives.c:560-575; prop_invar = 0 so ki = r_c / 1.0)
+// dg[j][{0,1,2}] = {e, (lambda r) e, (lambda r)^2 e}, e = exp(lambda_j r_c t), for this
+// thread's category (LIBPLL/core_derivatives.c:560-575; prop_invar = 0 so
+// ki = r_c / 1.0).  Kept in registers: a thread's category never changes.
 template <int C>
-__device__ __forceinline__ void fill_diag(const ModelConst &m, double len, double *diag)
+__device__ __forceinline__ void diag_regs(const ModelConst &m, double len, int cat,
+                                          double dg[4][3])
 {
-  if (threadIdx.x < C * 4)
+  const double ki = m.rates[cat] / (1.0 - 0.0);
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
   {
-    const int c = threadIdx.x / 4, j = threadIdx.x % 4;
-    const double ki = m.rates[c] / (1.0 - 0.0);
     const double lr = __dmul_rn(m.evals[j], ki);
     const double e = exp(__dmul_rn(lr, len));
-    diag[threadIdx.x * 3 + 0] = e;
-    diag[threadIdx.x * 3 + 1] = __dmul_rn(lr, e);
-    diag[threadIdx.x * 3 + 2] = __dmul_rn(__dmul_rn(__dmul_rn(lr, m.evals[j]), ki), e);
+    dg[j][0] = e;
+    dg[j][1] = __dmul_rn(lr, e);
+    dg[j][2] = __dmul_rn(__dmul_rn(__dmul_rn(lr, m.evals[j]), ki), e);
+  }
+}
+
+// Sum over the 4 category lanes of a site for 4 passes at once ("transpose and
+// add"): on entry lane k (= category k) holds v[ps][q] for passes ps = 0..3; on
+// exit it holds r[q] = sum over categories for pass quad_pass(k).  9 double
+// shuffles replace the 36 a per-pass gather would need, and afterwards all
+// four lanes (not one) carry a site through the division / log.  The category
+// sum is formed as (c0 + c1) + (c2 + c3).
+__device__ __forceinline__ int quad_pass(int k) { return ((k & 1) << 1) | (k >> 1); }
+
+template <int NQ>
+__device__ __forceinline__ void quad_transpose_sum(const double (&v)[4][NQ], int k,
+                                                   double (&r)[NQ])
+{
+  const bool odd = k & 1, hi = k & 2;
+#pragma unroll
+  for (int q = 0; q < NQ; ++q)
+  {
+    const double s0 = odd ? v[0][q] : v[2][q], s1 = odd ? v[1][q] : v[3][q];
+    const double k0 = odd ? v[2][q] : v[0][q], k1 = odd ? v[3][q] : v[1][q];
+    const double a0 = __dadd_rn(k0, __shfl_xor_sync(0xffffffffu, s0, 1));
+    const double a1 = __dadd_rn(k1, __shfl_xor_sync(0xffffffffu, s1, 1));
+    const double snd = hi ? a0 : a1, kp = hi ? a1 : a0;
+    r[q] = __dadd_rn(kp, __shfl_xor_sync(0xffffffffu, snd, 2));
+  }
+}
+
+// per-site epilogue shared by both reduction layouts
+template <bool WITH_LNL>
+__device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[3], double terma,
+                                           unsigned int site, unsigned int full,
+                                           const unsigned int *sclr, double out[3])
+{
+  // LIBPLL/core_derivatives_avx.c:1111-1156: sites below `full` (= sites/4*4) use
+  // the reciprocal form of the 4-site vector step, the tail true divisions
+  if (site < full)
+  {
+    const double recip = __ddiv_rn(1.0, lk[0]);
+    const double a = __dmul_rn(lk[1], recip);
+    const double b = __dadd_rn(__dmul_rn(a, a), -__dmul_rn(lk[2], recip));
+    out[0] = __dadd_rn(out[0], -a);
+    out[1] = __dadd_rn(out[1], b);
+  }
+  else
+  {
+    const double a = -__ddiv_rn(lk[1], lk[0]);
+    const double b = __dadd_rn(__dmul_rn(a, a), -__ddiv_rn(lk[2], lk[0]));
+    out[0] = __dadd_rn(out[0], a);
+    out[1] = __dadd_rn(out[1], b);
+  }
+  if (WITH_LNL)
+  {
+    double l = log(terma);
+    const unsigned int sc = sclr ? sclr[site] : 0u;
+    if (sc) l = __dadd_rn(l, __dmul_rn((double)sc, m.log_scale_thr));
+    out[2] = __dadd_rn(out[2], l);
   }
 }
 
 // One tile of the site sweep.  out[0] += -L'/L terms, out[1] += second
 // derivative terms, out[2] += log-likelihood terms (only if WITH_LNL).
-// Per-site arithmetic follows LIBPLL/core_derivatives_avx.c:1003-1156: sites
-// below `full` (= sites/4*4) use the reciprocal form of the 4-site vector
-// step, the remaining sites the scalar tail with true divisions.
 template <int C, bool WITH_LNL>
 __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *sumtable,
                                            const unsigned int *sclr, unsigned int sites,
-                                           unsigned int tile, const double *diag,
+                                           unsigned int tile, const double (&dg)[4][3],
                                            double out[3])
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
   const unsigned int full = sites / 4 * 4;
-  double sv[kPasses][4];
-#pragma unroll
-  for (int ps = 0; ps < kPasses; ++ps)
+  constexpr int NQ = WITH_LNL ? 4 : 3;
+  double ck[kPasses][NQ];
   {
-    const unsigned int site = min(site0 + ps * kSitesPerPass, sites - 1);
-    ld256_stream(sumtable + ((size_t)site * C + cat) * 4, sv[ps]);
-  }
-  const double *dg = diag + cat * 12;
+    double sv[kPasses][4];
 #pragma unroll
-  for (int ps = 0; ps < kPasses; ++ps)
-  {
-    const unsigned int site = site0 + ps * kSitesPerPass;
-    double ck[3];
-#pragma unroll
-    for (int q = 0; q < 3; ++q)
+    for (int ps = 0; ps < kPasses; ++ps)
     {
-      double a = __dadd_rn(0.0, __dmul_rn(sv[ps][0], dg[0 * 3 + q]));
-      a = __dadd_rn(a, __dmul_rn(sv[ps][1], dg[1 * 3 + q]));
-      a = __dadd_rn(a, __dmul_rn(sv[ps][2], dg[2 * 3 + q]));
-      ck[q] = __dadd_rn(a, __dmul_rn(sv[ps][3], dg[3 * 3 + q]));
-    }
-    double lk[3] = {ck[0], ck[1], ck[2]};
-    double term = 0.0, terma = 0.0;
-    if (WITH_LNL)
-    {
-      term = (ck[0] > 0.0) ? __dmul_rn(ck[0], m.rate_weight) : 0.0;
-      terma = term;
+      const unsigned int site = min(site0 + ps * kSitesPerPass, sites - 1);
+      ld256_stream(sumtable + ((size_t)site * C + cat) * 4, sv[ps]);
     }
 #pragma unroll
-    for (int k = 1; k < C; ++k)
+    for (int ps = 0; ps < kPasses; ++ps)
     {
 #pragma unroll
       for (int q = 0; q < 3; ++q)
-        lk[q] = __dadd_rn(lk[q], __shfl_down_sync(0xffffffffu, ck[q], k, C));
-      if (WITH_LNL) terma = __dadd_rn(terma, __shfl_down_sync(0xffffffffu, term, k, C));
+      {
+        // ((0 + s0 d0) + s1 d1) + s2 d2) + s3 d3  (LIBPLL/core_derivatives_avx.c:1019-1034)
+        double a = __dadd_rn(0.0, __dmul_rn(sv[ps][0], dg[0][q]));
+        a = __dadd_rn(a, __dmul_rn(sv[ps][1], dg[1][q]));
+        a = __dadd_rn(a, __dmul_rn(sv[ps][2], dg[2][q]));
+        ck[ps][q] = __dadd_rn(a, __dmul_rn(sv[ps][3], dg[3][q]));
+      }
+      if (WITH_LNL) ck[ps][NQ - 1] = (ck[ps][0] > 0.0) ? __dmul_rn(ck[ps][0], m.rate_weight) : 0.0;
     }
-    if (cat == 0 && site < sites)
+  }
+  if (C == 4)
+  {
+    double r[NQ];
+    quad_transpose_sum<NQ>(ck, cat, r);
+    const unsigned int site = site0 + quad_pass(cat) * kSitesPerPass;
+    if (site < sites) site_terms<WITH_LNL>(m, r, r[NQ - 1], site, full, sclr, out);
+  }
+  else
+  {
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps)
     {
-      if (site < full)
-      {
-        const double recip = __ddiv_rn(1.0, lk[0]);
-        const double a = __dmul_rn(lk[1], recip);
-        const double b = __dadd_rn(__dmul_rn(a, a), -__dmul_rn(lk[2], recip));
-        out[0] = __dadd_rn(out[0], -a);
-        out[1] = __dadd_rn(out[1], b);
-      }
-      else
-      {
-        const double a = -__ddiv_rn(lk[1], lk[0]);
-        const double b = __dadd_rn(__dmul_rn(a, a), -__ddiv_rn(lk[2], lk[0]));
-        out[0] = __dadd_rn(out[0], a);
-        out[1] = __dadd_rn(out[1], b);
-      }
-      if (WITH_LNL)
-      {
-        double l = log(terma);
-        const unsigned int sc = sclr ? sclr[site] : 0u;
-        if (sc) l = __dadd_rn(l, __dmul_rn((double)sc, m.log_scale_thr));
-        out[2] = __dadd_rn(out[2], l);
-      }
+      const unsigned int site = site0 + ps * kSitesPerPass;
+      double lk[NQ];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) lk[q] = ck[ps][q];
+#pragma unroll
+      for (int k = 1; k < C; ++k)
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+          lk[q] = __dadd_rn(lk[q], __shfl_down_sync(0xffffffffu, ck[ps][q], k, C));
+      if (cat == 0 && site < sites) site_terms<WITH_LNL>(m, lk, lk[NQ - 1], site, full, sclr, out);
     }
   }
 }
@@ -539,8 +603,8 @@ struct NewtonArgs
   size_t entry_stride;      // doubles between consecutive entries' sumtables
   const unsigned int *sclr; // [B][sites] summed scaler counts, or null (=> 0)
   NewtonState *st;          // [B]
-  double *partials;         // [B][ntiles][2]
-  unsigned int sites, B, ntiles, max_iter;
+  double *partials;         // [B][nchunks][2]
+  unsigned int sites, B, ntiles, chunk_tiles, nchunks, max_iter;
   double eps, lambda;
   int want_lnl;
 };
@@ -548,29 +612,32 @@ struct NewtonArgs
 // Persistent cooperative kernel: the whole Newton-Raphson loop of
 // Partition::OptimizeBranch (PTPLL/pll_partition.cpp:419-481) for B branches
 // at once.  Each iteration = one sweep of every still-running branch's
-// sumtable (tiles spread over all CTAs), a grid barrier, a fixed-order
-// reduction + the scalar update done by one CTA per branch, a grid barrier.
+// sumtable (chunks of tiles spread over all CTAs), a grid barrier, a
+// fixed-order reduction + the scalar update done by one CTA per branch, a grid
+// barrier.  Reduction units (chunks) depend only on the site count, so results
+// are independent of the grid size.
 template <int C>
-__global__ void __launch_bounds__(kSitesPerPass *C) newton_kernel(NewtonArgs a)
+__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
   cg::grid_group grid = cg::this_grid();
-  __shared__ double diag[C * 12];
   __shared__ double red[T / 32 < 1 ? 1 : T / 32];
-  const unsigned int nwork = a.B * a.ntiles;
+  const unsigned int nwork = a.B * a.nchunks;
+  const int cat = threadIdx.x % C;
 
   for (unsigned int it = 0; it < a.max_iter; ++it)
   {
     for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
     {
-      const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+      const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
       if (__ldcg(&a.st[e].done)) continue;
-      __syncthreads();
-      fill_diag<C>(a.m, __ldcg(&a.st[e].len), diag);
-      __syncthreads();
+      double dg[4][3];
+      diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
       double out[3] = {0.0, 0.0, 0.0};
-      sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
-                           tile, diag, out);
+      const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
+      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+        sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+                             tile, dg, out);
       const double s1 = block_sum<T>(out[0], red);
       const double s2 = block_sum<T>(out[1], red);
       if (threadIdx.x == 0)
@@ -584,10 +651,10 @@ __global__ void __launch_bounds__(kSitesPerPass *C) newton_kernel(NewtonArgs a)
     {
       if (__ldcg(&a.st[e].done)) continue;
       double a1 = 0.0, a2 = 0.0;
-      for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
+      for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
       {
-        a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.ntiles + t) * 2 + 0));
-        a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.ntiles + t) * 2 + 1));
+        a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 2 + 0));
+        a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 2 + 1));
       }
       a1 = block_sum<T>(a1, red);
       a2 = block_sum<T>(a2, red);
@@ -633,93 +700,109 @@ __global__ void __launch_bounds__(kSitesPerPass *C) newton_kernel(NewtonArgs a)
   // log-likelihood at the final length, from the same sumtable
   for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
   {
-    const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
-    __syncthreads();
-    fill_diag<C>(a.m, __ldcg(&a.st[e].len), diag);
-    __syncthreads();
+    const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
+    double dg[4][3];
+    diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
     double out[3] = {0.0, 0.0, 0.0};
-    sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                        a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, diag,
-                        out);
-    const double s = block_sum<T>(out[2], red);
-    if (threadIdx.x == 0) a.partials[(size_t)w * 2] = s;
+    const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
+    for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+      sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                          a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out);
+    const double sm = block_sum<T>(out[2], red);
+    if (threadIdx.x == 0) a.partials[(size_t)w * 2] = sm;
   }
   grid.sync();
   for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
   {
     double acc = 0.0;
-    for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
-      acc = __dadd_rn(acc, __ldcg(a.partials + ((size_t)e * a.ntiles + t) * 2));
+    for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+      acc = __dadd_rn(acc, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 2));
     acc = block_sum<T>(acc, red);
     if (threadIdx.x == 0) a.st[e].lnl = acc;
   }
 }
 
 // ------------------------------------------------- NNI candidate preparation
-// For candidate b (blockIdx.y) and one tile of sites: the two CLV updates that
-// face each other across the swapped edge (kept in registers, never written),
-// their per-site scaler counts, and the sumtable entries of the central edge.
+// For one candidate and one tile of sites: the two CLV updates that face each
+// other across the swapped edge (kept in registers, never written), their
+// per-site scaler counts, and the sumtable entries of the central edge.
 // Reads 4 neighbour CLVs (or tip masks) + their scaler words; writes the
 // candidate's sumtable (32 B per entry) and one summed scaler word per site.
+// The candidate index is the fastest-varying part of blockIdx.x, so the CTAs
+// that run together work on the SAME tile of sites for different candidates:
+// each directional CLV tile is fetched from HBM once and then served from L2
+// to the ~2.6 candidates that use it.
 template <int C>
-__global__ void __launch_bounds__(kSitesPerPass *C)
+__global__ void __launch_bounds__(kHeavySites *C)
     nni_prepare_kernel(DevState s, ModelConst m, const DevCand *__restrict__ cands,
-                       double *sumtables, size_t entry_stride, unsigned int *sclr)
+                       unsigned int ncands, double *sumtables, size_t entry_stride,
+                       unsigned int *sclr)
 {
-  constexpr int T = kSitesPerPass * C;
-  __shared__ double mats[4][C * 16];
-  const unsigned int b = blockIdx.y;
+  const unsigned int b = blockIdx.x % ncands, tile = blockIdx.x / ncands;
   const DevCand cd = cands[b];
   const int cat = threadIdx.x % C;
-  const unsigned int site0 = blockIdx.x * kTileSites + threadIdx.x / C;
-  for (int i = threadIdx.x; i < C * 16; i += T)
-  {
-    mats[0][i] = s.pmat[(size_t)cd.p.c1_mat * C * 16 + i];
-    mats[1][i] = s.pmat[(size_t)cd.p.c2_mat * C * 16 + i];
-    mats[2][i] = s.pmat[(size_t)cd.q.c1_mat * C * 16 + i];
-    mats[3][i] = s.pmat[(size_t)cd.q.c2_mat * C * 16 + i];
-  }
-  __syncthreads();
+  const unsigned int site0 = tile * kHeavyTile + threadIdx.x / C;
   double *out = sumtables + (size_t)b * entry_stride;
 
-#pragma unroll 2
-  for (int ps = 0; ps < kPasses; ++ps)
+  // phase A: the CLV on the p side for all passes of the tile (kept in registers)
+  double pp[kHeavyPasses][4];
+  unsigned int cnt[kHeavyPasses];
   {
-    const unsigned int site_raw = site0 + ps * kSitesPerPass;
-    const unsigned int site = min(site_raw, s.sites - 1);
-    double x1[4], x2[4], y1[4], y2[4];
-    load_entry<C>(s, cd.p.c1_clv, site, cat, x1);
-    load_entry<C>(s, cd.p.c2_clv, site, cat, x2);
-    load_entry<C>(s, cd.q.c1_clv, site, cat, y1);
-    load_entry<C>(s, cd.q.c2_clv, site, cat, y2);
-    unsigned int cnt = load_scaler(s, cd.p.c1_scaler, site) + load_scaler(s, cd.p.c2_scaler, site) +
-                       load_scaler(s, cd.q.c1_scaler, site) + load_scaler(s, cd.q.c2_scaler, site);
-    double pp[4], qq[4];
-    combine_entry(mats[0] + cat * 16, mats[1] + cat * 16, x1, x2, pp);
-    combine_entry(mats[2] + cat * 16, mats[3] + cat * 16, y1, y2, qq);
-    bool sp = (pp[0] < PT_SCALE_THRESHOLD) & (pp[1] < PT_SCALE_THRESHOLD) &
-              (pp[2] < PT_SCALE_THRESHOLD) & (pp[3] < PT_SCALE_THRESHOLD);
-    bool sq = (qq[0] < PT_SCALE_THRESHOLD) & (qq[1] < PT_SCALE_THRESHOLD) &
-              (qq[2] < PT_SCALE_THRESHOLD) & (qq[3] < PT_SCALE_THRESHOLD);
-    sp = site_all<C>(sp);
-    sq = site_all<C>(sq);
-    if (sp)
-    {
+    double lm[16], rm[16];
+    load_matrix<C>(s.pmat + ((size_t)cd.p.c1_mat * C + cat) * 16, lm);
+    load_matrix<C>(s.pmat + ((size_t)cd.p.c2_mat * C + cat) * 16, rm);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) pp[i] = __dmul_rn(pp[i], PT_SCALE_FACTOR);
-    }
-    if (sq)
+    for (int ps = 0; ps < kHeavyPasses; ++ps)
     {
+      const unsigned int site = min(site0 + ps * kHeavySites, s.sites - 1);
+      double x1[4], x2[4];
+      load_entry<C>(s, cd.p.c1_clv, site, cat, x1);
+      load_entry<C>(s, cd.p.c2_clv, site, cat, x2);
+      cnt[ps] = load_scaler(s, cd.p.c1_scaler, site) + load_scaler(s, cd.p.c2_scaler, site);
+      combine_entry(lm, rm, x1, x2, pp[ps]);
+      bool sp = (pp[ps][0] < PT_SCALE_THRESHOLD) & (pp[ps][1] < PT_SCALE_THRESHOLD) &
+                (pp[ps][2] < PT_SCALE_THRESHOLD) & (pp[ps][3] < PT_SCALE_THRESHOLD);
+      sp = site_all<C>(sp);
+      if (sp)
+      {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) qq[i] = __dmul_rn(qq[i], PT_SCALE_FACTOR);
+        for (int i = 0; i < 4; ++i) pp[ps][i] = __dmul_rn(pp[ps][i], PT_SCALE_FACTOR);
+        cnt[ps] += 1u;
+      }
     }
-    cnt += (sp ? 1u : 0u) + (sq ? 1u : 0u);
-    double sum[4];
-    sumtable_entry<C>(m, pp, qq, sum);
-    if (site_raw < s.sites)
+  }
+  // phase B: the q side, the sumtable entry, the stores
+  {
+    double lm[16], rm[16];
+    load_matrix<C>(s.pmat + ((size_t)cd.q.c1_mat * C + cat) * 16, lm);
+    load_matrix<C>(s.pmat + ((size_t)cd.q.c2_mat * C + cat) * 16, rm);
+#pragma unroll
+    for (int ps = 0; ps < kHeavyPasses; ++ps)
     {
-      st256(out + ((size_t)site * C + cat) * 4, sum);
-      if (cat == 0) sclr[(size_t)b * s.sites + site] = cnt;
+      const unsigned int site_raw = site0 + ps * kHeavySites;
+      const unsigned int site = min(site_raw, s.sites - 1);
+      double y1[4], y2[4], qq[4];
+      load_entry<C>(s, cd.q.c1_clv, site, cat, y1);
+      load_entry<C>(s, cd.q.c2_clv, site, cat, y2);
+      unsigned int c2 = cnt[ps] + load_scaler(s, cd.q.c1_scaler, site) +
+                        load_scaler(s, cd.q.c2_scaler, site);
+      combine_entry(lm, rm, y1, y2, qq);
+      bool sq = (qq[0] < PT_SCALE_THRESHOLD) & (qq[1] < PT_SCALE_THRESHOLD) &
+                (qq[2] < PT_SCALE_THRESHOLD) & (qq[3] < PT_SCALE_THRESHOLD);
+      sq = site_all<C>(sq);
+      if (sq)
+      {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) qq[i] = __dmul_rn(qq[i], PT_SCALE_FACTOR);
+        c2 += 1u;
+      }
+      double sum[4];
+      sumtable_entry<C>(m, pp[ps], qq, sum);
+      if (site_raw < s.sites)
+      {
+        st256(out + ((size_t)site * C + cat) * 4, sum);
+        if (cat == 0) sclr[(size_t)b * s.sites + site] = c2;
+      }
     }
   }
 }
