@@ -82,7 +82,7 @@ struct ptgpu_engine
   unsigned int *d_bsclr = nullptr;
   NewtonState *d_bstate = nullptr;
   double *d_bpartials = nullptr;
-  DevCand *d_bcands = nullptr;
+  DevGroup *d_bcands = nullptr;     // candidate groups of the current chunk
   size_t bcap = 0;
   // op / matrix upload buffers
   DevOp *d_ops = nullptr;
@@ -230,11 +230,13 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
 #define CU_NEW(call)                                                                    \
   do { cudaError_t err__ = (call); if (err__ != cudaSuccess) { int rc__ = fail(PTGPU_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(err__)); ptgpu_destroy(e); return rc__; } } while (0)
   CU_NEW(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
-  CU_NEW(cudaMalloc(&e->d_tips, (size_t)tips * sites));
-  CU_NEW(cudaMemsetAsync(e->d_tips, 0, (size_t)tips * sites, e->stream));
+  const size_t tip_stride = ((size_t)sites + 15) & ~(size_t)15;      // rows start 16-byte aligned (TMA bulk)
+  const size_t scaler_stride = ((size_t)sites + 3) & ~(size_t)3;
+  CU_NEW(cudaMalloc(&e->d_tips, (size_t)tips * tip_stride));
+  CU_NEW(cudaMemsetAsync(e->d_tips, 0, (size_t)tips * tip_stride, e->stream));
   CU_NEW(cudaMalloc(&e->dev.clv, clv_stride * clv_buffers * sizeof(double)));
-  CU_NEW(cudaMalloc(&e->dev.scalers, (size_t)std::max(1u, scale_buffers) * sites * sizeof(unsigned int)));
-  CU_NEW(cudaMemsetAsync(e->dev.scalers, 0, (size_t)std::max(1u, scale_buffers) * sites * sizeof(unsigned int), e->stream));
+  CU_NEW(cudaMalloc(&e->dev.scalers, (size_t)std::max(1u, scale_buffers) * scaler_stride * sizeof(unsigned int)));
+  CU_NEW(cudaMemsetAsync(e->dev.scalers, 0, (size_t)std::max(1u, scale_buffers) * scaler_stride * sizeof(unsigned int), e->stream));
   CU_NEW(cudaMalloc(&e->dev.pmat, (size_t)prob_matrices * rate_cats * 16 * sizeof(double)));
   CU_NEW(cudaMemsetAsync(e->dev.pmat, 0, (size_t)prob_matrices * rate_cats * 16 * sizeof(double), e->stream));
   CU_NEW(cudaMalloc(&e->d_sumtable, clv_stride * sizeof(double)));
@@ -249,6 +251,8 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   e->dev.n_tips = tips;
   e->dev.sites = sites;
   e->dev.clv_stride = clv_stride;
+  e->dev.tip_stride = tip_stride;
+  e->dev.scaler_stride = scaler_stride;
   CU_NEW(cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, device));
   {
     int rc = PTGPU_OK, occ = 0;
@@ -262,6 +266,15 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
     if (rc) { ptgpu_destroy(e); return rc; }
     if (occ < 1) { ptgpu_destroy(e); return fail(PTGPU_ERR_CUDA, "newton kernel does not fit an SM"); }
     e->coop_blocks_per_sm = occ;
+    cudaError_t ea = cudaSuccess;
+    switch (rate_cats)
+    {
+      case 1: ea = cudaFuncSetAttribute(nni_prepare_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<1>)); break;
+      case 2: ea = cudaFuncSetAttribute(nni_prepare_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<2>)); break;
+      case 4: ea = cudaFuncSetAttribute(nni_prepare_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<4>)); break;
+      default: ea = cudaFuncSetAttribute(nni_prepare_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<8>)); break;
+    }
+    if (ea != cudaSuccess) { ptgpu_destroy(e); return fail(PTGPU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(ea)); }
   }
   CU_NEW(cudaStreamSynchronize(e->stream));
 #undef CU_NEW
@@ -334,7 +347,7 @@ int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *se
     LaunchScope ls(e, PTGPU_KERNEL_TIP_ENCODE);
     const unsigned int blocks = std::min<unsigned int>((e->sites + 255) / 256, 4u * (unsigned int)e->sm_count);
     tip_encode_kernel<<<blocks, 256, 0, e->stream>>>((const unsigned char *)e->d_raw,
-                                                     e->d_tips + (size_t)tip_index * e->sites,
+                                                     e->d_tips + (size_t)tip_index * e->dev.tip_stride,
                                                      e->sites, lut, bad_d);
   }
   CU(cudaGetLastError());
@@ -614,7 +627,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
   size_t free_b = 0, total_b = 0;
   CU(cudaMemGetInfo(&free_b, &total_b));
   const size_t per_cand = stride * sizeof(double) + (size_t)e->sites * sizeof(unsigned int) +
-                          (size_t)e->ntiles * 2 * sizeof(double) + sizeof(NewtonState) + sizeof(DevCand);
+                          (size_t)e->ntiles * 2 * sizeof(double) + sizeof(NewtonState) + sizeof(DevGroup);
   size_t have = e->bcap * per_cand;
   size_t budget = std::max(have, (size_t)((free_b + have) * 0.8));
   size_t chunk = std::min<size_t>(count, std::max<size_t>(1, budget / per_cand));
@@ -627,7 +640,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     CU(cudaMalloc(&e->d_bsclr, chunk * (size_t)e->sites * sizeof(unsigned int)));
     CU(cudaMalloc(&e->d_bstate, chunk * sizeof(NewtonState)));
     CU(cudaMalloc(&e->d_bpartials, chunk * (size_t)e->ntiles * 2 * sizeof(double)));
-    CU(cudaMalloc(&e->d_bcands, chunk * sizeof(DevCand)));
+    CU(cudaMalloc(&e->d_bcands, chunk * sizeof(DevGroup)));
     e->bcap = chunk;
   }
   std::vector<NewtonState> hst(chunk);
@@ -639,12 +652,61 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
       hst[i] = NewtonState{};
       hst[i].len = cands[base + i].length0;
     }
-    if ((rc = upload(e, e->d_bcands, cands + base, nb * sizeof(DevCand)))) return rc;
+    // candidates that read the same four neighbours (the LEFT and RIGHT move
+    // across one edge) share one group: their matrix-vector products are done once
+    std::vector<DevGroup> groups;
+    groups.reserve(nb);
+    auto child = [](const ptgpu_operation_t &op, int which) {
+      DevChild c;
+      c.clv = which ? op.child2_clv_index : op.child1_clv_index;
+      c.scaler = which ? op.child2_scaler_index : op.child1_scaler_index;
+      c.mat = which ? op.child2_matrix_index : op.child1_matrix_index;
+      c.pad = 0;
+      return c;
+    };
+    auto same = [](const DevChild &a, const DevChild &b) {
+      return a.clv == b.clv && a.scaler == b.scaler && a.mat == b.mat;
+    };
+    for (unsigned int i = 0; i < nb; ++i)
+    {
+      const ptgpu_nni_candidate_t &c0 = cands[base + i];
+      DevGroup g{};
+      g.ch[0] = child(c0.p, 0); g.ch[1] = child(c0.p, 1);
+      g.ch[2] = child(c0.q, 0); g.ch[3] = child(c0.q, 1);
+      g.ncand = 1;
+      g.out[0] = i;
+      if (i + 1 < nb)
+      {
+        // second candidate must combine (ch3, ch1) on one side and (ch2, ch0) on the other;
+        // child order within a side and which side is "p" for the swap partner are free
+        // up to relabelling ch0<->ch1 / ch2<->ch3 of the first candidate
+        const ptgpu_nni_candidate_t &c1 = cands[base + i + 1];
+        const DevChild a0 = child(c1.p, 0), a1 = child(c1.p, 1), b0 = child(c1.q, 0), b1 = child(c1.q, 1);
+        for (int flip = 0; flip < 4 && g.ncand == 1; ++flip)
+        {
+          DevGroup t = g;
+          if (flip & 1) std::swap(t.ch[0], t.ch[1]);
+          if (flip & 2) std::swap(t.ch[2], t.ch[3]);
+          const bool pside = (same(a0, t.ch[3]) && same(a1, t.ch[1])) || (same(a0, t.ch[1]) && same(a1, t.ch[3]));
+          const bool qside = (same(b0, t.ch[2]) && same(b1, t.ch[0])) || (same(b0, t.ch[0]) && same(b1, t.ch[2]));
+          if (pside && qside)
+          {
+            g = t;
+            g.ncand = 2;
+            g.out[1] = i + 1;
+          }
+        }
+      }
+      groups.push_back(g);
+      if (g.ncand == 2) ++i;
+    }
+    const unsigned int ng = (unsigned int)groups.size();
+    if ((rc = upload(e, e->d_bcands, groups.data(), ng * sizeof(DevGroup)))) return rc;
     if ((rc = upload(e, e->d_bstate, hst.data(), nb * sizeof(NewtonState)))) return rc;
     {
       LaunchScope ls(e, PTGPU_KERNEL_NNI_PREPARE);
-      DISPATCH_CATS(e, (nni_prepare_kernel<C><<<e->nheavy * nb, kHeavySites * C, 0, e->stream>>>(
-                           e->dev, e->model, e->d_bcands, nb, e->d_bsum, stride, e->d_bsclr)));
+      DISPATCH_CATS(e, (nni_prepare_kernel<C><<<e->nheavy * ng, kHeavySites * C, sizeof(PrepSmem<C>), e->stream>>>(
+                           e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr)));
     }
     CU(cudaGetLastError());
     NewtonArgs a{};
@@ -680,7 +742,7 @@ int ptgpu_get_clv(ptgpu_engine *e, unsigned int clv_index, double *out)
   if (clv_index < e->tips)
   {
     std::vector<uint8_t> m(e->sites);
-    CU(cudaMemcpyAsync(m.data(), e->d_tips + (size_t)clv_index * e->sites, e->sites, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(m.data(), e->d_tips + (size_t)clv_index * e->dev.tip_stride, e->sites, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     for (unsigned int s = 0; s < e->sites; ++s)
       for (unsigned int c = 0; c < e->cats; ++c)
@@ -712,7 +774,7 @@ int ptgpu_get_scaler(ptgpu_engine *e, int scaler_index, unsigned int *out)
   if (scaler_index < 0 || (unsigned int)scaler_index >= e->scale_buffers)
     return fail(PTGPU_ERR_ARG, "get_scaler: index %d out of range", scaler_index);
   CU(cudaSetDevice(e->device));
-  CU(cudaMemcpyAsync(out, e->dev.scalers + (size_t)scaler_index * e->sites,
+  CU(cudaMemcpyAsync(out, e->dev.scalers + (size_t)scaler_index * e->dev.scaler_stride,
                      (size_t)e->sites * sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   return PTGPU_OK;

@@ -42,6 +42,8 @@ struct DevState
   unsigned int n_tips;
   unsigned int sites;
   size_t clv_stride;     // doubles per CLV buffer
+  size_t tip_stride;     // bytes per tip row (sites rounded up to 16: TMA bulk alignment)
+  size_t scaler_stride;  // words per scaler row (sites rounded up to 4)
 };
 
 // Model constants (kernel parameter => constant bank, broadcast reads).
@@ -74,6 +76,24 @@ struct DevCand // == ptgpu_nni_candidate_t
   DevOp p;
   DevOp q;
   double length0;
+};
+
+// A group of NNI candidates that read the same four neighbour CLVs: candidate 0
+// combines children (0,1) on the p side and (2,3) on the q side; an optional
+// candidate 1 (the other NNI across the same edge) combines (3,1) and (2,0).
+struct DevChild
+{
+  unsigned int clv;
+  int scaler;
+  unsigned int mat;
+  unsigned int pad;
+};
+struct DevGroup
+{
+  DevChild ch[4];
+  unsigned int ncand;   // 1 or 2
+  unsigned int out[2];  // candidate slots (sumtable / scaler / state index)
+  unsigned int pad;
 };
 
 // Newton state of one branch (PTPLL/pll_partition.cpp:419-481)
@@ -124,6 +144,55 @@ __device__ __forceinline__ void st256(double *p, const double v[4])
                : "memory");
 }
 
+// ---- TMA bulk copies (cp.async.bulk, SASS UBLKCP) completing on an mbarrier ----
+__device__ __forceinline__ unsigned int smem_addr(const void *p)
+{
+  return (unsigned int)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned int bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes,
+                                         unsigned long long *bar)
+{
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_addr(dst)),
+      "l"(src), "r"(bytes), "r"(smem_addr(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned int parity)
+{
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_addr(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void lds256(const double *p, double v[4])
+{
+  const double2 a = *reinterpret_cast<const double2 *>(p);
+  const double2 b = *reinterpret_cast<const double2 *>(p + 2);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+
 // (a0 b0 + a1 b1) + (a2 b2 + a3 b3), every product and sum rounded separately
 __device__ __forceinline__ double dot4(const double *a, const double b[4])
 {
@@ -139,7 +208,7 @@ __device__ __forceinline__ void load_entry(const DevState &s, unsigned int clv_i
 {
   if (clv_index < s.n_tips)
   {
-    const unsigned int m = s.tips[(size_t)clv_index * s.sites + site];
+    const unsigned int m = s.tips[(size_t)clv_index * s.tip_stride + site];
 #pragma unroll
     for (int j = 0; j < 4; ++j) v[j] = ((m >> j) & 1u) ? 1.0 : 0.0;
   }
@@ -154,7 +223,7 @@ __device__ __forceinline__ void load_entry(const DevState &s, unsigned int clv_i
 __device__ __forceinline__ unsigned int load_scaler(const DevState &s, int scaler_index,
                                                     unsigned int site)
 {
-  return scaler_index < 0 ? 0u : s.scalers[(size_t)scaler_index * s.sites + site];
+  return scaler_index < 0 ? 0u : s.scalers[(size_t)scaler_index * s.scaler_stride + site];
 }
 
 // AND of a predicate over the C lanes that hold one site
@@ -323,7 +392,7 @@ __global__ void __launch_bounds__(kHeavySites *C)
         {
           st256(dst + ((size_t)site * C + cat) * 4, p[j]);
           if (cat == 0 && op.parent_scaler >= 0)
-            s.scalers[(size_t)op.parent_scaler * s.sites + site] = sc[j] + (small ? 1u : 0u);
+            s.scalers[(size_t)op.parent_scaler * s.scaler_stride + site] = sc[j] + (small ? 1u : 0u);
         }
       }
     }
@@ -732,78 +801,167 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
 // that run together work on the SAME tile of sites for different candidates:
 // each directional CLV tile is fetched from HBM once and then served from L2
 // to the ~2.6 candidates that use it.
+// Shared-memory staging of one candidate's four neighbour tiles.  Each child is
+// a contiguous run in HBM (CLV tile kHeavyTile*C*32 B, scaler tile, or tip-mask
+// tile), fetched by ONE thread with TMA bulk copies that complete on the
+// child's mbarrier; all 4 x (16 KB + 0.5 KB) are in flight at once per CTA, so
+// memory-level parallelism no longer depends on registers or warp count.
+template <int C>
+struct PrepSmem
+{
+  double clv[4][kHeavyTile * C * 4];
+  unsigned int scal[4][kHeavyTile];
+  unsigned char tip[4][kHeavyTile];
+  unsigned long long bar[4];
+};
+
+template <int C>
+__device__ __forceinline__ void stage_child(const DevState &s, PrepSmem<C> &sm, int slot,
+                                            unsigned int clv_index, int scaler_index,
+                                            unsigned int site_base, unsigned int nvalid)
+{
+  if (clv_index < s.n_tips)
+  {
+    const unsigned int bytes = (nvalid + 15u) & ~15u;
+    mbar_expect_tx(&sm.bar[slot], bytes);
+    bulk_g2s(sm.tip[slot], s.tips + (size_t)clv_index * s.tip_stride + site_base, bytes,
+             &sm.bar[slot]);
+    return;
+  }
+  const unsigned int cbytes = nvalid * C * 32u;
+  const unsigned int sbytes = scaler_index >= 0 ? ((nvalid * 4u + 15u) & ~15u) : 0u;
+  mbar_expect_tx(&sm.bar[slot], cbytes + sbytes);
+  bulk_g2s(sm.clv[slot],
+           s.clv + (size_t)(clv_index - s.n_tips) * s.clv_stride + (size_t)site_base * C * 4,
+           cbytes, &sm.bar[slot]);
+  if (sbytes)
+    bulk_g2s(sm.scal[slot], s.scalers + (size_t)scaler_index * s.scaler_stride + site_base,
+             sbytes, &sm.bar[slot]);
+}
+
+template <int C>
+__device__ __forceinline__ unsigned int staged_entry(const DevState &s, const PrepSmem<C> &sm,
+                                                     int slot, unsigned int clv_index,
+                                                     int scaler_index, unsigned int local_site,
+                                                     int cat, double v[4])
+{
+  if (clv_index < s.n_tips)
+  {
+    const unsigned int m = sm.tip[slot][local_site];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = ((m >> j) & 1u) ? 1.0 : 0.0;
+    return 0u;
+  }
+  lds256(&sm.clv[slot][((size_t)local_site * C + cat) * 4], v);
+  return scaler_index >= 0 ? sm.scal[slot][local_site] : 0u;
+}
+
+// One CTA = one candidate group x one tile of sites.  The four projected
+// vectors M_k * child_k (the expensive part: 4 dot products each) are computed
+// once and shared by the two candidates of the group; per candidate only the
+// elementwise products, the scaling test and the sumtable entry remain.
+template <int C>
+__device__ __forceinline__ void finish_candidate(const DevState &s, const ModelConst &m,
+                                                 const double a[4], const double b[4],
+                                                 const double c[4], const double d[4],
+                                                 unsigned int cnt, bool store, double *dst,
+                                                 unsigned int *sclr_dst, int cat)
+{
+  double pp[4], qq[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+  {
+    pp[i] = __dmul_rn(a[i], b[i]);
+    qq[i] = __dmul_rn(c[i], d[i]);
+  }
+  bool sp = (pp[0] < PT_SCALE_THRESHOLD) & (pp[1] < PT_SCALE_THRESHOLD) &
+            (pp[2] < PT_SCALE_THRESHOLD) & (pp[3] < PT_SCALE_THRESHOLD);
+  bool sq = (qq[0] < PT_SCALE_THRESHOLD) & (qq[1] < PT_SCALE_THRESHOLD) &
+            (qq[2] < PT_SCALE_THRESHOLD) & (qq[3] < PT_SCALE_THRESHOLD);
+  sp = site_all<C>(sp);
+  sq = site_all<C>(sq);
+  if (sp)
+  {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) pp[i] = __dmul_rn(pp[i], PT_SCALE_FACTOR);
+  }
+  if (sq)
+  {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) qq[i] = __dmul_rn(qq[i], PT_SCALE_FACTOR);
+  }
+  double sum[4];
+  sumtable_entry<C>(m, pp, qq, sum);
+  if (store)
+  {
+    st256(dst, sum);
+    if (cat == 0) *sclr_dst = cnt + (sp ? 1u : 0u) + (sq ? 1u : 0u);
+  }
+}
+
 template <int C>
 __global__ void __launch_bounds__(kHeavySites *C)
-    nni_prepare_kernel(DevState s, ModelConst m, const DevCand *__restrict__ cands,
-                       unsigned int ncands, double *sumtables, size_t entry_stride,
+    nni_prepare_kernel(DevState s, ModelConst m, const DevGroup *__restrict__ groups,
+                       unsigned int ngroups, double *sumtables, size_t entry_stride,
                        unsigned int *sclr)
 {
-  const unsigned int b = blockIdx.x % ncands, tile = blockIdx.x / ncands;
-  const DevCand cd = cands[b];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  PrepSmem<C> &sm = *reinterpret_cast<PrepSmem<C> *>(smem_raw);
+  const unsigned int g = blockIdx.x % ngroups, tile = blockIdx.x / ngroups;
+  const DevGroup gr = groups[g];
   const int cat = threadIdx.x % C;
-  const unsigned int site0 = tile * kHeavyTile + threadIdx.x / C;
-  double *out = sumtables + (size_t)b * entry_stride;
+  const unsigned int lsite0 = threadIdx.x / C;
+  const unsigned int site_base = tile * kHeavyTile;
+  const unsigned int nvalid = min((unsigned int)kHeavyTile, s.sites - site_base);
 
-  // phase A: the CLV on the p side for all passes of the tile (kept in registers)
-  double pp[kHeavyPasses][4];
-  unsigned int cnt[kHeavyPasses];
+  if (threadIdx.x == 0)
   {
-    double lm[16], rm[16];
-    load_matrix<C>(s.pmat + ((size_t)cd.p.c1_mat * C + cat) * 16, lm);
-    load_matrix<C>(s.pmat + ((size_t)cd.p.c2_mat * C + cat) * 16, rm);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) mbar_init(&sm.bar[i], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      stage_child<C>(s, sm, k, gr.ch[k].clv, gr.ch[k].scaler, site_base, nvalid);
+  }
+
+  double proj[4][kHeavyPasses][4];
+  unsigned int cnt[kHeavyPasses];
+#pragma unroll
+  for (int ps = 0; ps < kHeavyPasses; ++ps) cnt[ps] = 0u;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+  {
+    double mt[16];
+    load_matrix<C>(s.pmat + ((size_t)gr.ch[k].mat * C + cat) * 16, mt);
+    mbar_wait(&sm.bar[k], 0);
 #pragma unroll
     for (int ps = 0; ps < kHeavyPasses; ++ps)
     {
-      const unsigned int site = min(site0 + ps * kHeavySites, s.sites - 1);
-      double x1[4], x2[4];
-      load_entry<C>(s, cd.p.c1_clv, site, cat, x1);
-      load_entry<C>(s, cd.p.c2_clv, site, cat, x2);
-      cnt[ps] = load_scaler(s, cd.p.c1_scaler, site) + load_scaler(s, cd.p.c2_scaler, site);
-      combine_entry(lm, rm, x1, x2, pp[ps]);
-      bool sp = (pp[ps][0] < PT_SCALE_THRESHOLD) & (pp[ps][1] < PT_SCALE_THRESHOLD) &
-                (pp[ps][2] < PT_SCALE_THRESHOLD) & (pp[ps][3] < PT_SCALE_THRESHOLD);
-      sp = site_all<C>(sp);
-      if (sp)
-      {
+      const unsigned int ls = min(lsite0 + ps * kHeavySites, nvalid - 1);
+      double x[4];
+      cnt[ps] += staged_entry<C>(s, sm, k, gr.ch[k].clv, gr.ch[k].scaler, ls, cat, x);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) pp[ps][i] = __dmul_rn(pp[ps][i], PT_SCALE_FACTOR);
-        cnt[ps] += 1u;
-      }
+      for (int i = 0; i < 4; ++i) proj[k][ps][i] = dot4(mt + 4 * i, x);
     }
   }
-  // phase B: the q side, the sumtable entry, the stores
+#pragma unroll
+  for (int ps = 0; ps < kHeavyPasses; ++ps)
   {
-    double lm[16], rm[16];
-    load_matrix<C>(s.pmat + ((size_t)cd.q.c1_mat * C + cat) * 16, lm);
-    load_matrix<C>(s.pmat + ((size_t)cd.q.c2_mat * C + cat) * 16, rm);
-#pragma unroll
-    for (int ps = 0; ps < kHeavyPasses; ++ps)
-    {
-      const unsigned int site_raw = site0 + ps * kHeavySites;
-      const unsigned int site = min(site_raw, s.sites - 1);
-      double y1[4], y2[4], qq[4];
-      load_entry<C>(s, cd.q.c1_clv, site, cat, y1);
-      load_entry<C>(s, cd.q.c2_clv, site, cat, y2);
-      unsigned int c2 = cnt[ps] + load_scaler(s, cd.q.c1_scaler, site) +
-                        load_scaler(s, cd.q.c2_scaler, site);
-      combine_entry(lm, rm, y1, y2, qq);
-      bool sq = (qq[0] < PT_SCALE_THRESHOLD) & (qq[1] < PT_SCALE_THRESHOLD) &
-                (qq[2] < PT_SCALE_THRESHOLD) & (qq[3] < PT_SCALE_THRESHOLD);
-      sq = site_all<C>(sq);
-      if (sq)
-      {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) qq[i] = __dmul_rn(qq[i], PT_SCALE_FACTOR);
-        c2 += 1u;
-      }
-      double sum[4];
-      sumtable_entry<C>(m, pp[ps], qq, sum);
-      if (site_raw < s.sites)
-      {
-        st256(out + ((size_t)site * C + cat) * 4, sum);
-        if (cat == 0) sclr[(size_t)b * s.sites + site] = c2;
-      }
-    }
+    const unsigned int ls_raw = lsite0 + ps * kHeavySites;
+    const bool ok = ls_raw < nvalid;
+    const unsigned int site = site_base + min(ls_raw, nvalid - 1);
+    const size_t eoff = ((size_t)site * C + cat) * 4;
+    finish_candidate<C>(s, m, proj[0][ps], proj[1][ps], proj[2][ps], proj[3][ps], cnt[ps], ok,
+                        sumtables + (size_t)gr.out[0] * entry_stride + eoff,
+                        sclr + (size_t)gr.out[0] * s.sites + site, cat);
+    if (gr.ncand > 1)
+      finish_candidate<C>(s, m, proj[3][ps], proj[1][ps], proj[2][ps], proj[0][ps], cnt[ps], ok,
+                          sumtables + (size_t)gr.out[1] * entry_stride + eoff,
+                          sclr + (size_t)gr.out[1] * s.sites + site, cat);
   }
 }
 
