@@ -90,6 +90,9 @@ void ptgpu_destroy(ptgpu_engine *e); /* pll_partition_destroy */
    result is kept as kernel constants.  subst = ac ag at cg ct gt. */
 int ptgpu_set_model(ptgpu_engine *e, const double freqs[4], const double subst[6],
                     const double *category_rates);
+/* pll_compute_gamma_cats(alpha, cats, rates, PLL_GAMMA_RATES_MEAN)
+   (LIBPLL/gamma.c:220-292): host-only, needs no engine and no device. */
+int ptgpu_gamma_rates_mean(double alpha, unsigned int cats, double *rates_out);
 /* read back what the kernels use (test hook) */
 int ptgpu_get_eigen(ptgpu_engine *e, double evecs[16], double inv_evecs[16],
                     double evals[4]);
@@ -140,6 +143,25 @@ int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
                           int child_scaler_index, unsigned int matrix_index,
                           double length0, unsigned int max_iter, double epsilon,
                           double map_lambda, double *length_out, int *iterations);
+
+/* One edge of pllmod's local branch-length optimisation, i.e. the body of
+   recomp_iterative up to and including pllmod_opt_minimize_newton
+   (PLLMOD/optimize/pll_optimize.c:771-827, opt_algorithms.c:71-172): sumtable
+   of the edge, then the safeguarded Newton-Raphson / bisection iteration in
+   [xmin, xmax] from xguess with the reference's stopping rules, all in one
+   device-resident loop.  PLLMOD = /root/reference/lib/libptpll/lib/pll-modules/src.
+   *status: 0 converged, PTGPU_NEWTON_DERIV (derivative not finite; the
+   reference sets PLLMOD_OPT_ERROR_NEWTON_DERIV and returns -inf),
+   PTGPU_NEWTON_LIMIT (max_iter evaluations used up; the reference sets
+   PLLMOD_OPT_ERROR_NEWTON_LIMIT).  No P matrix is touched: the caller decides
+   (keep_update, pll_optimize.c:829-868). */
+#define PTGPU_NEWTON_DERIV 1
+#define PTGPU_NEWTON_LIMIT 2
+int ptgpu_optimize_branch_bounded(ptgpu_engine *e, unsigned int parent_clv_index,
+                                  int parent_scaler_index, unsigned int child_clv_index,
+                                  int child_scaler_index, double xguess, double xmin,
+                                  double xmax, double tolerance, unsigned int max_iter,
+                                  double *length_out, int *status, int *iterations);
 
 /* Batched SingleBranchOptimizer::EvaluateMove
    (src/move_tester/single_branch_optimizer.cpp:23-64) for `count` candidates

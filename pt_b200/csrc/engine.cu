@@ -315,6 +315,13 @@ int ptgpu_set_model(ptgpu_engine *e, const double freqs[4], const double subst[6
   return PTGPU_OK;
 }
 
+int ptgpu_gamma_rates_mean(double alpha, unsigned int cats, double *rates_out)
+{
+  if (!gamma_mean_rates(alpha, cats, rates_out))
+    return fail(PTGPU_ERR_ARG, "ptgpu_gamma_rates_mean: alpha %g / categories %u out of range", alpha, cats);
+  return PTGPU_OK;
+}
+
 int ptgpu_get_eigen(ptgpu_engine *e, double evecs[16], double inv_evecs[16], double evals[4])
 {
   if (!e || !e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
@@ -539,7 +546,8 @@ int ptgpu_update_sumtable(ptgpu_engine *e, unsigned int parent_clv_index,
 }
 
 static int newton_single(ptgpu_engine *e, double len0, unsigned int max_iter, double eps,
-                         double lambda, NewtonState *out)
+                         double lambda, NewtonState *out, int mode = 0, double xmin = 0.0,
+                         double xmax = 0.0)
 {
   NewtonState init{};
   init.len = len0;
@@ -554,6 +562,7 @@ static int newton_single(ptgpu_engine *e, double len0, unsigned int max_iter, do
   a.partials = e->d_partials;
   a.sites = e->sites; a.B = 1; a.ntiles = e->ntiles; a.chunk_tiles = e->chunk_tiles; a.nchunks = e->nchunks; a.max_iter = max_iter;
   a.eps = eps; a.lambda = lambda; a.want_lnl = 0;
+  a.mode = mode; a.xmin = xmin; a.xmax = xmax;
   if ((rc = run_newton(e, a))) return rc;
   e->counters[2] += max_iter; // upper bound; exact count is returned in state.iters
   (void)out;
@@ -602,6 +611,34 @@ int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
   if (iterations) *iterations = hs->iters;
   if (hs->status == 1) return fail(PTGPU_ERR_NOT_FINITE, "d1 is not finite");
   if (hs->status == 2) return fail(PTGPU_ERR_NOT_FINITE, "d2 is not finite");
+  return PTGPU_OK;
+}
+
+int ptgpu_optimize_branch_bounded(ptgpu_engine *e, unsigned int parent_clv_index,
+                                  int parent_scaler_index, unsigned int child_clv_index,
+                                  int child_scaler_index, double xguess, double xmin,
+                                  double xmax, double tolerance, unsigned int max_iter,
+                                  double *length_out, int *status, int *iterations)
+{
+  if (!e || !length_out || !status)
+    return fail(PTGPU_ERR_ARG, "ptgpu_optimize_branch_bounded: null argument");
+  if (!(xmin <= xmax) || !(tolerance > 0) || !max_iter)
+    return fail(PTGPU_ERR_ARG, "ptgpu_optimize_branch_bounded: bad bounds / tolerance");
+  int rc;
+  if ((rc = ptgpu_update_sumtable(e, parent_clv_index, child_clv_index, parent_scaler_index,
+                                  child_scaler_index)))
+    return rc;
+  // rts = xguess clamped into [xmin, xmax] (PLLMOD/optimize/opt_algorithms.c:88-92)
+  double rts = xguess;
+  if (rts < xmin) rts = xmin;
+  if (rts > xmax) rts = xmax;
+  if ((rc = newton_single(e, rts, max_iter, tolerance, 0.0, nullptr, 1, xmin, xmax))) return rc;
+  NewtonState *hs = (NewtonState *)(e->stg.host + 64);
+  CU(cudaMemcpyAsync(hs, e->d_state, sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  *length_out = hs->len;
+  *status = hs->status;
+  if (iterations) *iterations = hs->iters;
   return PTGPU_OK;
 }
 

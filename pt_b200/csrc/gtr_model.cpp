@@ -207,3 +207,165 @@ unsigned int nucleotide_mask(unsigned char ch)
 }
 
 } // namespace ptgpu
+
+// ---------------------------------------------------------------------------
+// Discrete-Gamma category rates (mean of each equal-probability category),
+// Yang (1994) J Mol Evol 39:306-314, built from the published routines it
+// cites: Lanczos/Stirling ln Gamma (Pike & Hill 1966, ACM 291), incomplete
+// gamma ratio (Bhattacharjee 1970, AS 32), normal quantile (Odeh & Evans 1974,
+// AS 70) and chi-square quantile (Best & Roberts 1975, AS 91).  The operation
+// order is that of the reference's host routine
+// (/root/reference/lib/libptpll/lib/pll-modules/libs/libpll/src/gamma.c:24-292)
+// because the rates feed every P matrix: they have to be the same doubles.
+// ---------------------------------------------------------------------------
+namespace ptgpu {
+namespace {
+
+double log_gamma(double a)
+{
+  double x = a, lead = 0.0;
+  if (x < 7.0)
+  {
+    double prod = 1.0, z = a - 1.0;
+    while ((z = z + 1.0) < 7.0) prod *= z;
+    x = z;
+    lead = -std::log(prod);
+  }
+  const double z = 1 / (x * x);
+  return lead + (x - 0.5) * std::log(x) - x + .918938533204673 +
+         (((-.000595238095238 * z + .000793650793651) * z - .002777777777778) * z +
+          .083333333333333) / x;
+}
+
+// P(alpha, x) = regularised lower incomplete gamma; -1 on a domain error
+double gamma_ratio(double x, double alpha, double lg_alpha)
+{
+  constexpr double kAccurate = 1e-8, kOverflow = 1e30;
+  if (x == 0) return 0;
+  if (x < 0 || alpha <= 0) return -1;
+  const double front = std::exp(alpha * std::log(x) - x - lg_alpha);
+  if (!(x > 1 && x >= alpha))
+  {
+    double sum = 1, term = 1, k = alpha;
+    do
+    {
+      k++;
+      term *= x / k;
+      sum += term;
+    } while (term > kAccurate);
+    sum *= front / alpha;
+    return sum;
+  }
+  // continued fraction with renormalisation of the convergents
+  double a = 1 - alpha, b = a + x + 1, n = 0;
+  double conv[6] = {1, x, x + 1, x * b, 0, 0};
+  double ratio = conv[2] / conv[3];
+  for (;;)
+  {
+    a++;
+    b += 2;
+    n++;
+    const double an = a * n;
+    conv[4] = b * conv[2] - an * conv[0];
+    conv[5] = b * conv[3] - an * conv[1];
+    if (conv[5] != 0)
+    {
+      const double next = conv[4] / conv[5];
+      const double gap = std::fabs(ratio - next);
+      if (!(gap > kAccurate) && gap <= kAccurate * next) return 1 - front * ratio;
+      ratio = next;
+    }
+    for (int i = 0; i < 4; ++i) conv[i] = conv[i + 2];
+    if (!(std::fabs(conv[4]) < kOverflow))
+      for (int i = 0; i < 4; ++i) conv[i] /= kOverflow;
+  }
+}
+
+double normal_quantile(double p)
+{
+  const double q = p < 0.5 ? p : 1 - p;
+  if (q < 1e-20) return -9999;
+  const double y = std::sqrt(std::log(1 / (q * q)));
+  const double num = (((y * -.453642210148e-4 + -.0204231210245) * y + -.342242088547) * y + -1) * y +
+                     -.322232431088;
+  const double den = (((y * .0038560700634 + .103537752850) * y + .531103462366) * y + .588581570495) * y +
+                     .0993484626060;
+  const double z = y + num / den;
+  return p < 0.5 ? -z : z;
+}
+
+double chi2_quantile(double p, double v)
+{
+  constexpr double kEps = .5e-6, kLn2 = .6931471805;
+  if (p < .000002 || p > .999998 || v <= 0) return -1;
+  const double g = log_gamma(v / 2);
+  const double half = v / 2, c = half - 1;
+  double ch;
+  if (!(v >= -1.24 * std::log(p)))
+  {
+    ch = std::pow(p * half * std::exp(g + half * kLn2), 1 / half);
+    if (ch - kEps < 0) return ch;
+  }
+  else if (v > .32)
+  {
+    const double x = normal_quantile(p);
+    const double p1 = 0.222222 / v;
+    ch = v * std::pow(x * std::sqrt(p1) + 1 - p1, 3.0);
+    if (ch > 2.2 * v + 6) ch = -2 * (std::log(1 - p) - c * std::log(.5 * ch) + g);
+  }
+  else
+  {
+    ch = 0.4;
+    const double a = std::log(1 - p);
+    double prev;
+    do
+    {
+      prev = ch;
+      const double p1 = 1 + ch * (4.67 + ch);
+      const double p2 = ch * (6.73 + ch * (6.66 + ch));
+      const double t = -0.5 + (4.67 + 2 * ch) / p1 - (6.73 + ch * (13.32 + 3 * ch)) / p2;
+      ch -= (1 - std::exp(a + g + .5 * ch + c * kLn2) * p2 / p1) / t;
+    } while (!(std::fabs(prev / ch - 1) - .01 <= 0));
+  }
+  double prev;
+  do
+  {
+    prev = ch;
+    const double p1 = .5 * ch;
+    double t = gamma_ratio(p1, half, g);
+    if (t < 0.0) return -1;
+    const double p2 = p - t;
+    t = p2 * std::exp(half * kLn2 + g + p1 - c * std::log(ch));
+    const double b = t / ch;
+    const double a = 0.5 * t - b * c;
+    const double s1 = (210 + a * (140 + a * (105 + a * (84 + a * (70 + 60 * a))))) / 420;
+    const double s2 = (420 + a * (735 + a * (966 + a * (1141 + 1278 * a)))) / 2520;
+    const double s3 = (210 + a * (462 + a * (707 + 932 * a))) / 2520;
+    const double s4 = (252 + a * (672 + 1182 * a) + c * (294 + a * (889 + 1740 * a))) / 5040;
+    const double s5 = (84 + 264 * a + c * (175 + 606 * a)) / 2520;
+    const double s6 = (120 + c * (346 + 127 * c)) / 5040;
+    ch += t * (1 + 0.5 * t * s1 - b * c * (s1 - b * (s2 - b * (s3 - b * (s4 - b * (s5 - b * s6))))));
+  } while (std::fabs(prev / ch - 1) > kEps);
+  return ch;
+}
+
+} // namespace
+
+bool gamma_mean_rates(double alpha, unsigned int cats, double *rates)
+{
+  if (alpha < 0.02 || cats < 1 || !rates) return false;
+  if (cats == 1) { rates[0] = 1.0; return true; }
+  const double scale = alpha / alpha * cats;
+  const double lg1 = log_gamma(alpha + 1);
+  std::array<double, 64> cut{};
+  if (cats > cut.size()) return false;
+  for (unsigned int i = 0; i + 1 < cats; ++i)
+    cut[i] = chi2_quantile((i + 1.0) / cats, 2.0 * alpha) / (2.0 * alpha);
+  for (unsigned int i = 0; i + 1 < cats; ++i) cut[i] = gamma_ratio(cut[i] * alpha, alpha + 1, lg1);
+  rates[0] = cut[0] * scale;
+  rates[cats - 1] = (1 - cut[cats - 2]) * scale;
+  for (unsigned int i = 1; i + 1 < cats; ++i) rates[i] = (cut[i] - cut[i - 1]) * scale;
+  return true;
+}
+
+} // namespace ptgpu

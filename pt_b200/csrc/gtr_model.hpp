@@ -11,4 +11,8 @@ void gtr_eigensystem(const double freqs[4], const double subst[6], double evecs[
 // IUPAC nucleotide code -> 4-bit state set (A=1 C=2 G=4 T=8), 0 if illegal.
 unsigned int nucleotide_mask(unsigned char ch);
 
+// Mean rates of `cats` equal-probability categories of Gamma(alpha, alpha)
+// (Yang 1994); false if alpha < 0.02 or cats is 0 / > 64.
+bool gamma_mean_rates(double alpha, unsigned int cats, double *rates);
+
 } // namespace ptgpu

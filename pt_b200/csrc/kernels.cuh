@@ -106,7 +106,9 @@ struct NewtonState
   int iters;
   int done;             // 0 running, 1 finished
   int maybe_decreasing;
-  int status;           // 0 ok, 1 d1 not finite, 2 d2 not finite
+  int status;           // mode 0: 0 ok, 1 d1 not finite, 2 d2 not finite
+                        // mode 1: 0 ok, 1 derivative not finite, 2 iteration limit
+  double xl, xh;        // mode 1: current bracket
 };
 
 // ---------------------------------------------------------------- helpers
@@ -676,7 +678,56 @@ struct NewtonArgs
   unsigned int sites, B, ntiles, chunk_tiles, nchunks, max_iter;
   double eps, lambda;
   int want_lnl;
+  int mode;                 // 0: Partition::OptimizeBranch, 1: pllmod_opt_minimize_newton
+  double xmin, xmax;        // mode 1 bounds
 };
+
+// One step of pllmod_opt_minimize_newton (PLLMOD/optimize/opt_algorithms.c:71-172)
+// after the derivative evaluation number st.iters+1 at st.len: bracket update,
+// Newton step with bisection fallback, stopping rules.  Plain double arithmetic
+// without contraction, as the reference is compiled (-mavx, no FMA).
+__device__ __forceinline__ void bounded_newton_step(NewtonState &st, double f, double df,
+                                                    const NewtonArgs &a)
+{
+  const bool first = st.iters == 0;
+  st.iters += 1;
+  st.d1 = f;
+  st.d2 = df;
+  if (!isfinite(f) || !isfinite(df)) { st.status = 1; st.done = 1; return; }
+  if (first)
+  {
+    if (df >= 0.0 && fabs(f) < a.eps) { st.done = 1; return; }
+    if (f < 0.0) { st.xl = st.len; st.xh = a.xmax; }
+    else { st.xh = st.len; st.xl = a.xmin; }
+  }
+  else
+  {
+    if (df > 0.0 && fabs(f) < a.eps) { st.done = 1; return; }
+    if (f < 0.0) st.xl = st.len; else st.xh = st.len;
+  }
+  const double xl = st.xl, xh = st.xh;
+  double rts = st.len, dx;
+  const double rts_old = rts;
+  const double t1 = __dadd_rn(__dmul_rn(__dadd_rn(rts, -xh), df), -f);
+  const double t2 = __dadd_rn(__dmul_rn(__dadd_rn(rts, -xl), df), -f);
+  if (df <= 0.0 || __dmul_rn(t1, t2) >= 0.0)
+  {
+    dx = __dmul_rn(0.5, __dadd_rn(xh, -xl));
+    rts = __dadd_rn(xl, dx);
+    if (xl == rts) { st.len = rts; st.done = 1; return; }
+  }
+  else
+  {
+    dx = __ddiv_rn(f, df);
+    const double temp = rts;
+    rts = __dadd_rn(rts, -dx);
+    if (temp == rts) { st.len = rts; st.done = 1; return; }
+  }
+  if (fabs(dx) < a.eps) { st.len = rts_old; st.done = 1; return; }
+  if ((unsigned int)st.iters >= a.max_iter) { st.len = rts_old; st.status = 2; st.done = 1; return; }
+  if (rts < a.xmin) rts = a.xmin;
+  st.len = rts;
+}
 
 // Persistent cooperative kernel: the whole Newton-Raphson loop of
 // Partition::OptimizeBranch (PTPLL/pll_partition.cpp:419-481) for B branches
@@ -736,26 +787,33 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
         st.done = 0;
         st.maybe_decreasing = __ldcg(&a.st[e].maybe_decreasing);
         st.status = 0;
-        double d1 = a1, d2 = a2;
-        if (a.lambda != 0.0) d1 = __dadd_rn(d1, a.lambda);
-        st.d1 = d1;
-        st.d2 = d2;
-        st.iters += 1;
-        if (!isfinite(d1)) { st.status = 1; st.done = 1; }
-        else if (!isfinite(d2)) { st.status = 2; st.done = 1; }
-        else if (fabs(d1) < a.eps) st.done = 1;
+        st.xl = __ldcg(&a.st[e].xl);
+        st.xh = __ldcg(&a.st[e].xh);
+        if (a.mode == 1)
+          bounded_newton_step(st, a1, a2, a);
         else
         {
-          const double step = __ddiv_rn(d1, d2);
-          st.len = (d2 < 0.0) ? __dadd_rn(st.len, step) : __dadd_rn(st.len, -step);
-          if (st.len < 0.0)
+          double d1 = a1, d2 = a2;
+          if (a.lambda != 0.0) d1 = __dadd_rn(d1, a.lambda);
+          st.d1 = d1;
+          st.d2 = d2;
+          st.iters += 1;
+          if (!isfinite(d1)) { st.status = 1; st.done = 1; }
+          else if (!isfinite(d2)) { st.status = 2; st.done = 1; }
+          else if (fabs(d1) < a.eps) st.done = 1;
+          else
           {
-            st.len = a.eps;
-            if (st.maybe_decreasing) st.done = 1;
-            st.maybe_decreasing = 1;
+            const double step = __ddiv_rn(d1, d2);
+            st.len = (d2 < 0.0) ? __dadd_rn(st.len, step) : __dadd_rn(st.len, -step);
+            if (st.len < 0.0)
+            {
+              st.len = a.eps;
+              if (st.maybe_decreasing) st.done = 1;
+              st.maybe_decreasing = 1;
+            }
           }
+          if (st.iters >= (int)a.max_iter) st.done = 1;
         }
-        if (st.iters >= (int)a.max_iter) st.done = 1;
         a.st[e] = st;
       }
     }

@@ -1,0 +1,137 @@
+// pt_b200/host/include/pll_partition.hpp -- pt::pll::Partition over the B200
+// engine (include/ptgpu.h).
+//
+// Drop-in for the reference's lib/libptpll/src/pll_partition.hpp:23-96: same
+// class name, constructor, public methods, constants and exception behaviour,
+// so src/wanderer.cpp, src/guru.cpp, the move testers and both Catch test files
+// of the reference compile against it unchanged.  What differs is behind the
+// methods: there is no pll_partition_t; every numeric step is a call into the
+// extern "C" engine, which runs hand-written sm_100a kernels (no CPU path).
+//
+//   reference member (pll_partition.hpp)            here
+//   PartitionPtr partition_ (pll_partition_t)       ptgpu_engine* engine_
+//   double* sumtable_ (host scratch, :45)           engine-owned device sumtable
+//   travbuffer_/branch_lengths_/matrix_indices_/    same host scratch (the traversal
+//   operations_ (:39-42)                            descriptor is still built on the host)
+//
+// Threading is the reference's: one Partition per wanderer thread, methods not
+// re-entrant per object.  Each Partition owns one engine = one CUDA stream on
+// one device; devices are assigned round-robin over the visible GPUs
+// (wanderer-parallel) unless PTGPU_DEVICE pins one.
+#ifndef PT_B200_HOST_PLL_PARTITION_HPP_
+#define PT_B200_HOST_PLL_PARTITION_HPP_
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <libpll/pll.h>
+
+#include "model.hpp"
+#include "pll_util.hpp"
+
+struct ptgpu_engine;
+
+namespace pt { namespace pll {
+
+// MAX_ITER: Max iterations when optimizing branch lengths.
+const unsigned int MAX_ITER = 32;
+const double EPSILON = 1e-6; // Threshold for detecting zero.
+
+class Partition
+{
+ private:
+  const unsigned int tip_node_count_;
+  bool map_mode_;
+  ptgpu_engine* engine_;
+  Model model_;
+  unsigned int site_count_;
+
+  // scratch buffers for TraversalUpdate()
+  std::vector<pll_unode_t*> travbuffer_;
+  std::vector<double> branch_lengths_;
+  std::vector<unsigned int> matrix_indices_;
+  std::vector<pll_operation_t> operations_;
+
+ public:
+  Partition(pll_utree_t* tree,
+            const Model& model,
+            const std::vector<std::string>& labels,
+            const std::vector<std::string>& sequences,
+            bool map_mode = false);
+
+  Partition(Partition&& rhs);
+
+  Partition(const Partition& rhs) = delete;
+  Partition& operator=(const Partition& rhs) = delete;
+  Partition& operator=(Partition&& rhs) = delete;
+
+  ~Partition();
+
+  double LogLikelihood(pll_unode_t* tree, double* per_site_lnl = nullptr);
+  double LogMarginalLikelihood(pll_unode_t* root);
+
+  unsigned int TraversalUpdate(pll_unode_t* root, TraversalType type);
+  void UpdateBranchLength(pll_unode_t* node, double length);
+
+  double OptimizeBranch(pll_unode_t* node);
+  void OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod = false);
+  void OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod = false);
+  void OptimizeBranchNeighborhood(pll_unode_t* node, int radius);
+
+  double OptimizeModelOnce(pll_unode_t* tree);
+  double OptimizeModel(pll_unode_t* tree);
+
+  double OptimizeAllBranchesAndModel(pll_unode_t* tree, bool use_pllmod = false);
+
+  Model GetModel() const;
+  void SetModel(const Model& model);
+
+  unsigned int tip_node_count() const;
+  unsigned int inner_node_count() const;
+  unsigned int node_count() const;
+  unsigned int branch_count() const;
+
+  // ---- additions of the B200 build (not in the reference surface) ----
+
+  // Scores every NNI candidate Wanderer::QueueMoves would test on `tree`
+  // (src/wanderer.cpp:242-285: inner-node entries of tree->nodes in order,
+  // pendant edges skipped, LEFT then RIGHT) in ONE batched engine call with
+  // SingleBranchOptimizer semantics (src/move_tester/single_branch_optimizer.cpp:23-64):
+  // optimised central branch length and log-likelihood per candidate.  The
+  // tree, its lengths and the partition's CLV orientation flags are left
+  // untouched (the batch works on a private set of directional CLVs).
+  struct NniScore {
+    pll_unode_t* node;   // the edge node passed to pll_utree_nni
+    int type;            // PLL_UTREE_MOVE_NNI_LEFT / _RIGHT
+    double length;       // optimised length of the central branch
+    double lnl;          // log-likelihood at that length
+  };
+  std::vector<NniScore> ScoreNniNeighborhood(pll_utree_t* tree);
+
+  int device() const { return device_; }
+  ptgpu_engine* engine() { return engine_; }
+
+ private:
+  int device_;
+  unsigned int directional_base_;  // first extra CLV / scaler buffer (0 = none allocated)
+
+  void SetTipStates(pll_utree_t* tree, const std::vector<std::string>& labels,
+                    const std::vector<std::string>& sequences);
+  void AllocateScratchBuffers();
+  void Check(int rc) const;
+  double MapLogPrior(pll_unode_t* tree);
+  double LocalBranchOptimization(pll_unode_t* tree, double bl_min, double bl_max,
+                                 double tolerance, int smoothings, int radius);
+  bool OptimizeEdgeBounded(pll_unode_t* edge, double bl_min, double bl_max,
+                           double tolerance, int radius);
+};
+
+inline unsigned int Partition::tip_node_count() const { return tip_node_count_; }
+inline unsigned int Partition::inner_node_count() const { return tip_node_count_ - 2; }
+inline unsigned int Partition::node_count() const { return tip_node_count() + inner_node_count(); }
+inline unsigned int Partition::branch_count() const { return node_count() - 1; }
+
+} } // namespace pt::pll
+
+#endif // PT_B200_HOST_PLL_PARTITION_HPP_

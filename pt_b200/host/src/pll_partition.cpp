@@ -1,0 +1,576 @@
+// pt_b200/host/src/pll_partition.cpp -- pt::pll::Partition over the B200 engine.
+//
+// Host control flow follows the reference's lib/libptpll/src/pll_partition.cpp
+// (cited as PTPLL/pll_partition.cpp:line) so that callers observe the same
+// sequence of states; every numeric step is an extern "C" call into
+// libptgpu.so (include/ptgpu.h).  Nothing here computes a likelihood on the
+// CPU: if the engine cannot be created the constructor throws.
+#include "pll_partition.hpp"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <strings.h>
+#include <vector>
+
+#include "ptgpu.h"
+
+static_assert(sizeof(pll_operation_t) == sizeof(ptgpu_operation_t),
+              "ptgpu_operation_t must mirror pll_operation_t");
+
+namespace pt { namespace pll {
+
+namespace {
+
+// pll-modules' DNA model names (PLLMOD/util/models_dna.c:64-106); SetModel
+// accepts exactly these, case-insensitively, and GetModel reports the
+// canonical spelling, as pllmod_util_model_info_dna does.
+const char* const kDnaModels[] = {
+    "JC", "K80", "F81", "HKY", "TN93ef", "TN93", "K81", "K81uf", "TPM2", "TPM2uf", "TPM3",
+    "TPM3uf", "TIM1", "TIM1uf", "TIM2", "TIM2uf", "TIM3", "TIM3uf", "TVMef", "TVM", "SYM", "GTR"};
+
+const char* canonical_model_name(const std::string& name)
+{
+  for (const char* m : kDnaModels)
+    if (strcasecmp(name.c_str(), m) == 0) return m;
+  return nullptr;
+}
+
+const double kMapLambda = 10.0;  // exponential prior rate, PTPLL/pll_partition.cpp:255,318,435
+
+std::atomic<unsigned int> g_next_device{0};
+
+int pick_device()
+{
+  if (const char* env = std::getenv("PTGPU_DEVICE")) return std::atoi(env);
+  const int n = ptgpu_device_count();
+  if (n <= 0) return 0;  // ptgpu_create reports the missing device
+  return static_cast<int>(g_next_device.fetch_add(1) % static_cast<unsigned int>(n));
+}
+
+int visit_all(pll_unode_t*) { return 1; }
+
+} // namespace
+
+void Partition::Check(int rc) const
+{
+  if (rc == PTGPU_OK) return;
+  const std::string msg = ptgpu_last_error();
+  if (rc == PTGPU_ERR_NOT_FINITE) throw std::range_error(msg);
+  if (rc == PTGPU_ERR_ARG || rc == PTGPU_ERR_STATE) throw std::invalid_argument(msg);
+  throw std::runtime_error("ptgpu: " + msg);
+}
+
+// PTPLL/pll_partition.cpp:25-65
+Partition::Partition(pll_utree_t* tree,
+                     const Model& model,
+                     const std::vector<std::string>& labels,
+                     const std::vector<std::string>& sequences,
+                     bool map_mode) :
+    tip_node_count_(tree->tip_count),
+    map_mode_(map_mode),
+    engine_(nullptr),
+    site_count_(0),
+    device_(0),
+    directional_base_(0)
+{
+  if (!TreeHealthy(tree)) throw std::invalid_argument("Tree is missing branch lengths");
+  if (sequences.empty()) throw std::invalid_argument("No sequences supplied");
+  site_count_ = static_cast<unsigned int>(sequences[0].size());
+
+  // One CLV + scaler buffer per inner node as in pll_partition_create
+  // (PTPLL/pll_partition.cpp:47-57), plus one per inner-node RECORD (3(n-2))
+  // for the directional CLVs of the batched NNI scorer.
+  const bool directional = !std::getenv("PTGPU_NO_DIRECTIONAL");
+  const unsigned int extra = directional ? 3 * inner_node_count() : 0;
+  directional_base_ = directional ? inner_node_count() : 0;
+  device_ = pick_device();
+  Check(ptgpu_create(tip_node_count_, inner_node_count() + extra, site_count_,
+                     static_cast<unsigned int>(model.category_rates.size()), branch_count(),
+                     inner_node_count() + extra, device_, &engine_));
+  try {
+    SetModel(model);
+    SetTipStates(tree, labels, sequences);
+  } catch (...) {
+    ptgpu_destroy(engine_);
+    engine_ = nullptr;
+    throw;
+  }
+  AllocateScratchBuffers();
+}
+
+// PTPLL/pll_partition.cpp:67-80: the engine moves, scratch is re-allocated
+Partition::Partition(Partition&& rhs) :
+    tip_node_count_(rhs.tip_node_count_),
+    map_mode_(rhs.map_mode_),
+    engine_(rhs.engine_),
+    model_(std::move(rhs.model_)),
+    site_count_(rhs.site_count_),
+    device_(rhs.device_),
+    directional_base_(rhs.directional_base_)
+{
+  rhs.engine_ = nullptr;
+  AllocateScratchBuffers();
+}
+
+Partition::~Partition()
+{
+  if (engine_) ptgpu_destroy(engine_);
+}
+
+void Partition::AllocateScratchBuffers()
+{
+  travbuffer_.resize(node_count());
+  branch_lengths_.resize(branch_count());
+  matrix_indices_.resize(branch_count());
+  operations_.resize(inner_node_count());
+}
+
+// PTPLL/pll_partition.cpp:87-108
+void Partition::SetModel(const Model& model)
+{
+  const char* name = canonical_model_name(model.model_name);
+  if (!name) throw std::invalid_argument("Invalid model name " + model.model_name);
+  if (model.frequencies.size() != STATES || model.subst_params.size() != STATES * (STATES - 1) / 2)
+    throw std::invalid_argument("Invalid number of frequencies or substitution rates");
+  // (the reference sets frequencies and rates before it checks the category
+  // count; the engine takes all three at once, so the check comes first)
+  if (model_.category_rates.size() && model.category_rates.size() != model_.category_rates.size())
+    throw std::invalid_argument("Invalid number of category rates");
+  Check(ptgpu_set_model(engine_, model.frequencies.data(), model.subst_params.data(),
+                        model.category_rates.data()));
+  model_ = model;
+  model_.model_name = name;
+}
+
+// PTPLL/pll_partition.cpp:110-151
+Model Partition::GetModel() const { return model_; }
+
+// PTPLL/pll_partition.cpp:153-194
+void Partition::SetTipStates(pll_utree_t* tree,
+                             const std::vector<std::string>& labels,
+                             const std::vector<std::string>& sequences)
+{
+  if (labels.size() != sequences.size())
+    throw std::invalid_argument("Number of labels does not match number of sequences");
+  if (tip_node_count_ != labels.size())
+    throw std::invalid_argument("Unexpected number of tip nodes supplied");
+
+  std::map<std::string, unsigned int> clv_of_label;
+  for (unsigned int i = 0; i < tip_node_count_; ++i) {
+    const pll_unode_t* tip = tree->nodes[i];
+    if (!clv_of_label.emplace(tip->label, tip->clv_index).second)
+      throw std::invalid_argument(std::string("Error inserting tip label ") + tip->label +
+                                  " into map (possibly a duplicate)");
+  }
+  for (unsigned int i = 0; i < tip_node_count_; ++i) {
+    auto it = clv_of_label.find(labels[i]);
+    if (it == clv_of_label.end())
+      throw std::invalid_argument("Sequence with header " + labels[i] +
+                                  " does not appear in the tree");
+    if (sequences[i].size() != site_count_)
+      throw std::invalid_argument("Sequence " + labels[i] + " has a different length");
+    Check(ptgpu_set_tip_states(engine_, it->second, sequences[i].c_str()));
+  }
+}
+
+// sum over all branches of log(lambda) - lambda*length in post-order, the edge
+// of `tree` counted once (PTPLL/pll_partition.cpp:317-343)
+double Partition::MapLogPrior(pll_unode_t* tree)
+{
+  std::vector<pll_unode_t*> nodes(node_count(), nullptr);
+  unsigned int found = 0;
+  if (!pll_utree_traverse(tree, PLL_TREE_TRAVERSE_POSTORDER, visit_all, nodes.data(), &found))
+    throw std::invalid_argument("LogLikelihood() requires an inner node");
+  if (found != nodes.size()) throw std::invalid_argument("Unexpected number of nodes");
+  double prior = 0.0;
+  for (pll_unode_t* n : nodes) {
+    if (n == tree->back) continue;
+    prior += std::log(kMapLambda) - (kMapLambda * n->length);
+  }
+  return prior;
+}
+
+// PTPLL/pll_partition.cpp:309-346
+double Partition::LogLikelihood(pll_unode_t* tree, double* per_site_lnl)
+{
+  double lnl = 0.0;
+  Check(ptgpu_compute_edge_loglikelihood(engine_, tree->clv_index, tree->scaler_index,
+                                         tree->back->clv_index, tree->back->scaler_index,
+                                         tree->pmatrix_index, per_site_lnl, &lnl));
+  if (map_mode_) {
+    // the reference adds the terms one by one to lnl, in this order
+    std::vector<pll_unode_t*> nodes(node_count(), nullptr);
+    unsigned int found = 0;
+    if (!pll_utree_traverse(tree, PLL_TREE_TRAVERSE_POSTORDER, visit_all, nodes.data(), &found))
+      throw std::invalid_argument("LogLikelihood() requires an inner node");
+    if (found != nodes.size()) throw std::invalid_argument("Unexpected number of nodes");
+    for (pll_unode_t* n : nodes) {
+      if (n == tree->back) continue;
+      lnl += std::log(kMapLambda) - (kMapLambda * n->length);
+    }
+  }
+  return lnl;
+}
+
+// The Laplace approximation lives in lesplace (GSL), outside the hot path
+// (--marginal is off in every BASELINE config).
+double Partition::LogMarginalLikelihood(pll_unode_t*)
+{
+  throw std::logic_error("LogMarginalLikelihood is not provided by the B200 engine build "
+                         "(lesplace/GSL path, out of scope)");
+}
+
+// PTPLL/pll_partition.cpp:348-393
+unsigned int Partition::TraversalUpdate(pll_unode_t* root, TraversalType type)
+{
+  unsigned int traversal_size = 0;
+  int ok;
+  if (type == TraversalType::FULL)
+    ok = pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, cb_full_traversal,
+                            travbuffer_.data(), &traversal_size);
+  else if (type == TraversalType::PARTIAL)
+    ok = pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, cb_partial_traversal,
+                            travbuffer_.data(), &traversal_size);
+  else
+    throw std::invalid_argument("Invalid traversal type");
+  if (!ok) throw std::invalid_argument("TraversalUpdate() requires an inner node");
+
+  unsigned int matrix_count = 0, ops_count = 0;
+  pll_utree_create_operations(travbuffer_.data(), traversal_size, branch_lengths_.data(),
+                              matrix_indices_.data(), operations_.data(), &matrix_count,
+                              &ops_count);
+  Check(ptgpu_update_prob_matrices(engine_, matrix_indices_.data(), branch_lengths_.data(),
+                                   matrix_count));
+  Check(ptgpu_update_partials(engine_,
+                              reinterpret_cast<const ptgpu_operation_t*>(operations_.data()),
+                              ops_count));
+  return ops_count;
+}
+
+// PTPLL/pll_partition.cpp:395-406
+void Partition::UpdateBranchLength(pll_unode_t* node, double length)
+{
+  node->length = length;
+  node->back->length = length;
+  Check(ptgpu_update_prob_matrices(engine_, &node->pmatrix_index, &node->length, 1));
+}
+
+// PTPLL/pll_partition.cpp:408-488.  The sumtable, the <= MAX_ITER Newton steps
+// with the reference's stopping rules and the final P-matrix update run as one
+// device-resident sequence; only the optimised length comes back.
+double Partition::OptimizeBranch(pll_unode_t* node)
+{
+  pll_unode_t* child = node->back;
+  double len = node->length;
+  Check(ptgpu_optimize_branch(engine_, node->clv_index, node->scaler_index, child->clv_index,
+                              child->scaler_index, node->pmatrix_index, node->length, MAX_ITER,
+                              EPSILON, map_mode_ ? kMapLambda : 0.0, &len, nullptr));
+  node->length = len;
+  node->back->length = len;
+  return len;
+}
+
+// PTPLL/pll_partition.cpp:490-540
+void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
+{
+  if (use_pllmod) {
+    TraversalUpdate(tree, TraversalType::PARTIAL);
+    LocalBranchOptimization(tree, 1e-8, 100.0, 1e-8, 1, -1);
+    TraversalUpdate(tree, TraversalType::PARTIAL);
+    return;
+  }
+
+  std::vector<pll_unode_t*> nodes(node_count(), nullptr);
+  unsigned int found = 0;
+  if (!pll_utree_traverse(tree, PLL_TREE_TRAVERSE_POSTORDER, visit_all, nodes.data(), &found))
+    throw std::invalid_argument("OptimizeAllBranches() requires an inner node");
+  if (found != nodes.size()) throw std::invalid_argument("Unexpected number of nodes");
+
+  for (pll_unode_t* node : nodes) {
+    if (!node->next) node = node->back;  // a tip's branch is optimised from its parent
+    TraversalUpdate(node, TraversalType::PARTIAL);
+    OptimizeBranch(node);
+  }
+}
+
+// PTPLL/pll_partition.cpp:542-582
+void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
+{
+  TraversalUpdate(tree, TraversalType::PARTIAL);
+
+  if (use_pllmod) {
+    LocalBranchOptimization(tree, 1e-8, 100.0, 1e-8, static_cast<int>(MAX_ITER), -1);
+    TraversalUpdate(tree, TraversalType::PARTIAL);
+    return;
+  }
+
+  double before = LogLikelihood(tree);
+  OptimizeAllBranchesOnce(tree);
+  TraversalUpdate(tree, TraversalType::PARTIAL);
+  double after = LogLikelihood(tree);
+
+  for (unsigned int i = 0; std::fabs(before - after) > EPSILON && i < MAX_ITER; ++i) {
+    before = after;
+    OptimizeAllBranchesOnce(tree);
+    TraversalUpdate(tree, TraversalType::PARTIAL);
+    after = LogLikelihood(tree);
+  }
+}
+
+// PTPLL/pll_partition.cpp:584-638
+void Partition::OptimizeBranchNeighborhood(pll_unode_t* node, int radius)
+{
+  if (radius <= 0) throw std::invalid_argument("optimization radius must be positive");
+  TraversalUpdate(node, TraversalType::PARTIAL);
+  // PLLMOD_OPT_MIN_BRANCH_LEN, PLLMOD_OPT_MAX_BRANCH_LEN (pll_optimize.h:60-61)
+  LocalBranchOptimization(node, 1.0e-4, 100.0, EPSILON, static_cast<int>(MAX_ITER), radius);
+}
+
+// One edge of pllmod's recomp_iterative (PLLMOD/optimize/pll_optimize.c:771-934,
+// keep_update = 1, built with NOCHECK_PERBRANCH_IMPR => 30 Newton iterations):
+// optimise the edge at `p` on the device, then, while the radius lasts, turn
+// the CLV of p's node towards each of the two other edges, recurse, and turn
+// it back.  false = the reference's PLL_FAILURE (derivative not finite or the
+// iteration limit hit); the edge keeps its length in that case.
+bool Partition::OptimizeEdgeBounded(pll_unode_t* p, double bl_min, double bl_max,
+                                    double tolerance, int radius)
+{
+  pll_unode_t* q = p->next;
+  pll_unode_t* z = q ? q->next : nullptr;
+
+  double guess = p->length;
+  if (guess < bl_min || guess > bl_max) guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
+
+  double len = guess;
+  int status = 0;
+  Check(ptgpu_optimize_branch_bounded(engine_, p->clv_index, p->scaler_index, p->back->clv_index,
+                                      p->back->scaler_index, guess, bl_min, bl_max, tolerance, 30,
+                                      &len, &status, nullptr));
+  if (status != 0) return false;
+
+  if (std::fabs(p->length - len) > 1e-10)
+    Check(ptgpu_update_prob_matrices(engine_, &p->pmatrix_index, &len, 1));
+  p->length = len;
+  p->back->length = len;
+
+  if (radius && q && z) {
+    auto reorient = [this](pll_unode_t* parent, pll_unode_t* c1, pll_unode_t* c2) {
+      ptgpu_operation_t op;
+      op.parent_clv_index = parent->clv_index;
+      op.parent_scaler_index = parent->scaler_index;
+      op.child1_clv_index = c1->back->clv_index;
+      op.child1_matrix_index = c1->back->pmatrix_index;
+      op.child1_scaler_index = c1->back->scaler_index;
+      op.child2_clv_index = c2->back->clv_index;
+      op.child2_matrix_index = c2->back->pmatrix_index;
+      op.child2_scaler_index = c2->back->scaler_index;
+      Check(ptgpu_update_partials(engine_, &op, 1));
+    };
+    reorient(q, p, z);
+    if (!OptimizeEdgeBounded(q->back, bl_min, bl_max, tolerance, radius - 1)) return false;
+    reorient(z, q, p);
+    if (!OptimizeEdgeBounded(z->back, bl_min, bl_max, tolerance, radius - 1)) return false;
+    reorient(p, z, q);
+  }
+  return true;
+}
+
+// pllmod_opt_optimize_branch_lengths_local (PLLMOD/optimize/pll_optimize.c:969-1091);
+// radius < 0 = the whole tree (pllmod_opt_optimize_branch_lengths_iterative, :1107-1130).
+// Returns what the reference returns: -lnL, or -0.0 after a failure.
+double Partition::LocalBranchOptimization(pll_unode_t* tree, double bl_min, double bl_max,
+                                          double tolerance, int smoothings, int radius)
+{
+  auto edge_lnl = [this, tree]() {
+    double v = 0.0;
+    Check(ptgpu_compute_edge_loglikelihood(engine_, tree->back->clv_index,
+                                           tree->back->scaler_index, tree->clv_index,
+                                           tree->scaler_index, tree->pmatrix_index, nullptr, &v));
+    return v;
+  };
+  double lnl = edge_lnl();
+
+  const double xmin = bl_min > 0 ? bl_min : 1.0e-4;
+  const double xmax = bl_max > 0 ? bl_max : 100.0;
+  const double xtol = bl_min > 0 ? bl_min / 10.0 : 1.0e-4;
+
+  unsigned int iters = static_cast<unsigned int>(smoothings);
+  while (iters) {
+    if (!OptimizeEdgeBounded(tree, xmin, xmax, xtol, radius) ||
+        !OptimizeEdgeBounded(tree->back, xmin, xmax, xtol, radius - 1)) {
+      lnl = 0.0;  // PLL_FAILURE
+      break;
+    }
+    const double now = edge_lnl();
+    if (!(now - lnl > now * 1e-14)) {
+      lnl = now;
+      break;
+    }
+    --iters;
+    if (std::fabs(now - lnl) < tolerance) iters = 0;
+    lnl = now;
+  }
+  return -1 * lnl;
+}
+
+// Model-parameter optimisation is pll-modules' Brent / L-BFGS-B machinery
+// driving libpll's CPU likelihood (out of scope;
+// --optimize-models is off in every BASELINE config).
+double Partition::OptimizeModelOnce(pll_unode_t*)
+{
+  throw std::logic_error("OptimizeModelOnce is not provided by the B200 engine build "
+                         "(pll-modules model optimisation, out of scope)");
+}
+
+double Partition::OptimizeModel(pll_unode_t*)
+{
+  throw std::logic_error("OptimizeModel is not provided by the B200 engine build "
+                         "(pll-modules model optimisation, out of scope)");
+}
+
+double Partition::OptimizeAllBranchesAndModel(pll_unode_t*, bool)
+{
+  throw std::logic_error("OptimizeAllBranchesAndModel is not provided by the B200 engine build "
+                         "(pll-modules model optimisation, out of scope)");
+}
+
+// ---------------------------------------------------------------------------
+// Batched NNI neighbourhood (the north-star path): all candidates of one
+// Wanderer::QueueMoves in one engine call.
+// ---------------------------------------------------------------------------
+std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree)
+{
+  if (!directional_base_)
+    throw std::logic_error("directional CLV buffers were disabled (PTGPU_NO_DIRECTIONAL)");
+  const unsigned int tips = tip_node_count_;
+  const unsigned int inner = inner_node_count();
+
+  // directional buffer of an inner-node record: the CLV of its node seen from
+  // record->back, kept for all three records of every inner node
+  auto dir_clv = [&](const pll_unode_t* r) -> unsigned int {
+    return r->next ? tips + directional_base_ + (r->node_index - tips) : r->clv_index;
+  };
+  auto dir_scaler = [&](const pll_unode_t* r) -> int {
+    return r->next ? static_cast<int>(directional_base_ + (r->node_index - tips)) : -1;
+  };
+
+  // all P matrices at the tree's current lengths
+  std::vector<unsigned int> midx;
+  std::vector<double> mlen;
+  std::vector<char> seen(branch_count(), 0);
+  for (unsigned int i = 0; i < tips + inner; ++i) {
+    pll_unode_t* n = tree->nodes[i];
+    pll_unode_t* ring[3] = {n, n->next, n->next ? n->next->next : nullptr};
+    for (pll_unode_t* r : ring) {
+      if (!r || r->pmatrix_index >= seen.size() || seen[r->pmatrix_index]) continue;
+      seen[r->pmatrix_index] = 1;
+      midx.push_back(r->pmatrix_index);
+      mlen.push_back(r->length);
+    }
+  }
+  Check(ptgpu_update_prob_matrices(engine_, midx.data(), mlen.data(),
+                                   static_cast<unsigned int>(midx.size())));
+
+  // one op per inner-node record, children before parents (iterative post-order)
+  std::vector<ptgpu_operation_t> plan;
+  plan.reserve(3 * inner);
+  std::vector<char> done(3 * inner, 0);
+  std::vector<std::pair<pll_unode_t*, bool>> stack;
+  auto schedule = [&](pll_unode_t* start) {
+    stack.emplace_back(start, false);
+    while (!stack.empty()) {
+      auto [r, expanded] = stack.back();
+      stack.pop_back();
+      if (!r->next || done[r->node_index - tips]) continue;
+      pll_unode_t* a = r->next->back;
+      pll_unode_t* b = r->next->next->back;
+      if (!expanded) {
+        stack.emplace_back(r, true);
+        stack.emplace_back(b, false);
+        stack.emplace_back(a, false);
+        continue;
+      }
+      done[r->node_index - tips] = 1;
+      ptgpu_operation_t op;
+      op.parent_clv_index = dir_clv(r);
+      op.parent_scaler_index = dir_scaler(r);
+      op.child1_clv_index = dir_clv(a);
+      op.child1_matrix_index = a->pmatrix_index;
+      op.child1_scaler_index = dir_scaler(a);
+      op.child2_clv_index = dir_clv(b);
+      op.child2_matrix_index = b->pmatrix_index;
+      op.child2_scaler_index = dir_scaler(b);
+      plan.push_back(op);
+    }
+  };
+  for (unsigned int i = tips; i < tips + inner; ++i) {
+    pll_unode_t* n = tree->nodes[i];
+    schedule(n);
+    schedule(n->next);
+    schedule(n->next->next);
+  }
+  Check(ptgpu_update_partials(engine_, plan.data(), static_cast<unsigned int>(plan.size())));
+
+  // candidates in QueueMoves order (src/wanderer.cpp:242-285); after
+  // pll_utree_nni(p, type) (LIBPLL/utree_moves.c:72-109) p's node joins
+  // (y, w) and q's node joins (x, z)
+  std::vector<NniScore> out;
+  std::vector<ptgpu_nni_candidate_t> cands;
+  auto child_of = [&](ptgpu_operation_t& op, int which, const pll_unode_t* c) {
+    if (which == 0) {
+      op.child1_clv_index = dir_clv(c);
+      op.child1_matrix_index = c->pmatrix_index;
+      op.child1_scaler_index = dir_scaler(c);
+    } else {
+      op.child2_clv_index = dir_clv(c);
+      op.child2_matrix_index = c->pmatrix_index;
+      op.child2_scaler_index = dir_scaler(c);
+    }
+  };
+  for (unsigned int i = tips; i < tips + inner; ++i) {
+    pll_unode_t* p = tree->nodes[i];
+    pll_unode_t* q = p->back;
+    if (!q->next) continue;
+    for (int type : {PLL_UTREE_MOVE_NNI_LEFT, PLL_UTREE_MOVE_NNI_RIGHT}) {
+      const pll_unode_t* x = p->next->back;
+      const pll_unode_t* w = p->next->next->back;
+      const pll_unode_t* y = type == PLL_UTREE_MOVE_NNI_LEFT ? q->next->back : q->next->next->back;
+      const pll_unode_t* z = type == PLL_UTREE_MOVE_NNI_LEFT ? q->next->next->back : q->next->back;
+      ptgpu_nni_candidate_t c;
+      std::memset(&c, 0, sizeof c);
+      c.p.parent_scaler_index = c.q.parent_scaler_index = -1;
+      child_of(c.p, 0, y);
+      child_of(c.p, 1, w);
+      child_of(c.q, 0, x);
+      child_of(c.q, 1, z);
+      c.length0 = p->length;
+      cands.push_back(c);
+      out.push_back(NniScore{p, type, p->length, 0.0});
+    }
+  }
+  if (cands.empty()) return out;
+
+  std::vector<double> len(cands.size()), lnl(cands.size());
+  std::vector<int> status(cands.size());
+  Check(ptgpu_score_nni_batch(engine_, cands.data(), static_cast<unsigned int>(cands.size()),
+                              MAX_ITER, EPSILON, map_mode_ ? kMapLambda : 0.0, len.data(),
+                              lnl.data(), status.data()));
+  double prior = 0.0;
+  if (map_mode_) prior = MapLogPrior(GetVirtualRoot(tree));
+  for (size_t i = 0; i < out.size(); ++i) {
+    if (status[i] != PTGPU_OK) throw std::range_error("d1 or d2 is not finite");
+    out[i].length = len[i];
+    out[i].lnl = lnl[i];
+    if (map_mode_)  // swap the central branch's prior term for the one at its new length
+      out[i].lnl += prior + kMapLambda * out[i].node->length - kMapLambda * len[i];
+  }
+  return out;
+}
+
+} } // namespace pt::pll
