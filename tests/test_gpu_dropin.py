@@ -1,0 +1,73 @@
+"""Drop-in tests on the GPU: the reference's UNMODIFIED pt sources and Catch test
+files, compiled against this repository's pt::pll::Partition (pt_b200/host) and
+linked with the CUDA engine (oracle/Makefile.gpu, built where /root/reference
+exists; the binaries travel to the GPU box).  These read like the reference's
+own tests because they ARE the reference's own tests."""
+import json
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GPU = os.path.join(ROOT, "oracle", "_ref", "gpu")
+
+
+def need(name):
+    p = os.path.join(GPU, name)
+    if not os.path.exists(p):
+        pytest.skip(f"{p} not built (oracle/Makefile.gpu needs /root/reference at build time)")
+    return p
+
+
+def test_reference_test_ptpll_on_gpu():
+    """lib/libptpll/test/test_ptpll.cpp: lnL KAT -33.387713, OptimizeBranch 2.607234,
+    OptimizeAllBranches vs RAxML lengths, OptimizeBranchNeighborhood radius 1/2 KATs,
+    ParseMultiNewick / SynchronizeTipIndices, model getter"""
+    exe = need("test_ptpll_gpu")
+    r = subprocess.run([exe, "[partition],[optimization],[util],[model_getter]"],
+                       cwd=os.path.join(GPU, "testdata", "ptpll"), capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+    assert re.search(r"All tests passed \((\d+) assertions in 4 test cases\)", r.stdout), r.stdout[-500:]
+
+
+def test_reference_test_ptw_on_gpu():
+    """test/test_ptw.cpp: every case.  The only assertion allowed to fail is the
+    --optimize-models section (pll-modules model optimisation: out of scope)."""
+    exe = need("test_ptw_gpu")
+    r = subprocess.run([exe], cwd=os.path.join(GPU, "testdata", "ptw"), capture_output=True,
+                       text=True, timeout=1500)
+    m = re.search(r"assertions:\s+(\d+) \|\s+(\d+) passed \|\s+(\d+) failed", r.stdout)
+    if m is None:
+        assert "All tests passed" in r.stdout, r.stdout[-3000:]
+        return
+    total, passed, failed = map(int, m.groups())
+    assert failed == 1 and passed >= 136, r.stdout[-3000:]
+    assert "OptimizeAllBranchesAndModel is not provided" in r.stdout
+    assert r.stdout.count("FAILED:") == 1
+
+
+@pytest.mark.parametrize("config", ["config1", "config2"])
+def test_ptw_threads_good_trees_identical(config):
+    """BASELINE configs[0] / configs[1] (on DS1): good_trees.tsv, visited and tested tables of
+    ptw_threads with the GPU-backed Partition are identical to the reference's (sorted lines:
+    6-significant-digit lnL + topology)."""
+    from make_ptw_golden import run, summarise
+    exe = need("ptw_threads_gpu")
+    with open(os.path.join(ROOT, "tests", "golden", "ptw_golden.json")) as f:
+        gold = json.load(f)[config]
+    got = summarise(run(exe, gold["args"]))
+    assert got["counts"] == gold["counts"]
+    assert got["good_topologies_sha"] == gold["good_topologies_sha"]
+    assert got["visited_topologies_sha"] == gold["visited_topologies_sha"]
+    assert got["tested_topologies_sha"] == gold["tested_topologies_sha"]
+    assert got["good"] == gold["good"]
+    assert got["visited_sha"] == gold["visited_sha"]
+    assert got["tested_sha"] == gold["tested_sha"]
