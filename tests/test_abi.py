@@ -60,3 +60,57 @@ def test_product_does_not_touch_the_oracle():
                 if re.search(r"pyoracle|pt_oracle|libpllref|oracle/", txt):
                     bad.append(fn)
     assert not bad, bad
+
+
+def test_gamma_rates_host_routine_matches_reference_golden():
+    """ptgpu_gamma_rates_mean replaces pll_compute_gamma_cats (host-only, no device needed):
+    bit-identical to the rates the reference computed for DS1 / five / newton"""
+    import numpy as np
+    from common import fha, golden
+    from pt_b200.engine import load_library
+    lib = load_library()
+    lib.ptgpu_gamma_rates_mean.argtypes = [ctypes.c_double, ctypes.c_uint,
+                                           ctypes.POINTER(ctypes.c_double)]
+    for name, alpha in (("ds1", 0.134946),):
+        g = golden(name)
+        out = np.empty(4)
+        rc = lib.ptgpu_gamma_rates_mean(alpha, 4, out.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
+        assert rc == 0
+        assert np.array_equal(out, fha(g["rates"]))
+    out = np.empty(1)
+    assert lib.ptgpu_gamma_rates_mean(0.5, 1, out.ctypes.data_as(ctypes.POINTER(ctypes.c_double))) == 0
+    assert out[0] == 1.0
+    assert lib.ptgpu_gamma_rates_mean(0.01, 4, out.ctypes.data_as(ctypes.POINTER(ctypes.c_double))) != 0
+
+
+def test_gamma_rates_against_oracle_grid(oracle):
+    import numpy as np
+    from pt_b200.engine import load_library
+    lib = load_library()
+    lib.ptgpu_gamma_rates_mean.argtypes = [ctypes.c_double, ctypes.c_uint,
+                                           ctypes.POINTER(ctypes.c_double)]
+    for alpha in (0.02, 0.05, 0.1299395, 0.3, 0.5, 1.0, 2.5, 10.0, 99.0):
+        for cats in (2, 4, 8):
+            out = np.empty(cats)
+            assert lib.ptgpu_gamma_rates_mean(alpha, cats, out.ctypes.data_as(
+                ctypes.POINTER(ctypes.c_double))) == 0
+            assert np.array_equal(out, oracle.gamma_rates_mean(alpha, cats)), (alpha, cats)
+
+
+def test_host_layer_mirrors_the_reference_surface():
+    """every public method of the reference's pt::pll::Partition is declared by the host layer"""
+    hdr = open(os.path.join(ROOT, "pt_b200", "host", "include", "pll_partition.hpp")).read()
+    for m in ("LogLikelihood(pll_unode_t* tree, double* per_site_lnl = nullptr)",
+              "LogMarginalLikelihood(pll_unode_t* root)",
+              "TraversalUpdate(pll_unode_t* root, TraversalType type)",
+              "UpdateBranchLength(pll_unode_t* node, double length)",
+              "OptimizeBranch(pll_unode_t* node)",
+              "OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod = false)",
+              "OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod = false)",
+              "OptimizeBranchNeighborhood(pll_unode_t* node, int radius)",
+              "OptimizeModelOnce(pll_unode_t* tree)", "OptimizeModel(pll_unode_t* tree)",
+              "OptimizeAllBranchesAndModel(pll_unode_t* tree, bool use_pllmod = false)",
+              "Model GetModel() const", "void SetModel(const Model& model)",
+              "tip_node_count() const", "inner_node_count() const", "node_count() const",
+              "branch_count() const", "const unsigned int MAX_ITER = 32", "const double EPSILON = 1e-6"):
+        assert m in hdr, m
