@@ -175,6 +175,25 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
                           double epsilon, double map_lambda, double *length_out,
                           double *lnl_out, int *status_out);
 
+/* ---- site shards: one engine per GPU holds a contiguous range
+   of the alignment's sites.  CLV updates, P matrices and sumtables are purely
+   local; every reduction over sites (edge lnL; d1/d2 of each Newton step; the
+   per-candidate lnL of a batch) is formed locally in a fixed order and then
+   summed over shards by the caller's hook before the scalar update -- the
+   scheme of pll-modules' parallel_reduce_cb
+   (PLLMOD/optimize/pll_optimize.c:1211-1212 lnL, :1249-1255 df/ddf).
+   The hook must sum `count` doubles at `device_buf` IN PLACE over all shards,
+   ordered on `cuda_stream` (e.g. ncclAllReduce(ncclDouble, ncclSum) on that
+   stream), and return 0.  All shards make the same sequence of calls. */
+typedef int (*ptgpu_allreduce_fn)(void *ctx, double *device_buf, size_t count,
+                                  void *cuda_stream);
+int ptgpu_set_allreduce(ptgpu_engine *e, ptgpu_allreduce_fn fn, void *ctx);
+/* where this engine's sites sit in the whole alignment (keeps the reference's
+   4-site vector / scalar tail split of the derivative loop at the GLOBAL
+   position, LIBPLL/core_derivatives_avx.c:1111-1156) */
+int ptgpu_set_shard(ptgpu_engine *e, unsigned long long site_offset,
+                    unsigned long long global_sites);
+
 /* test / debug hooks: host copies of device state */
 int ptgpu_get_clv(ptgpu_engine *e, unsigned int clv_index, double *out);
 int ptgpu_set_clv(ptgpu_engine *e, unsigned int clv_index, const double *in);

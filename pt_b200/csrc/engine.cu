@@ -93,6 +93,13 @@ struct ptgpu_engine
   Staging stg;
   int coop_blocks_per_sm = 0;
   int sm_count = 0;
+  // site-shard mode (ptgpu_set_allreduce / ptgpu_set_shard)
+  ptgpu_allreduce_fn allreduce = nullptr;
+  void *allreduce_ctx = nullptr;
+  unsigned long long vec_end = ~0ull;
+  double *d_red = nullptr;          // [2 * red_cap] per-branch sums handed to the hook
+  size_t red_cap = 0;
+  unsigned int *d_active = nullptr;
   unsigned long long counters[4] = {0, 0, 0, 0};
   // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
   bool profiling = false;
@@ -289,7 +296,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   if (e->stream) cudaStreamSynchronize(e->stream);
   cudaFree(e->d_tips); cudaFree(e->d_raw); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
   cudaFree(e->d_sumtable); cudaFree(e->d_persite); cudaFree(e->d_partials); cudaFree(e->d_counter);
-  cudaFree(e->d_state); cudaFree(e->d_idx1);
+  cudaFree(e->d_state); cudaFree(e->d_idx1); cudaFree(e->d_red); cudaFree(e->d_active);
   cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials);
   cudaFree(e->d_bcands); cudaFree(e->d_ops); cudaFree(e->d_midx); cudaFree(e->d_mlen);
   for (auto &p : e->pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
@@ -435,8 +442,59 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   return PTGPU_OK;
 }
 
+// sum `count` doubles at `buf` (device) over all shards through the caller's hook
+int shard_sum(ptgpu_engine *e, double *buf, size_t count)
+{
+  const int rc = e->allreduce(e->allreduce_ctx, buf, count, (void *)e->stream);
+  if (rc != 0) return fail(PTGPU_ERR_STATE, "allreduce hook failed with code %d", rc);
+  return PTGPU_OK;
+}
+
+// Newton over site shards: local sweep + fixed-order local reduction, the hook
+// sums the [2B] buffer over shards, every shard applies the same scalar update
+// (so all shards stay in lock step and leave the loop together).
+template <int C>
+int newton_split(ptgpu_engine *e, NewtonArgs &a)
+{
+  int rc;
+  if ((rc = ensure(&e->d_red, &e->red_cap, (size_t)a.B * 2))) return rc;
+  if (!e->d_active) CU(cudaMalloc(&e->d_active, sizeof(unsigned int)));
+  const unsigned int work = std::max(1u, a.B * a.nchunks);
+  const unsigned int grid = std::min(work, (unsigned int)e->sm_count * 8u);
+  unsigned int *active_h = (unsigned int *)(e->stg.host + 256);
+  for (unsigned int it = 0; it < a.max_iter; ++it)
+  {
+    {
+      LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
+      newton_sweep_kernel<C, false><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+    }
+    { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<2><<<a.B, 256, 0, e->stream>>>(a, e->d_red, 1); }
+    CU(cudaGetLastError());
+    if ((rc = shard_sum(e, e->d_red, (size_t)a.B * 2))) return rc;
+    CU(cudaMemsetAsync(e->d_active, 0, sizeof(unsigned int), e->stream));
+    { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_update_kernel<<<(a.B + 127) / 128, 128, 0, e->stream>>>(a, e->d_red, e->d_active); }
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(active_h, e->d_active, sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (*(volatile unsigned int *)active_h == 0) break;
+  }
+  if (!a.want_lnl) return PTGPU_OK;
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
+    newton_sweep_kernel<C, true><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+  }
+  { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<1><<<a.B, 256, 0, e->stream>>>(a, e->d_red, 0); }
+  CU(cudaGetLastError());
+  if ((rc = shard_sum(e, e->d_red, a.B))) return rc;
+  { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_store_lnl_kernel<<<(a.B + 127) / 128, 128, 0, e->stream>>>(a, e->d_red); }
+  CU(cudaGetLastError());
+  return PTGPU_OK;
+}
+
 int run_newton(ptgpu_engine *e, NewtonArgs &a)
 {
+  a.vec_end = e->vec_end;
+  if (e->allreduce) { DISPATCH_CATS(e, return newton_split<C>(e, a)); }
   DISPATCH_CATS(e, return launch_newton<C>(e, a));
   return PTGPU_OK;
 }
@@ -510,6 +568,11 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
     d_persite = e->d_persite;
   }
   double *result = (double *)e->stg.dev;
+  if (e->allreduce)
+  {
+    if ((rc = ensure(&e->d_red, &e->red_cap, 2))) return rc;
+    result = e->d_red;  // shard partial stays on the device for the hook
+  }
   {
     LaunchScope ls(e, PTGPU_KERNEL_EDGE_LNL);
     DISPATCH_CATS(e, (edge_lnl_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
@@ -520,6 +583,11 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
   if (persite_lnl)
     CU(cudaMemcpyAsync(persite_lnl, d_persite, (size_t)e->sites * sizeof(double),
                        cudaMemcpyDeviceToHost, e->stream));
+  if (e->allreduce)
+  {
+    if ((rc = shard_sum(e, e->d_red, 1))) return rc;
+    CU(cudaMemcpyAsync(e->stg.host, e->d_red, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  }
   CU(cudaStreamSynchronize(e->stream));
   *lnl_out = *(volatile double *)e->stg.host;
   return PTGPU_OK;
@@ -767,6 +835,27 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     }
     e->counters[3] += nb;
   }
+  return PTGPU_OK;
+}
+
+int ptgpu_set_allreduce(ptgpu_engine *e, ptgpu_allreduce_fn fn, void *ctx)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_set_allreduce: null engine");
+  e->allreduce = fn;
+  e->allreduce_ctx = ctx;
+  return PTGPU_OK;
+}
+
+int ptgpu_set_shard(ptgpu_engine *e, unsigned long long site_offset, unsigned long long global_sites)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_set_shard: null engine");
+  if (site_offset + e->sites > global_sites)
+    return fail(PTGPU_ERR_ARG, "ptgpu_set_shard: shard [%llu, %llu) exceeds %llu sites", site_offset,
+                site_offset + e->sites, global_sites);
+  // the reference's derivative loop treats the last global_sites % 4 sites
+  // differently (scalar tail, LIBPLL/core_derivatives_avx.c:1148-1156)
+  const unsigned long long gfull = global_sites / 4 * 4;
+  e->vec_end = gfull <= site_offset ? 0ull : gfull - site_offset;
   return PTGPU_OK;
 }
 

@@ -611,11 +611,14 @@ template <int C, bool WITH_LNL>
 __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *sumtable,
                                            const unsigned int *sclr, unsigned int sites,
                                            unsigned int tile, const double (&dg)[4][3],
-                                           double out[3])
+                                           double out[3], unsigned long long vec_end = ~0ull)
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
-  const unsigned int full = sites / 4 * 4;
+  // local index of the first site that the reference's scalar tail loop handles
+  // (a site shard passes where the GLOBAL sites/4*4 falls inside it)
+  const unsigned int full =
+      vec_end == ~0ull ? sites / 4 * 4 : (unsigned int)min((unsigned long long)sites, vec_end);
   constexpr int NQ = WITH_LNL ? 4 : 3;
   double ck[kPasses][NQ];
   {
@@ -680,6 +683,7 @@ struct NewtonArgs
   int want_lnl;
   int mode;                 // 0: Partition::OptimizeBranch, 1: pllmod_opt_minimize_newton
   double xmin, xmax;        // mode 1 bounds
+  unsigned long long vec_end; // ~0: unsharded; else local index where the global scalar tail starts
 };
 
 // One step of pllmod_opt_minimize_newton (PLLMOD/optimize/opt_algorithms.c:71-172)
@@ -729,6 +733,49 @@ __device__ __forceinline__ void bounded_newton_step(NewtonState &st, double f, d
   st.len = rts;
 }
 
+// The per-branch scalar step after one derivative evaluation: mode 0 is the
+// loop body of Partition::OptimizeBranch (PTPLL/pll_partition.cpp:433-481),
+// mode 1 one step of pllmod_opt_minimize_newton.
+__device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsigned int e, double a1,
+                                                     double a2)
+{
+  NewtonState st;
+  st.len = __ldcg(&a.st[e].len);
+  st.lnl = 0.0;
+  st.iters = __ldcg(&a.st[e].iters);
+  st.done = 0;
+  st.maybe_decreasing = __ldcg(&a.st[e].maybe_decreasing);
+  st.status = 0;
+  st.xl = __ldcg(&a.st[e].xl);
+  st.xh = __ldcg(&a.st[e].xh);
+  if (a.mode == 1)
+    bounded_newton_step(st, a1, a2, a);
+  else
+  {
+    double d1 = a1, d2 = a2;
+    if (a.lambda != 0.0) d1 = __dadd_rn(d1, a.lambda);
+    st.d1 = d1;
+    st.d2 = d2;
+    st.iters += 1;
+    if (!isfinite(d1)) { st.status = 1; st.done = 1; }
+    else if (!isfinite(d2)) { st.status = 2; st.done = 1; }
+    else if (fabs(d1) < a.eps) st.done = 1;
+    else
+    {
+      const double step = __ddiv_rn(d1, d2);
+      st.len = (d2 < 0.0) ? __dadd_rn(st.len, step) : __dadd_rn(st.len, -step);
+      if (st.len < 0.0)
+      {
+        st.len = a.eps;
+        if (st.maybe_decreasing) st.done = 1;
+        st.maybe_decreasing = 1;
+      }
+    }
+    if (st.iters >= (int)a.max_iter) st.done = 1;
+  }
+  a.st[e] = st;
+}
+
 // Persistent cooperative kernel: the whole Newton-Raphson loop of
 // Partition::OptimizeBranch (PTPLL/pll_partition.cpp:419-481) for B branches
 // at once.  Each iteration = one sweep of every still-running branch's
@@ -757,7 +804,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
       const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
       for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
         sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
-                             tile, dg, out);
+                             tile, dg, out, a.vec_end);
       const double s1 = block_sum<T>(out[0], red);
       const double s2 = block_sum<T>(out[1], red);
       if (threadIdx.x == 0)
@@ -780,41 +827,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
       a2 = block_sum<T>(a2, red);
       if (threadIdx.x == 0)
       {
-        NewtonState st;
-        st.len = __ldcg(&a.st[e].len);
-        st.lnl = 0.0;
-        st.iters = __ldcg(&a.st[e].iters);
-        st.done = 0;
-        st.maybe_decreasing = __ldcg(&a.st[e].maybe_decreasing);
-        st.status = 0;
-        st.xl = __ldcg(&a.st[e].xl);
-        st.xh = __ldcg(&a.st[e].xh);
-        if (a.mode == 1)
-          bounded_newton_step(st, a1, a2, a);
-        else
-        {
-          double d1 = a1, d2 = a2;
-          if (a.lambda != 0.0) d1 = __dadd_rn(d1, a.lambda);
-          st.d1 = d1;
-          st.d2 = d2;
-          st.iters += 1;
-          if (!isfinite(d1)) { st.status = 1; st.done = 1; }
-          else if (!isfinite(d2)) { st.status = 2; st.done = 1; }
-          else if (fabs(d1) < a.eps) st.done = 1;
-          else
-          {
-            const double step = __ddiv_rn(d1, d2);
-            st.len = (d2 < 0.0) ? __dadd_rn(st.len, step) : __dadd_rn(st.len, -step);
-            if (st.len < 0.0)
-            {
-              st.len = a.eps;
-              if (st.maybe_decreasing) st.done = 1;
-              st.maybe_decreasing = 1;
-            }
-          }
-          if (st.iters >= (int)a.max_iter) st.done = 1;
-        }
-        a.st[e] = st;
+        newton_scalar_update(a, e, a1, a2);
       }
     }
     grid.sync();
@@ -834,7 +847,8 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
     for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
       sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                          a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out);
+                          a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
+                          a.vec_end);
     const double sm = block_sum<T>(out[2], red);
     if (threadIdx.x == 0) a.partials[(size_t)w * 2] = sm;
   }
@@ -847,6 +861,95 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
     acc = block_sum<T>(acc, red);
     if (threadIdx.x == 0) a.st[e].lnl = acc;
   }
+}
+
+// ---- split-phase Newton for site shards -----------------------
+// The same three phases as the cooperative kernel, as separate launches so that
+// the caller's sum over shards (the allreduce hook, one [2B] or [B] buffer per
+// iteration) can run between the local reduction and the scalar update -- the
+// scheme of pll-modules' parallel_reduce_cb (PLLMOD/optimize/pll_optimize.c:1211-1255).
+template <int C, bool WITH_LNL>
+__global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonArgs a)
+{
+  constexpr int T = kSitesPerPass * C;
+  __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  const unsigned int nwork = a.B * a.nchunks;
+  const int cat = threadIdx.x % C;
+  for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
+  {
+    const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
+    if (!WITH_LNL && a.st[e].done) continue;
+    double dg[4][3];
+    diag_regs<C>(a.m, a.st[e].len, cat, dg);
+    double out[3] = {0.0, 0.0, 0.0};
+    const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
+    for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+      sweep_tile<C, WITH_LNL>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                              (WITH_LNL && a.sclr) ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
+                              tile, dg, out, a.vec_end);
+    if (WITH_LNL)
+    {
+      const double sm = block_sum<T>(out[2], red);
+      if (threadIdx.x == 0) a.partials[(size_t)w * 2] = sm;
+    }
+    else
+    {
+      const double s1 = block_sum<T>(out[0], red);
+      const double s2 = block_sum<T>(out[1], red);
+      if (threadIdx.x == 0)
+      {
+        a.partials[(size_t)w * 2 + 0] = s1;
+        a.partials[(size_t)w * 2 + 1] = s2;
+      }
+    }
+  }
+}
+
+// one CTA per branch: chunk partials -> shard[e*NV .. ] in fixed order (zeros for
+// branches that are done, so the cross-shard sum stays well defined)
+template <int NV>
+__global__ void __launch_bounds__(256) newton_reduce_kernel(NewtonArgs a, double *shard, int skip_done)
+{
+  __shared__ double red[8];
+  const unsigned int e = blockIdx.x;
+  const bool idle = skip_done && a.st[e].done;
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+  {
+    double acc = 0.0;
+    if (!idle)
+      for (unsigned int t = threadIdx.x; t < a.nchunks; t += 256)
+        acc = __dadd_rn(acc, a.partials[((size_t)e * a.nchunks + t) * 2 + v]);
+    acc = block_sum<256>(acc, red);
+    if (threadIdx.x == 0) shard[(size_t)e * NV + v] = acc;
+  }
+}
+
+// scalar updates from the (summed) shard buffer; *active receives the number of
+// branches still running
+__global__ void newton_update_kernel(NewtonArgs a, const double *shard, unsigned int *active)
+{
+  const unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= a.B) return;
+  if (!a.st[e].done) newton_scalar_update(a, e, shard[(size_t)e * 2], shard[(size_t)e * 2 + 1]);
+  if (!a.st[e].done) atomicAdd(active, 1u);
+}
+
+__global__ void newton_store_lnl_kernel(NewtonArgs a, const double *shard)
+{
+  const unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < a.B) a.st[e].lnl = shard[e];
+}
+
+// edge log-likelihood of a shard: tile partials -> one double in device memory
+__global__ void __launch_bounds__(256) sum_partials_kernel(const double *partials, unsigned int n,
+                                                           double *out)
+{
+  __shared__ double red[8];
+  double acc = 0.0;
+  for (unsigned int t = threadIdx.x; t < n; t += 256) acc = __dadd_rn(acc, partials[t]);
+  acc = block_sum<256>(acc, red);
+  if (threadIdx.x == 0) *out = acc;
 }
 
 // ------------------------------------------------- NNI candidate preparation

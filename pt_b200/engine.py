@@ -28,6 +28,9 @@ OP_DTYPE = np.dtype([
 CAND_DTYPE = np.dtype([("p", OP_DTYPE), ("q", OP_DTYPE), ("length0", np.float64)])
 assert OP_DTYPE.itemsize == 32 and CAND_DTYPE.itemsize == 72
 
+# ptgpu_allreduce_fn: int (*)(void *ctx, double *device_buf, size_t count, void *cuda_stream)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
+
 _dp = C.POINTER(C.c_double)
 _up = C.POINTER(C.c_uint)
 _lib = None
@@ -162,6 +165,16 @@ class Engine:
             C.c_double(map_lambda), C.byref(out), C.byref(it)))
         return out.value, it.value
 
+    def optimize_branch_bounded(self, pclv, pscaler, cclv, cscaler, guess, xmin=1e-4, xmax=100.0,
+                                tol=1e-5, max_iter=30):
+        """(length, status, iterations): pllmod's safeguarded Newton on one edge"""
+        out = C.c_double(); st = C.c_int(); it = C.c_int()
+        self._chk(self.lib.ptgpu_optimize_branch_bounded(
+            self.h, C.c_uint(pclv), C.c_int(pscaler), C.c_uint(cclv), C.c_int(cscaler),
+            C.c_double(guess), C.c_double(xmin), C.c_double(xmax), C.c_double(tol),
+            C.c_uint(max_iter), C.byref(out), C.byref(st), C.byref(it)))
+        return out.value, st.value, it.value
+
     def score_nni_batch(self, cands, max_iter=32, eps=1e-6, map_lambda=0.0):
         c = np.ascontiguousarray(cands, dtype=CAND_DTYPE)
         n = len(c)
@@ -210,6 +223,17 @@ class Engine:
 
     def stream(self):
         return self.lib.ptgpu_stream(self.h)
+
+    # --- site shards ----------------------------------------------------------
+    def set_shard(self, site_offset, global_sites):
+        self._chk(self.lib.ptgpu_set_shard(self.h, C.c_ulonglong(site_offset),
+                                           C.c_ulonglong(global_sites)))
+
+    def set_allreduce(self, fn):
+        """fn: ALLREDUCE_FN instance (kept alive by the caller) or None"""
+        self._hook = fn
+        self._chk(self.lib.ptgpu_set_allreduce(
+            self.h, C.cast(fn, C.c_void_p) if fn is not None else None, None))
 
     def synchronize(self):
         self._chk(self.lib.ptgpu_synchronize(self.h))
