@@ -63,15 +63,21 @@ class ClockSampler(threading.Thread):
             line = p.stdout.readline()
             if not line:
                 break
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append([time.time()] + [x.strip() for x in line.split(",")])
         p.terminate()
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """summary of the samples taken inside [t0, t1] (the timed region); the sampler itself
+        is started before the warm-up so that nvidia-smi's start-up (NVML attach can stall the
+        driver for tens of ms) never falls inside the timed region"""
         self._stop_evt.set()
-        sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
+        rows = [r[1:] for r in self.rows if t0 is None or t0 <= r[0] <= t1]
+        if not rows:
+            rows = [r[1:] for r in self.rows]
+        sm = [float(r[1]) for r in rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
         reasons = set()
-        for r in self.rows:
+        for r in rows:
             if len(r) > 8:
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
                                     "sw_power_cap"), r[5:9]):
@@ -223,6 +229,9 @@ def run_ours(args):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    sampler = ClockSampler(local)   # started long before the timed region (see stop())
+    if rank == 0:
+        sampler.start()
     n, S = args.taxa, args.sites
     base = parent_tree(n, 0)
     aln = simulate(base, S, np.random.default_rng(SEED_ALN))
@@ -264,12 +273,10 @@ def run_ours(args):
     e.set_profiling(True)
     e.kernel_times(reset=True)
     c0 = e.counters()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     if dist:
         dist.barrier()
     torch.cuda.synchronize()
+    wall0 = time.time()
     ev0.record(stream)
     for _ in range(args.steps):
         step()
@@ -294,7 +301,7 @@ def run_ours(args):
         torch.cuda.synchronize()
         if i:
             t_e2e.append(time.perf_counter() - t0)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
     e2e_s = sum(t_e2e)
 
     if dist:

@@ -13,6 +13,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -101,6 +102,7 @@ struct ptgpu_engine
   size_t red_cap = 0;
   unsigned int *d_active = nullptr;
   unsigned long long counters[4] = {0, 0, 0, 0};
+  unsigned long long lnl_sweeps = 0, final_sweeps = 0;
   // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
   bool profiling = false;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> pending;
@@ -192,7 +194,10 @@ int check_op(const ptgpu_engine *e, const ptgpu_operation_t &op, bool need_paren
 template <int C>
 int coop_occupancy(int *out)
 {
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, newton_kernel<C>, kSitesPerPass * C, 0));
+  int a = 0, b = 0;
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, newton_kernel<C, false>, kSitesPerPass * C, 0));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, newton_kernel<C, true>, kSitesPerPass * C, 0));
+  *out = std::min(a, b);
   return PTGPU_OK;
 }
 
@@ -247,7 +252,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   CU_NEW(cudaMalloc(&e->dev.pmat, (size_t)prob_matrices * rate_cats * 16 * sizeof(double)));
   CU_NEW(cudaMemsetAsync(e->dev.pmat, 0, (size_t)prob_matrices * rate_cats * 16 * sizeof(double), e->stream));
   CU_NEW(cudaMalloc(&e->d_sumtable, clv_stride * sizeof(double)));
-  CU_NEW(cudaMalloc(&e->d_partials, (size_t)e->ntiles * 2 * sizeof(double)));
+  CU_NEW(cudaMalloc(&e->d_partials, (size_t)e->ntiles * 3 * sizeof(double)));
   CU_NEW(cudaMalloc(&e->d_counter, sizeof(unsigned int)));
   CU_NEW(cudaMemsetAsync(e->d_counter, 0, sizeof(unsigned int), e->stream));
   CU_NEW(cudaMalloc(&e->d_state, sizeof(NewtonState)));
@@ -436,8 +441,8 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   void *params[] = {&a};
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-    CU(cudaLaunchCooperativeKernel((void *)newton_kernel<C>, dim3(grid), dim3(kSitesPerPass * C),
-                                   params, 0, e->stream));
+    void *fn = a.want_lnl ? (void *)newton_kernel<C, true> : (void *)newton_kernel<C, false>;
+    CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kSitesPerPass * C), params, 0, e->stream));
   }
   return PTGPU_OK;
 }
@@ -457,35 +462,41 @@ template <int C>
 int newton_split(ptgpu_engine *e, NewtonArgs &a)
 {
   int rc;
-  if ((rc = ensure(&e->d_red, &e->red_cap, (size_t)a.B * 2))) return rc;
-  if (!e->d_active) CU(cudaMalloc(&e->d_active, sizeof(unsigned int)));
+  if ((rc = ensure(&e->d_red, &e->red_cap, (size_t)a.B * 3))) return rc;
+  if (!e->d_active) CU(cudaMalloc(&e->d_active, 2 * sizeof(unsigned int)));
   const unsigned int work = std::max(1u, a.B * a.nchunks);
   const unsigned int grid = std::min(work, (unsigned int)e->sm_count * 8u);
-  unsigned int *active_h = (unsigned int *)(e->stg.host + 256);
+  volatile unsigned int *active_h = (volatile unsigned int *)(e->stg.host + 256);
+  unsigned int pending_lnl = 0;
   for (unsigned int it = 0; it < a.max_iter; ++it)
   {
     {
       LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-      newton_sweep_kernel<C, false><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+      if (a.want_lnl) newton_sweep_kernel<C, true, false><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+      else newton_sweep_kernel<C, false, false><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
     }
-    { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<2><<<a.B, 256, 0, e->stream>>>(a, e->d_red, 1); }
+    { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<false><<<a.B, 256, 0, e->stream>>>(a, e->d_red); }
     CU(cudaGetLastError());
-    if ((rc = shard_sum(e, e->d_red, (size_t)a.B * 2))) return rc;
-    CU(cudaMemsetAsync(e->d_active, 0, sizeof(unsigned int), e->stream));
+    if ((rc = shard_sum(e, e->d_red, (size_t)a.B * 3))) return rc;
+    CU(cudaMemsetAsync(e->d_active, 0, 2 * sizeof(unsigned int), e->stream));
     { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_update_kernel<<<(a.B + 127) / 128, 128, 0, e->stream>>>(a, e->d_red, e->d_active); }
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(active_h, e->d_active, sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync((void *)active_h, e->d_active, 2 * sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
-    if (*(volatile unsigned int *)active_h == 0) break;
+    pending_lnl = active_h[1];
+    if (active_h[0] == 0) break;
   }
   if (!a.want_lnl) return PTGPU_OK;
+  // every shard sees the same flags (same sums, same updates), so all of them
+  // take the same branch here
+  if (!pending_lnl) return PTGPU_OK;
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-    newton_sweep_kernel<C, true><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+    newton_sweep_kernel<C, true, true><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
   }
-  { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<1><<<a.B, 256, 0, e->stream>>>(a, e->d_red, 0); }
+  { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<true><<<a.B, 256, 0, e->stream>>>(a, e->d_red); }
   CU(cudaGetLastError());
-  if ((rc = shard_sum(e, e->d_red, a.B))) return rc;
+  if ((rc = shard_sum(e, e->d_red, (size_t)a.B * 3))) return rc;
   { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_store_lnl_kernel<<<(a.B + 127) / 128, 128, 0, e->stream>>>(a, e->d_red); }
   CU(cudaGetLastError());
   return PTGPU_OK;
@@ -732,7 +743,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
   size_t free_b = 0, total_b = 0;
   CU(cudaMemGetInfo(&free_b, &total_b));
   const size_t per_cand = stride * sizeof(double) + (size_t)e->sites * sizeof(unsigned int) +
-                          (size_t)e->ntiles * 2 * sizeof(double) + sizeof(NewtonState) + sizeof(DevGroup);
+                          (size_t)e->ntiles * 3 * sizeof(double) + sizeof(NewtonState) + sizeof(DevGroup);
   size_t have = e->bcap * per_cand;
   size_t budget = std::max(have, (size_t)((free_b + have) * 0.8));
   size_t chunk = std::min<size_t>(count, std::max<size_t>(1, budget / per_cand));
@@ -744,7 +755,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     CU(cudaMalloc(&e->d_bsum, chunk * stride * sizeof(double)));
     CU(cudaMalloc(&e->d_bsclr, chunk * (size_t)e->sites * sizeof(unsigned int)));
     CU(cudaMalloc(&e->d_bstate, chunk * sizeof(NewtonState)));
-    CU(cudaMalloc(&e->d_bpartials, chunk * (size_t)e->ntiles * 2 * sizeof(double)));
+    CU(cudaMalloc(&e->d_bpartials, chunk * (size_t)e->ntiles * 3 * sizeof(double)));
     CU(cudaMalloc(&e->d_bcands, chunk * sizeof(DevGroup)));
     e->bcap = chunk;
   }
@@ -832,7 +843,12 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
       lnl_out[base + i] = hst[i].lnl;
       if (status_out) status_out[base + i] = hst[i].status ? PTGPU_ERR_NOT_FINITE : PTGPU_OK;
       e->counters[2] += (unsigned long long)hst[i].iters;
+      e->lnl_sweeps += (unsigned long long)hst[i].lnl_sweeps;
+      e->final_sweeps += (unsigned long long)hst[i].final_sweeps;
     }
+    if (getenv("PTGPU_DEBUG"))
+      fprintf(stderr, "[ptgpu] batch of %u: %llu lnL-carrying sweeps, %llu extra final sweeps so far\n", nb,
+              e->lnl_sweeps, e->final_sweeps);
     e->counters[3] += nb;
   }
   return PTGPU_OK;

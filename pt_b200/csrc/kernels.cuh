@@ -109,6 +109,10 @@ struct NewtonState
   int status;           // mode 0: 0 ok, 1 d1 not finite, 2 d2 not finite
                         // mode 1: 0 ok, 1 derivative not finite, 2 iteration limit
   double xl, xh;        // mode 1: current bracket
+  int lnl_valid;        // lnl holds the log-likelihood at `len` (the last sweep was at the final length)
+  int try_lnl;          // the next sweep should also sum site log-likelihoods (it is probably the last)
+  int lnl_sweeps;       // statistics: sweeps that carried the lnL sums / extra final sweeps
+  int final_sweeps;
 };
 
 // ---------------------------------------------------------------- helpers
@@ -349,8 +353,14 @@ __device__ __forceinline__ void load_matrix(const double *pm, double m[16])
   for (int i = 0; i < 4; ++i) ld256_nc(pm + 4 * i, m + 4 * i);
 }
 
+#ifndef PT_PART_MINB
+#define PT_PART_MINB 1
+#endif
+#ifndef PT_PREP_MINB
+#define PT_PREP_MINB 1
+#endif
 template <int C>
-__global__ void __launch_bounds__(kHeavySites *C)
+__global__ void __launch_bounds__(kHeavySites *C, PT_PART_MINB)
     partials_kernel(DevState s, const DevOp *__restrict__ ops, unsigned int nops)
 {
   const int cat = threadIdx.x % C;
@@ -573,11 +583,38 @@ __device__ __forceinline__ void quad_transpose_sum(const double (&v)[4][NQ], int
   }
 }
 
+// Sum of per-site log-likelihoods as the log of a running product: every site
+// contributes its mantissa to `prod` (one DMUL) and its binary exponent to
+// `esum` (integer), and the scaler count enters as -256 per rescaling; one log
+// per thread and chunk replaces one log per site.  log(prod) + esum ln 2 equals
+// sum_i [log(terma_i) + sc_i log(2^-256)] up to rounding (the product carries
+// ~n ulp of relative error, i.e. ~n 1e-16 ABSOLUTE error in the log).
+struct LnlProd
+{
+  double prod = 1.0;
+  int esum = 0;
+  bool zero = false;   // a site with likelihood 0: the sum is -inf, as the reference's log(0)
+  __device__ __forceinline__ void add(double terma, unsigned int sc)
+  {
+    if (!(terma > 0.0)) { zero = zero || terma == 0.0; if (terma != 0.0) prod = terma; return; }  // NaN propagates
+    if (terma < 2.2250738585072014e-308) { terma = __dmul_rn(terma, 1.2676506002282294e30); esum -= 100; }  // denormal: x 2^100
+    const int hi = __double2hiint(terma), lo = __double2loint(terma);
+    esum += ((hi >> 20) & 0x7ff) - 1022 - 256 * (int)sc;
+    prod = __dmul_rn(prod, __hiloint2double((hi & 0x800fffff) | 0x3fe00000, lo));  // mantissa in [0.5, 1)
+    if (prod < 3.0549363634996047e-151) { prod = __dmul_rn(prod, 3.2733906078961419e150); esum -= 500; }  // x 2^500
+  }
+  __device__ __forceinline__ double value() const
+  {
+    if (zero) return -INFINITY;
+    return __dadd_rn(log(prod), __dmul_rn((double)esum, 0.69314718055994530942));
+  }
+};
+
 // per-site epilogue shared by both reduction layouts
 template <bool WITH_LNL>
 __device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[3], double terma,
                                            unsigned int site, unsigned int full,
-                                           const unsigned int *sclr, double out[3])
+                                           const unsigned int *sclr, double out[3], LnlProd &lp)
 {
   // LIBPLL/core_derivatives_avx.c:1111-1156: sites below `full` (= sites/4*4) use
   // the reciprocal form of the 4-site vector step, the tail true divisions
@@ -596,13 +633,7 @@ __device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[
     out[0] = __dadd_rn(out[0], a);
     out[1] = __dadd_rn(out[1], b);
   }
-  if (WITH_LNL)
-  {
-    double l = log(terma);
-    const unsigned int sc = sclr ? sclr[site] : 0u;
-    if (sc) l = __dadd_rn(l, __dmul_rn((double)sc, m.log_scale_thr));
-    out[2] = __dadd_rn(out[2], l);
-  }
+  if (WITH_LNL) lp.add(terma, sclr ? sclr[site] : 0u);
 }
 
 // One tile of the site sweep.  out[0] += -L'/L terms, out[1] += second
@@ -611,7 +642,8 @@ template <int C, bool WITH_LNL>
 __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *sumtable,
                                            const unsigned int *sclr, unsigned int sites,
                                            unsigned int tile, const double (&dg)[4][3],
-                                           double out[3], unsigned long long vec_end = ~0ull)
+                                           double out[3], LnlProd &lp,
+                                           unsigned long long vec_end = ~0ull)
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
@@ -649,7 +681,7 @@ __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *su
     double r[NQ];
     quad_transpose_sum<NQ>(ck, cat, r);
     const unsigned int site = site0 + quad_pass(cat) * kSitesPerPass;
-    if (site < sites) site_terms<WITH_LNL>(m, r, r[NQ - 1], site, full, sclr, out);
+    if (site < sites) site_terms<WITH_LNL>(m, r, r[NQ - 1], site, full, sclr, out, lp);
   }
   else
   {
@@ -665,7 +697,7 @@ __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *su
 #pragma unroll
         for (int q = 0; q < NQ; ++q)
           lk[q] = __dadd_rn(lk[q], __shfl_down_sync(0xffffffffu, ck[ps][q], k, C));
-      if (cat == 0 && site < sites) site_terms<WITH_LNL>(m, lk, lk[NQ - 1], site, full, sclr, out);
+      if (cat == 0 && site < sites) site_terms<WITH_LNL>(m, lk, lk[NQ - 1], site, full, sclr, out, lp);
     }
   }
 }
@@ -677,7 +709,7 @@ struct NewtonArgs
   size_t entry_stride;      // doubles between consecutive entries' sumtables
   const unsigned int *sclr; // [B][sites] summed scaler counts, or null (=> 0)
   NewtonState *st;          // [B]
-  double *partials;         // [B][nchunks][2]
+  double *partials;         // [B][nchunks][3]: d1, d2 and (if want_lnl) lnL sums per chunk
   unsigned int sites, B, ntiles, chunk_tiles, nchunks, max_iter;
   double eps, lambda;
   int want_lnl;
@@ -737,11 +769,17 @@ __device__ __forceinline__ void bounded_newton_step(NewtonState &st, double f, d
 // loop body of Partition::OptimizeBranch (PTPLL/pll_partition.cpp:433-481),
 // mode 1 one step of pllmod_opt_minimize_newton.
 __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsigned int e, double a1,
-                                                     double a2)
+                                                     double a2, double a3 = 0.0)
 {
   NewtonState st;
   st.len = __ldcg(&a.st[e].len);
+  const double evaluated_at = st.len;
   st.lnl = 0.0;
+  st.lnl_valid = 0;
+  const int had_lnl = __ldcg(&a.st[e].try_lnl);
+  st.try_lnl = 0;
+  st.lnl_sweeps = __ldcg(&a.st[e].lnl_sweeps) + (had_lnl ? 1 : 0);
+  st.final_sweeps = 0;
   st.iters = __ldcg(&a.st[e].iters);
   st.done = 0;
   st.maybe_decreasing = __ldcg(&a.st[e].maybe_decreasing);
@@ -764,14 +802,34 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
     {
       const double step = __ddiv_rn(d1, d2);
       st.len = (d2 < 0.0) ? __dadd_rn(st.len, step) : __dadd_rn(st.len, -step);
+      // Will the next evaluation be the last?  Newton converges quadratically,
+      // |d1(k+1)| ~ c |d1(k)|^2 with c estimated from the last two evaluations;
+      // if that prediction is within 100x of the stopping threshold the next
+      // sweep also sums the site log-likelihoods (a wrong guess costs either
+      // one cheap extra log pass or one extra sweep at the end, never accuracy).
+      {
+        const double prev = __ldcg(&a.st[e].d1);
+        const double pred = (st.iters > 1 && prev != 0.0)
+                                ? fabs(d1) * (fabs(d1) / fabs(prev)) * (fabs(d1) / fabs(prev))
+                                : fabs(d1);
+        st.try_lnl = pred < 100.0 * a.eps;
+      }
       if (st.len < 0.0)
       {
         st.len = a.eps;
         if (st.maybe_decreasing) st.done = 1;
         st.maybe_decreasing = 1;
+        st.try_lnl = 1;
       }
     }
     if (st.iters >= (int)a.max_iter) st.done = 1;
+  }
+  // the sweep that produced (a1, a2) also summed the site log-likelihoods at the
+  // length it ran at; if that is where the branch ends up, the score is known
+  if (a.want_lnl && had_lnl && st.done && st.len == evaluated_at)
+  {
+    st.lnl = a3;
+    st.lnl_valid = 1;
   }
   a.st[e] = st;
 }
@@ -783,7 +841,7 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
 // fixed-order reduction + the scalar update done by one CTA per branch, a grid
 // barrier.  Reduction units (chunks) depend only on the site count, so results
 // are independent of the grid size.
-template <int C>
+template <int C, bool LNL>
 __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
@@ -801,34 +859,43 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
       double dg[4][3];
       diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
       double out[3] = {0.0, 0.0, 0.0};
+      LnlProd lp;
       const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-        sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
-                             tile, dg, out, a.vec_end);
+      const bool with_lnl = LNL && __ldcg(&a.st[e].try_lnl);
+      if (with_lnl)
+        for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+          sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                              a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
+                              lp, a.vec_end);
+      else
+        for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+          sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites, tile,
+                               dg, out, lp, a.vec_end);
       const double s1 = block_sum<T>(out[0], red);
       const double s2 = block_sum<T>(out[1], red);
+      const double s3 = LNL ? block_sum<T>(with_lnl ? lp.value() : 0.0, red) : 0.0;
       if (threadIdx.x == 0)
       {
-        a.partials[(size_t)w * 2 + 0] = s1;
-        a.partials[(size_t)w * 2 + 1] = s2;
+        a.partials[(size_t)w * 3 + 0] = s1;
+        a.partials[(size_t)w * 3 + 1] = s2;
+        if (LNL) a.partials[(size_t)w * 3 + 2] = s3;
       }
     }
     grid.sync();
     for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
     {
       if (__ldcg(&a.st[e].done)) continue;
-      double a1 = 0.0, a2 = 0.0;
+      double a1 = 0.0, a2 = 0.0, a3 = 0.0;
       for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
       {
-        a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 2 + 0));
-        a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 2 + 1));
+        a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 0));
+        a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 1));
+        if (LNL) a3 = __dadd_rn(a3, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 2));
       }
       a1 = block_sum<T>(a1, red);
       a2 = block_sum<T>(a2, red);
-      if (threadIdx.x == 0)
-      {
-        newton_scalar_update(a, e, a1, a2);
-      }
+      if (LNL) a3 = block_sum<T>(a3, red);
+      if (threadIdx.x == 0) newton_scalar_update(a, e, a1, a2, a3);
     }
     grid.sync();
     int active = 0;
@@ -836,30 +903,37 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
     if (!__syncthreads_or(active)) break;
   }
 
-  if (!a.want_lnl) return;
-  // log-likelihood at the final length, from the same sumtable
+  if (!LNL) return;
+  // branches that stopped somewhere else than at the last evaluated length
+  // (second negative step, iteration limit): one more sweep at the final length
+  int pending = 0;
+  for (unsigned int e = threadIdx.x; e < a.B; e += T) pending |= !__ldcg(&a.st[e].lnl_valid);
+  if (!__syncthreads_or(pending)) return;   // uniform over the grid: every CTA reads the same flags
   for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
   {
     const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
+    if (__ldcg(&a.st[e].lnl_valid)) continue;
     double dg[4][3];
     diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
     double out[3] = {0.0, 0.0, 0.0};
+    LnlProd lp;
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
     for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
       sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                           a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
-                          a.vec_end);
-    const double sm = block_sum<T>(out[2], red);
-    if (threadIdx.x == 0) a.partials[(size_t)w * 2] = sm;
+                          lp, a.vec_end);
+    const double sm = block_sum<T>(lp.value(), red);
+    if (threadIdx.x == 0) a.partials[(size_t)w * 3 + 2] = sm;
   }
   grid.sync();
   for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
   {
+    if (__ldcg(&a.st[e].lnl_valid)) continue;
     double acc = 0.0;
     for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
-      acc = __dadd_rn(acc, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 2));
+      acc = __dadd_rn(acc, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 2));
     acc = block_sum<T>(acc, red);
-    if (threadIdx.x == 0) a.st[e].lnl = acc;
+    if (threadIdx.x == 0) { a.st[e].lnl = acc; a.st[e].lnl_valid = 1; a.st[e].final_sweeps = 1; }
   }
 }
 
@@ -868,7 +942,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
 // the caller's sum over shards (the allreduce hook, one [2B] or [B] buffer per
 // iteration) can run between the local reduction and the scalar update -- the
 // scheme of pll-modules' parallel_reduce_cb (PLLMOD/optimize/pll_optimize.c:1211-1255).
-template <int C, bool WITH_LNL>
+template <int C, bool LNL, bool FINAL>
 __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
@@ -878,67 +952,74 @@ __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonAr
   for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
   {
     const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
-    if (!WITH_LNL && a.st[e].done) continue;
+    if (FINAL ? a.st[e].lnl_valid : a.st[e].done) continue;
     double dg[4][3];
     diag_regs<C>(a.m, a.st[e].len, cat, dg);
     double out[3] = {0.0, 0.0, 0.0};
+    LnlProd lp;
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-    for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-      sweep_tile<C, WITH_LNL>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                              (WITH_LNL && a.sclr) ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
-                              tile, dg, out, a.vec_end);
-    if (WITH_LNL)
-    {
-      const double sm = block_sum<T>(out[2], red);
-      if (threadIdx.x == 0) a.partials[(size_t)w * 2] = sm;
-    }
+    const bool with_lnl = LNL && (FINAL || a.st[e].try_lnl);
+    if (with_lnl)
+      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+        sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                            a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
+                            lp, a.vec_end);
     else
+      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+        sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites, tile,
+                             dg, out, lp, a.vec_end);
+    const double s1 = block_sum<T>(out[0], red);
+    const double s2 = block_sum<T>(out[1], red);
+    const double s3 = LNL ? block_sum<T>(with_lnl ? lp.value() : 0.0, red) : 0.0;
+    if (threadIdx.x == 0)
     {
-      const double s1 = block_sum<T>(out[0], red);
-      const double s2 = block_sum<T>(out[1], red);
-      if (threadIdx.x == 0)
-      {
-        a.partials[(size_t)w * 2 + 0] = s1;
-        a.partials[(size_t)w * 2 + 1] = s2;
-      }
+      a.partials[(size_t)w * 3 + 0] = s1;
+      a.partials[(size_t)w * 3 + 1] = s2;
+      a.partials[(size_t)w * 3 + 2] = s3;
     }
   }
 }
 
-// one CTA per branch: chunk partials -> shard[e*NV .. ] in fixed order (zeros for
-// branches that are done, so the cross-shard sum stays well defined)
-template <int NV>
-__global__ void __launch_bounds__(256) newton_reduce_kernel(NewtonArgs a, double *shard, int skip_done)
+// one CTA per branch: chunk partials -> shard[e*3 .. e*3+2] in fixed order (zeros
+// for idle branches, so the cross-shard sum stays well defined)
+template <bool FINAL>
+__global__ void __launch_bounds__(256) newton_reduce_kernel(NewtonArgs a, double *shard)
 {
   __shared__ double red[8];
   const unsigned int e = blockIdx.x;
-  const bool idle = skip_done && a.st[e].done;
+  const bool idle = FINAL ? a.st[e].lnl_valid : a.st[e].done;
 #pragma unroll
-  for (int v = 0; v < NV; ++v)
+  for (int v = 0; v < 3; ++v)
   {
     double acc = 0.0;
     if (!idle)
       for (unsigned int t = threadIdx.x; t < a.nchunks; t += 256)
-        acc = __dadd_rn(acc, a.partials[((size_t)e * a.nchunks + t) * 2 + v]);
+        acc = __dadd_rn(acc, a.partials[((size_t)e * a.nchunks + t) * 3 + v]);
     acc = block_sum<256>(acc, red);
-    if (threadIdx.x == 0) shard[(size_t)e * NV + v] = acc;
+    if (threadIdx.x == 0) shard[(size_t)e * 3 + v] = acc;
   }
 }
 
 // scalar updates from the (summed) shard buffer; *active receives the number of
-// branches still running
+// branches still running, active[1] the number still lacking their final lnL
 __global__ void newton_update_kernel(NewtonArgs a, const double *shard, unsigned int *active)
 {
   const unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= a.B) return;
-  if (!a.st[e].done) newton_scalar_update(a, e, shard[(size_t)e * 2], shard[(size_t)e * 2 + 1]);
+  if (!a.st[e].done)
+    newton_scalar_update(a, e, shard[(size_t)e * 3], shard[(size_t)e * 3 + 1], shard[(size_t)e * 3 + 2]);
   if (!a.st[e].done) atomicAdd(active, 1u);
+  else if (a.want_lnl && !a.st[e].lnl_valid) atomicAdd(active + 1, 1u);
 }
 
 __global__ void newton_store_lnl_kernel(NewtonArgs a, const double *shard)
 {
   const unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < a.B) a.st[e].lnl = shard[e];
+  if (e < a.B && !a.st[e].lnl_valid)
+  {
+    a.st[e].lnl = shard[(size_t)e * 3 + 2];
+    a.st[e].lnl_valid = 1;
+  }
 }
 
 // edge log-likelihood of a shard: tile partials -> one double in device memory
@@ -1061,7 +1142,7 @@ __device__ __forceinline__ void finish_candidate(const DevState &s, const ModelC
 }
 
 template <int C>
-__global__ void __launch_bounds__(kHeavySites *C)
+__global__ void __launch_bounds__(kHeavySites *C, PT_PREP_MINB)
     nni_prepare_kernel(DevState s, ModelConst m, const DevGroup *__restrict__ groups,
                        unsigned int ngroups, double *sumtables, size_t entry_stride,
                        unsigned int *sclr)

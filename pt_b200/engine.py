@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libptgpu.so")
+LIB_PATH = os.environ.get("PTGPU_LIB") or os.path.join(_HERE, "lib", "libptgpu.so")
 
 PTGPU_OK = 0
 PTGPU_ERR_CUDA = -1
