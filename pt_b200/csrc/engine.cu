@@ -103,6 +103,7 @@ struct ptgpu_engine
   unsigned int *d_active = nullptr;
   unsigned long long counters[4] = {0, 0, 0, 0};
   unsigned long long lnl_sweeps = 0, final_sweeps = 0;
+  int partials_version = 4; // PTGPU_PARTIALS=3 selects the register-resident-matrix walker
   // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
   bool profiling = false;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> pending;
@@ -232,6 +233,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
 
   ptgpu_engine *e = new ptgpu_engine;
   e->device = device;
+  if (const char *pv = getenv("PTGPU_PARTIALS")) e->partials_version = atoi(pv);
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
@@ -551,7 +553,10 @@ int ptgpu_update_partials(ptgpu_engine *e, const ptgpu_operation_t *ops, unsigne
   if ((rc = upload(e, e->d_ops, ops, count * sizeof(DevOp)))) return rc;
   {
     LaunchScope ls(e, PTGPU_KERNEL_PARTIALS);
-    DISPATCH_CATS(e, (partials_kernel<C><<<e->nheavy, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
+    if (e->partials_version == 3)
+    { DISPATCH_CATS(e, (partials_kernel<C><<<e->nheavy, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count))); }
+    else
+    { DISPATCH_CATS(e, (partials_kernel_v4<C><<<e->nheavy, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count))); }
   }
   CU(cudaGetLastError());
   e->counters[1] += (unsigned long long)count * e->sites;

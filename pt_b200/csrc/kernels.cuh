@@ -412,6 +412,114 @@ __global__ void __launch_bounds__(kHeavySites *C, PT_PART_MINB)
   }
 }
 
+// ---- kernel 1, version 4: P matrices staged per warp in shared memory ----------
+// Same barrier-free walk as partials_kernel, but the two 4x4xC matrices of an
+// operation are no longer held in 64 registers per thread: every warp keeps a
+// private, double-buffered copy in shared memory, filled one operation AHEAD
+// with cp.async (LDGSTS) so neither the descriptor->matrix address chain nor
+// the matrix fetch sits on the critical path, and consumed row by row
+// (LDS.128 broadcast; category blocks are padded to 18 doubles so the four
+// category rows of a quarter-warp fall into different banks).  ~80 registers
+// instead of 126 => 6 instead of 4 resident CTAs per SM for the same tile.
+constexpr int kMatPad = 18;  // doubles per (matrix, category) block in shared memory
+
+__device__ __forceinline__ void cp_async16(void *dst, const void *src)
+{
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int C>
+__device__ __forceinline__ void stage_matrices(const DevState &s, const DevOp &op, double *dst, int lane)
+{
+  // 2 matrices x C categories x 8 chunks of 16 bytes
+#pragma unroll
+  for (int c = lane; c < 2 * C * 8; c += 32)
+  {
+    const int which = c / (C * 8), rest = c % (C * 8), cat = rest / 8, within = rest % 8;
+    const double *src = s.pmat + ((size_t)(which ? op.c2_mat : op.c1_mat) * C + cat) * 16 + within * 2;
+    cp_async16(dst + (which * C + cat) * kMatPad + within * 2, src);
+  }
+  cp_async_commit();
+}
+
+template <int C>
+__global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 6 : 1))
+    partials_kernel_v4(DevState s, const DevOp *__restrict__ ops, unsigned int nops)
+{
+  constexpr int WARPS = (kHeavySites * C + 31) / 32;
+  __shared__ __align__(16) double mats[WARPS][2][2 * C * kMatPad];
+  const int cat = threadIdx.x % C;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned int site0 = blockIdx.x * kHeavyTile + threadIdx.x / C;
+
+  DevOp op = ops[0];
+  stage_matrices<C>(s, op, mats[warp][0], lane);
+  for (unsigned int o = 0; o < nops; ++o)
+  {
+    const int stage = o & 1;
+    DevOp nxt = op;
+    if (o + 1 < nops)
+    {
+      nxt = ops[o + 1];
+      stage_matrices<C>(s, nxt, mats[warp][stage ^ 1], lane);
+      cp_async_wait<1>();
+    }
+    else
+      cp_async_wait<0>();
+    __syncwarp();
+    const double *lmat = mats[warp][stage] + cat * kMatPad;
+    const double *rmat = mats[warp][stage] + (C + cat) * kMatPad;
+    double *dst = s.clv + (size_t)(op.parent_clv - s.n_tips) * s.clv_stride;
+#pragma unroll 1
+    for (int half = 0; half < kHeavyPasses; half += 2)
+    {
+      double l[2][4], r[2][4], p[2][4];
+      unsigned int sc[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+      {
+        const unsigned int site = min(site0 + (half + j) * kHeavySites, s.sites - 1);
+        load_entry<C>(s, op.c1_clv, site, cat, l[j]);
+        load_entry<C>(s, op.c2_clv, site, cat, r[j]);
+        sc[j] = load_scaler(s, op.c1_scaler, site) + load_scaler(s, op.c2_scaler, site);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+      {
+        double lrow[4], rrow[4];
+        lds256(lmat + 4 * i, lrow);
+        lds256(rmat + 4 * i, rrow);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) p[j][i] = __dmul_rn(dot4(lrow, l[j]), dot4(rrow, r[j]));
+      }
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+      {
+        const unsigned int site = site0 + (half + j) * kHeavySites;
+        bool small = (p[j][0] < PT_SCALE_THRESHOLD) & (p[j][1] < PT_SCALE_THRESHOLD) &
+                     (p[j][2] < PT_SCALE_THRESHOLD) & (p[j][3] < PT_SCALE_THRESHOLD);
+        small = site_all<C>(small) && op.parent_scaler >= 0;
+        if (small)
+        {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) p[j][i] = __dmul_rn(p[j][i], PT_SCALE_FACTOR);
+        }
+        if (site < s.sites)
+        {
+          st256(dst + ((size_t)site * C + cat) * 4, p[j]);
+          if (cat == 0 && op.parent_scaler >= 0)
+            s.scalers[(size_t)op.parent_scaler * s.scaler_stride + site] = sc[j] + (small ? 1u : 0u);
+        }
+      }
+    }
+    __syncwarp(); // scaler words / this stage's matrices are free for the op after next
+    op = nxt;
+  }
+}
+
 // Fixed-order finish shared by the reduction kernels: every CTA drops its
 // per-tile partial(s) into `partials[tile*NV + v]`; the last CTA to arrive
 // sums all tiles in a fixed tree, so the result depends only on `sites`,
