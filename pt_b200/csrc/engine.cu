@@ -104,6 +104,7 @@ struct ptgpu_engine
   unsigned long long counters[4] = {0, 0, 0, 0};
   unsigned long long lnl_sweeps = 0, final_sweeps = 0;
   int partials_version = 4; // PTGPU_PARTIALS=3 selects the register-resident-matrix walker
+  int prepare_version = 2;  // PTGPU_PREPARE=1 selects the register-resident-matrix prepare kernel
   // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
   bool profiling = false;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> pending;
@@ -234,6 +235,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   ptgpu_engine *e = new ptgpu_engine;
   e->device = device;
   if (const char *pv = getenv("PTGPU_PARTIALS")) e->partials_version = atoi(pv);
+  if (const char *pv = getenv("PTGPU_PREPARE")) e->prepare_version = atoi(pv);
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
@@ -281,13 +283,20 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
     if (occ < 1) { ptgpu_destroy(e); return fail(PTGPU_ERR_CUDA, "newton kernel does not fit an SM"); }
     e->coop_blocks_per_sm = occ;
     cudaError_t ea = cudaSuccess;
+#define PT_SET_SMEM(CC)                                                                                   \
+  ea = cudaFuncSetAttribute(nni_prepare_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                            (int)sizeof(PrepSmem<CC>));                                                   \
+  if (ea == cudaSuccess)                                                                                  \
+    ea = cudaFuncSetAttribute(nni_prepare_kernel_v2<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
+                              (int)sizeof(PrepSmem2<CC>));
     switch (rate_cats)
     {
-      case 1: ea = cudaFuncSetAttribute(nni_prepare_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<1>)); break;
-      case 2: ea = cudaFuncSetAttribute(nni_prepare_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<2>)); break;
-      case 4: ea = cudaFuncSetAttribute(nni_prepare_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<4>)); break;
-      default: ea = cudaFuncSetAttribute(nni_prepare_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PrepSmem<8>)); break;
+      case 1: { PT_SET_SMEM(1) break; }
+      case 2: { PT_SET_SMEM(2) break; }
+      case 4: { PT_SET_SMEM(4) break; }
+      default: { PT_SET_SMEM(8) break; }
     }
+#undef PT_SET_SMEM
     if (ea != cudaSuccess) { ptgpu_destroy(e); return fail(PTGPU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(ea)); }
   }
   CU_NEW(cudaStreamSynchronize(e->stream));
@@ -826,8 +835,12 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     if ((rc = upload(e, e->d_bstate, hst.data(), nb * sizeof(NewtonState)))) return rc;
     {
       LaunchScope ls(e, PTGPU_KERNEL_NNI_PREPARE);
-      DISPATCH_CATS(e, (nni_prepare_kernel<C><<<e->nheavy * ng, kHeavySites * C, sizeof(PrepSmem<C>), e->stream>>>(
-                           e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr)));
+      if (e->prepare_version == 1)
+      { DISPATCH_CATS(e, (nni_prepare_kernel<C><<<e->nheavy * ng, kHeavySites * C, sizeof(PrepSmem<C>), e->stream>>>(
+                           e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr))); }
+      else
+      { DISPATCH_CATS(e, (nni_prepare_kernel_v2<C><<<e->nheavy * ng, kHeavySites * C, sizeof(PrepSmem2<C>), e->stream>>>(
+                           e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr))); }
     }
     CU(cudaGetLastError());
     NewtonArgs a{};

@@ -1315,4 +1315,104 @@ __global__ void __launch_bounds__(kHeavySites *C, PT_PREP_MINB)
   }
 }
 
+// ---- NNI prepare, version 2 ---------------------------------------------------
+// Same staging (TMA bulk copies on four mbarriers) and same arithmetic as
+// nni_prepare_kernel, with the register footprint cut so that three CTAs fit an
+// SM: the four P matrices are staged once per CTA in shared memory (padded
+// category blocks, broadcast LDS.128 rows) instead of 32 registers per thread,
+// and the tile is walked two passes at a time (64 projection registers instead
+// of 128).
+template <int C>
+struct PrepSmem2
+{
+  double clv[4][kHeavyTile * C * 4];
+  unsigned int scal[4][kHeavyTile];
+  unsigned char tip[4][kHeavyTile];
+  unsigned long long bar[4];
+  // everything above has the layout of PrepSmem<C> (stage_child / staged_entry use that view)
+  __align__(16) double mat[4][C * kMatPad];
+};
+
+template <int C>
+__global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 3 : 1))
+    nni_prepare_kernel_v2(DevState s, ModelConst m, const DevGroup *__restrict__ groups,
+                          unsigned int ngroups, double *sumtables, size_t entry_stride,
+                          unsigned int *sclr)
+{
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  PrepSmem2<C> &sm = *reinterpret_cast<PrepSmem2<C> *>(smem_raw);
+  const unsigned int g = blockIdx.x % ngroups, tile = blockIdx.x / ngroups;
+  const DevGroup gr = groups[g];
+  const int cat = threadIdx.x % C;
+  const unsigned int lsite0 = threadIdx.x / C;
+  const unsigned int site_base = tile * kHeavyTile;
+  const unsigned int nvalid = min((unsigned int)kHeavyTile, s.sites - site_base);
+
+  if (threadIdx.x == 0)
+  {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) mbar_init(&sm.bar[i], 1);
+    mbar_fence_init();
+  }
+  // the four matrices: 4 x C x 16 doubles, one double2 per thread and step
+  for (int c = threadIdx.x; c < 4 * C * 8; c += kHeavySites * C)
+  {
+    const int k = c / (C * 8), rest = c % (C * 8), mc = rest / 8, within = rest % 8;
+    const double2 v = *reinterpret_cast<const double2 *>(
+        s.pmat + ((size_t)gr.ch[k].mat * C + mc) * 16 + within * 2);
+    *reinterpret_cast<double2 *>(&sm.mat[k][mc * kMatPad + within * 2]) = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      stage_child<C>(s, *reinterpret_cast<PrepSmem<C> *>(smem_raw), k, gr.ch[k].clv, gr.ch[k].scaler,
+                     site_base, nvalid);
+  }
+
+#pragma unroll 1
+  for (int half = 0; half < kHeavyPasses; half += 2)
+  {
+    double proj[4][2][4];
+    unsigned int cnt[2] = {0u, 0u};
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+      if (half == 0) mbar_wait(&sm.bar[k], 0);
+      double x[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+      {
+        const unsigned int ls = min(lsite0 + (half + j) * kHeavySites, nvalid - 1);
+        cnt[j] += staged_entry<C>(s, *reinterpret_cast<PrepSmem<C> *>(smem_raw), k, gr.ch[k].clv,
+                                  gr.ch[k].scaler, ls, cat, x[j]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+      {
+        double row[4];
+        lds256(&sm.mat[k][cat * kMatPad + 4 * i], row);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) proj[k][j][i] = dot4(row, x[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      const unsigned int ls_raw = lsite0 + (half + j) * kHeavySites;
+      const bool ok = ls_raw < nvalid;
+      const unsigned int site = site_base + min(ls_raw, nvalid - 1);
+      const size_t eoff = ((size_t)site * C + cat) * 4;
+      finish_candidate<C>(s, m, proj[0][j], proj[1][j], proj[2][j], proj[3][j], cnt[j], ok,
+                          sumtables + (size_t)gr.out[0] * entry_stride + eoff,
+                          sclr + (size_t)gr.out[0] * s.sites + site, cat);
+      if (gr.ncand > 1)
+        finish_candidate<C>(s, m, proj[3][j], proj[1][j], proj[2][j], proj[0][j], cnt[j], ok,
+                            sumtables + (size_t)gr.out[1] * entry_stride + eoff,
+                            sclr + (size_t)gr.out[1] * s.sites + site, cat);
+    }
+  }
+}
+
 } // namespace ptgpu
