@@ -318,12 +318,16 @@ def run_ours(args):
     launches = c1["launches"] - c0["launches"]
     site_updates = c1["site_updates"] - c0["site_updates"]
     passes = c1["newton_passes"] - c0["newton_passes"]
+    lnl_sweeps = c1["lnl_sweeps"] - c0["lnl_sweeps"]
+    final_sweeps = c1["final_sweeps"] - c0["final_sweeps"]
     peak, peak_kind = measured_peak()
     child_bytes = sum((1 if c < n else 132) for row in cand_rows for c in (row[2][2], row[2][5], row[3][2], row[3][5]))
     algo = dict(
         partials=op_bytes(plan_rows, n, S),                                  # per launch
         nni_prepare=(child_bytes + ncand * 132) * S,                          # per launch
-        newton=(passes / steps) * S * 128 + ncand * S * 132,                  # per launch
+        # per launch: every derivative sweep reads the candidate's sumtable (128 B/site); the
+        # sweeps that also sum the site lnL read the scaler word too; rare extra lnL-only sweeps
+        newton=(passes * 128 + lnl_sweeps * 4 + final_sweeps * 132) / steps * S,
     )
     kernels = {}
     for k, bytes_per_launch in algo.items():
@@ -352,6 +356,8 @@ def run_ours(args):
                     l2="inputs (>20 GB of CLVs per step) far exceed the 126 MB L2; no flush needed"),
         clv_site_updates_per_s=world * site_updates / (kt["partials"][0] * 1e-3) if kt["partials"][0] else None,
         newton_iterations_per_candidate=passes / steps / ncand,
+        lnl_carrying_sweeps_per_candidate=lnl_sweeps / steps / ncand,
+        extra_lnl_sweeps_per_candidate=final_sweeps / steps / ncand,
         gpu_launches=int(launches), kernels=kernels, roofline=roof, clocks=clocks,
         e2e=dict(value=world * ncand * len(t_e2e) / e2e_s, unit="candidates/s",
                  h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h),

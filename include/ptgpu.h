@@ -203,8 +203,10 @@ int ptgpu_set_pmatrix(ptgpu_engine *e, unsigned int matrix_index, const double *
 int ptgpu_get_sumtable(ptgpu_engine *e, double *out);
 
 /* counters since create: [0] kernel launches, [1] CLV site-updates,
-   [2] Newton derivative passes (site sweeps), [3] NNI candidates scored */
-int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[4]);
+   [2] Newton derivative passes (site sweeps), [3] NNI candidates scored,
+   [4] batch sweeps that also summed the site log-likelihoods (they read the
+   scaler word too), [5] extra lnL-only sweeps after the Newton loop */
+int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[6]);
 
 /* Optional per-kernel timing with CUDA events on the engine's stream (used by
    bench.py for the roofline figures; off by default).  Kinds index the arrays

@@ -197,8 +197,14 @@ template <int C>
 int coop_occupancy(int *out)
 {
   int a = 0, b = 0;
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, newton_kernel<C, false>, kSitesPerPass * C, 0));
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, newton_kernel<C, true>, kSitesPerPass * C, 0));
+  const int ring = (int)sweep_ring_bytes<C>();
+  CU(cudaFuncSetAttribute(newton_kernel<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
+  CU(cudaFuncSetAttribute(newton_kernel<C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
+  CU(cudaFuncSetAttribute(newton_sweep_kernel<C, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
+  CU(cudaFuncSetAttribute(newton_sweep_kernel<C, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
+  CU(cudaFuncSetAttribute(newton_sweep_kernel<C, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, newton_kernel<C, false>, kSitesPerPass * C, ring));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, newton_kernel<C, true>, kSitesPerPass * C, ring));
   *out = std::min(a, b);
   return PTGPU_OK;
 }
@@ -240,7 +246,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
   e->nheavy = (sites + kHeavyTile - 1) / kHeavyTile;
-  e->chunk_tiles = std::min(8u, std::max(1u, e->ntiles / 128u));
+  e->chunk_tiles = std::min(32u, std::max(1u, e->ntiles / 128u));
   e->nchunks = (e->ntiles + e->chunk_tiles - 1) / e->chunk_tiles;
   const size_t clv_stride = (size_t)sites * rate_cats * 4;
 #define CU_NEW(call)                                                                    \
@@ -453,7 +459,7 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
     void *fn = a.want_lnl ? (void *)newton_kernel<C, true> : (void *)newton_kernel<C, false>;
-    CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kSitesPerPass * C), params, 0, e->stream));
+    CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kSitesPerPass * C), params, sweep_ring_bytes<C>(), e->stream));
   }
   return PTGPU_OK;
 }
@@ -483,8 +489,8 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
   {
     {
       LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-      if (a.want_lnl) newton_sweep_kernel<C, true, false><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
-      else newton_sweep_kernel<C, false, false><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+      if (a.want_lnl) newton_sweep_kernel<C, true, false><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
+      else newton_sweep_kernel<C, false, false><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
     }
     { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<false><<<a.B, 256, 0, e->stream>>>(a, e->d_red); }
     CU(cudaGetLastError());
@@ -503,7 +509,7 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
   if (!pending_lnl) return PTGPU_OK;
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-    newton_sweep_kernel<C, true, true><<<grid, kSitesPerPass * C, 0, e->stream>>>(a);
+    newton_sweep_kernel<C, true, true><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
   }
   { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<true><<<a.B, 256, 0, e->stream>>>(a, e->d_red); }
   CU(cudaGetLastError());
@@ -973,10 +979,12 @@ int ptgpu_get_sumtable(ptgpu_engine *e, double *out)
   return PTGPU_OK;
 }
 
-int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[4])
+int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[6])
 {
   if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_get_counters: null argument");
   for (int i = 0; i < 4; ++i) out[i] = e->counters[i];
+  out[4] = e->lnl_sweeps;
+  out[5] = e->final_sweeps;
   return PTGPU_OK;
 }
 

@@ -722,7 +722,7 @@ struct LnlProd
 template <bool WITH_LNL>
 __device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[3], double terma,
                                            unsigned int site, unsigned int full,
-                                           const unsigned int *sclr, double out[3], LnlProd &lp)
+                                           unsigned int sc, double out[3], LnlProd &lp)
 {
   // LIBPLL/core_derivatives_avx.c:1111-1156: sites below `full` (= sites/4*4) use
   // the reciprocal form of the 4-site vector step, the tail true divisions
@@ -741,17 +741,17 @@ __device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[
     out[0] = __dadd_rn(out[0], a);
     out[1] = __dadd_rn(out[1], b);
   }
-  if (WITH_LNL) lp.add(terma, sclr ? sclr[site] : 0u);
+  if (WITH_LNL) lp.add(terma, sc);
 }
 
 // One tile of the site sweep.  out[0] += -L'/L terms, out[1] += second
 // derivative terms, out[2] += log-likelihood terms (only if WITH_LNL).
 template <int C, bool WITH_LNL>
-__device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *sumtable,
-                                           const unsigned int *sclr, unsigned int sites,
-                                           unsigned int tile, const double (&dg)[4][3],
-                                           double out[3], LnlProd &lp,
-                                           unsigned long long vec_end = ~0ull)
+__device__ __forceinline__ void sweep_tile_compute(const ModelConst &m, const double (&sv)[kPasses][4],
+                                                   const unsigned int (&scv)[kPasses], unsigned int sites,
+                                                   unsigned int tile, const double (&dg)[4][3],
+                                                   double out[3], LnlProd &lp,
+                                                   unsigned long long vec_end)
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
@@ -762,13 +762,6 @@ __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *su
   constexpr int NQ = WITH_LNL ? 4 : 3;
   double ck[kPasses][NQ];
   {
-    double sv[kPasses][4];
-#pragma unroll
-    for (int ps = 0; ps < kPasses; ++ps)
-    {
-      const unsigned int site = min(site0 + ps * kSitesPerPass, sites - 1);
-      ld256_stream(sumtable + ((size_t)site * C + cat) * 4, sv[ps]);
-    }
 #pragma unroll
     for (int ps = 0; ps < kPasses; ++ps)
     {
@@ -789,7 +782,7 @@ __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *su
     double r[NQ];
     quad_transpose_sum<NQ>(ck, cat, r);
     const unsigned int site = site0 + quad_pass(cat) * kSitesPerPass;
-    if (site < sites) site_terms<WITH_LNL>(m, r, r[NQ - 1], site, full, sclr, out, lp);
+    if (site < sites) site_terms<WITH_LNL>(m, r, r[NQ - 1], site, full, scv[0], out, lp);
   }
   else
   {
@@ -805,9 +798,118 @@ __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *su
 #pragma unroll
         for (int q = 0; q < NQ; ++q)
           lk[q] = __dadd_rn(lk[q], __shfl_down_sync(0xffffffffu, ck[ps][q], k, C));
-      if (cat == 0 && site < sites) site_terms<WITH_LNL>(m, lk, lk[NQ - 1], site, full, sclr, out, lp);
+      if (cat == 0 && site < sites) site_terms<WITH_LNL>(m, lk, lk[NQ - 1], site, full, scv[ps], out, lp);
     }
   }
+}
+
+// The summed scaler words a thread will need in the epilogue of this tile, fetched
+// together with the sumtable entries (C == 4: the lane ends up with exactly one
+// site, quad_pass(cat); otherwise the category-0 lane handles every pass).
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void load_scaler_words(const unsigned int *sclr, unsigned int sites,
+                                                  unsigned int tile, unsigned int (&scv)[kPasses])
+{
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps) scv[ps] = 0u;
+  if (!WITH_LNL || !sclr) return;
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  if (C == 4)
+    scv[0] = __ldg(sclr + min(site0 + quad_pass(cat) * kSitesPerPass, sites - 1));
+  else if (cat == 0)
+  {
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps) scv[ps] = __ldg(sclr + min(site0 + ps * kSitesPerPass, sites - 1));
+  }
+}
+
+// direct form: loads straight into registers
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *sumtable,
+                                           const unsigned int *sclr, unsigned int sites,
+                                           unsigned int tile, const double (&dg)[4][3],
+                                           double out[3], LnlProd &lp,
+                                           unsigned long long vec_end = ~0ull)
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  double sv[kPasses][4];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = min(site0 + ps * kSitesPerPass, sites - 1);
+    ld256_stream(sumtable + ((size_t)site * C + cat) * 4, sv[ps]);
+  }
+  unsigned int scv[kPasses];
+  load_scaler_words<C, WITH_LNL>(sclr, sites, tile, scv);
+  sweep_tile_compute<C, WITH_LNL>(m, sv, scv, sites, tile, dg, out, lp, vec_end);
+}
+
+// Streaming form: the tiles [t0, t1) of one sumtable flow through a per-thread
+// ring in shared memory.  Every thread copies ITS OWN entries of the tile that
+// lies kRingStages-1 tiles ahead with cp.async (LDGSTS) and later reads them
+// back, so the ring needs no barrier of any kind (thread-private slots, ordered
+// by cp.async groups), and the bytes in flight no longer depend on registers:
+// kRingStages-1 tiles x 32 KB per CTA are always on their way.
+constexpr int kRingStages = 3;
+#ifndef PT_SWEEP_RING
+#define PT_SWEEP_RING 0   // measured on B200: plain LDG.256 streaming (3 CTAs/SM) beats the ring (2 CTAs/SM)
+#endif
+
+template <int C>
+constexpr size_t sweep_ring_bytes() { return PT_SWEEP_RING ? (size_t)kRingStages * kPasses * kSitesPerPass * C * 32 : 0; }
+
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void sweep_chunk(const ModelConst &m, const double *sumtable,
+                                            const unsigned int *sclr, unsigned int sites,
+                                            unsigned int t0, unsigned int t1, const double (&dg)[4][3],
+                                            double *ring, double out[3], LnlProd &lp,
+                                            unsigned long long vec_end)
+{
+  if (!PT_SWEEP_RING)
+  {
+    for (unsigned int tile = t0; tile < t1; ++tile)
+      sweep_tile<C, WITH_LNL>(m, sumtable, sclr, sites, tile, dg, out, lp, vec_end);
+    return;
+  }
+  constexpr int T = kSitesPerPass * C;
+  const int cat = threadIdx.x % C;
+  const unsigned int lsite = threadIdx.x / C;
+  auto issue = [&](unsigned int tile, int stage) {
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps)
+    {
+      const unsigned int site = min(tile * kTileSites + lsite + ps * kSitesPerPass, sites - 1);
+      const double *src = sumtable + ((size_t)site * C + cat) * 4;
+      double *dst = ring + ((size_t)(stage * kPasses + ps) * T + threadIdx.x) * 4;
+      cp_async16(dst, src);
+      cp_async16(dst + 2, src + 2);
+    }
+  };
+#pragma unroll
+  for (int k = 0; k < kRingStages - 1; ++k)
+  {
+    if (t0 + k < t1) issue(t0 + k, k);
+    cp_async_commit();
+  }
+  int stage = 0, fill = kRingStages - 1;
+  for (unsigned int tile = t0; tile < t1; ++tile)
+  {
+    if (tile + (kRingStages - 1) < t1) issue(tile + (kRingStages - 1), fill);
+    cp_async_commit();                       // (possibly empty) group: keeps the count uniform
+    unsigned int scv[kPasses];
+    load_scaler_words<C, WITH_LNL>(sclr, sites, tile, scv);
+    cp_async_wait<kRingStages - 1>();        // the group of `tile` has landed
+    double sv[kPasses][4];
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps)
+      lds256(ring + ((size_t)(stage * kPasses + ps) * T + threadIdx.x) * 4, sv[ps]);
+    sweep_tile_compute<C, WITH_LNL>(m, sv, scv, sites, tile, dg, out, lp, vec_end);
+    stage = stage + 1 == kRingStages ? 0 : stage + 1;
+    fill = fill + 1 == kRingStages ? 0 : fill + 1;
+  }
+  cp_async_wait<0>();
 }
 
 struct NewtonArgs
@@ -950,10 +1052,11 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
 // barrier.  Reduction units (chunks) depend only on the site count, so results
 // are independent of the grid size.
 template <int C, bool LNL>
-__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_kernel(NewtonArgs a)
+__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? (PT_SWEEP_RING ? 2 : 3) : 1)) newton_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
   cg::grid_group grid = cg::this_grid();
+  extern __shared__ __align__(16) double ring[];
   __shared__ double red[T / 32 < 1 ? 1 : T / 32];
   const unsigned int nwork = a.B * a.nchunks;
   const int cat = threadIdx.x % C;
@@ -971,14 +1074,12 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
       const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
       const bool with_lnl = LNL && __ldcg(&a.st[e].try_lnl);
       if (with_lnl)
-        for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-          sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                              a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
-                              lp, a.vec_end);
+        sweep_chunk<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                              a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
+                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
       else
-        for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-          sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites, tile,
-                               dg, out, lp, a.vec_end);
+        sweep_chunk<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
       const double s1 = block_sum<T>(out[0], red);
       const double s2 = block_sum<T>(out[1], red);
       const double s3 = LNL ? block_sum<T>(with_lnl ? lp.value() : 0.0, red) : 0.0;
@@ -1026,10 +1127,9 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 3 : 1)) newton_ker
     double out[3] = {0.0, 0.0, 0.0};
     LnlProd lp;
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-    for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-      sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                          a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
-                          lp, a.vec_end);
+    sweep_chunk<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                              a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
+                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
     const double sm = block_sum<T>(lp.value(), red);
     if (threadIdx.x == 0) a.partials[(size_t)w * 3 + 2] = sm;
   }
@@ -1054,6 +1154,7 @@ template <int C, bool LNL, bool FINAL>
 __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
+  extern __shared__ __align__(16) double ring[];
   __shared__ double red[T / 32 < 1 ? 1 : T / 32];
   const unsigned int nwork = a.B * a.nchunks;
   const int cat = threadIdx.x % C;
@@ -1068,14 +1169,12 @@ __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonAr
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
     const bool with_lnl = LNL && (FINAL || a.st[e].try_lnl);
     if (with_lnl)
-      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-        sweep_tile<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                            a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites, tile, dg, out,
-                            lp, a.vec_end);
+      sweep_chunk<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+                              a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
+                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
     else
-      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-        sweep_tile<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites, tile,
-                             dg, out, lp, a.vec_end);
+      sweep_chunk<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
     const double s1 = block_sum<T>(out[0], red);
     const double s2 = block_sum<T>(out[1], red);
     const double s3 = LNL ? block_sum<T>(with_lnl ? lp.value() : 0.0, red) : 0.0;

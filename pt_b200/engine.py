@@ -217,9 +217,10 @@ class Engine:
         return out
 
     def counters(self):
-        out = (C.c_ulonglong * 4)()
+        out = (C.c_ulonglong * 6)()
         self._chk(self.lib.ptgpu_get_counters(self.h, out))
-        return dict(launches=out[0], site_updates=out[1], newton_passes=out[2], candidates=out[3])
+        return dict(launches=out[0], site_updates=out[1], newton_passes=out[2], candidates=out[3],
+                    lnl_sweeps=out[4], final_sweeps=out[5])
 
     def stream(self):
         return self.lib.ptgpu_stream(self.h)
