@@ -104,6 +104,7 @@ struct ptgpu_engine
   unsigned long long counters[4] = {0, 0, 0, 0};
   unsigned long long lnl_sweeps = 0, final_sweeps = 0;
   int partials_version = 4; // PTGPU_PARTIALS=3 selects the register-resident-matrix walker
+  double lnl_margin = 100.0; // PTGPU_LNL_MARGIN
   int prepare_version = 2;  // PTGPU_PREPARE=1 selects the register-resident-matrix prepare kernel
   // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
   bool profiling = false;
@@ -242,6 +243,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   e->device = device;
   if (const char *pv = getenv("PTGPU_PARTIALS")) e->partials_version = atoi(pv);
   if (const char *pv = getenv("PTGPU_PREPARE")) e->prepare_version = atoi(pv);
+  if (const char *pv = getenv("PTGPU_LNL_MARGIN")) e->lnl_margin = atof(pv);
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
@@ -522,6 +524,7 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
 int run_newton(ptgpu_engine *e, NewtonArgs &a)
 {
   a.vec_end = e->vec_end;
+  a.lnl_margin = e->lnl_margin;
   if (e->allreduce) { DISPATCH_CATS(e, return newton_split<C>(e, a)); }
   DISPATCH_CATS(e, return launch_newton<C>(e, a));
   return PTGPU_OK;

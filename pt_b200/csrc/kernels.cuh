@@ -925,6 +925,7 @@ struct NewtonArgs
   int want_lnl;
   int mode;                 // 0: Partition::OptimizeBranch, 1: pllmod_opt_minimize_newton
   double xmin, xmax;        // mode 1 bounds
+  double lnl_margin;          // predictor margin: carry the lnL when predicted |d1| < margin * eps
   unsigned long long vec_end; // ~0: unsharded; else local index where the global scalar tail starts
 };
 
@@ -1022,7 +1023,7 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
         const double pred = (st.iters > 1 && prev != 0.0)
                                 ? fabs(d1) * (fabs(d1) / fabs(prev)) * (fabs(d1) / fabs(prev))
                                 : fabs(d1);
-        st.try_lnl = pred < 100.0 * a.eps;
+        st.try_lnl = pred < a.lnl_margin * a.eps;
       }
       if (st.len < 0.0)
       {
@@ -1447,11 +1448,18 @@ __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 3 : 1))
   const unsigned int site_base = tile * kHeavyTile;
   const unsigned int nvalid = min((unsigned int)kHeavyTile, s.sites - site_base);
 
+  // thread 0 arms the barriers and starts the four bulk copies at once (same
+  // thread: program order); everybody else stages the matrices meanwhile, and
+  // one CTA barrier publishes both the barriers and the matrices
   if (threadIdx.x == 0)
   {
 #pragma unroll
     for (int i = 0; i < 4; ++i) mbar_init(&sm.bar[i], 1);
     mbar_fence_init();
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      stage_child<C>(s, *reinterpret_cast<PrepSmem<C> *>(smem_raw), k, gr.ch[k].clv, gr.ch[k].scaler,
+                     site_base, nvalid);
   }
   // the four matrices: 4 x C x 16 doubles, one double2 per thread and step
   for (int c = threadIdx.x; c < 4 * C * 8; c += kHeavySites * C)
@@ -1462,13 +1470,6 @@ __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 3 : 1))
     *reinterpret_cast<double2 *>(&sm.mat[k][mc * kMatPad + within * 2]) = v;
   }
   __syncthreads();
-  if (threadIdx.x == 0)
-  {
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      stage_child<C>(s, *reinterpret_cast<PrepSmem<C> *>(smem_raw), k, gr.ch[k].clv, gr.ch[k].scaler,
-                     site_base, nvalid);
-  }
 
 #pragma unroll 1
   for (int half = 0; half < kHeavyPasses; half += 2)
