@@ -175,6 +175,67 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
                           double epsilon, double map_lambda, double *length_out,
                           double *lnl_out, int *status_out);
 
+/* Batched BranchNeighborhoodOptimizer::EvaluateMove
+   (src/move_tester/branch_neighborhood_optimizer.cpp:27-80) for `count`
+   candidates of one parent tree: per candidate the CLV updates across the
+   swapped edge, then pllmod_opt_optimize_branch_lengths_local
+   (PLLMOD/optimize/pll_optimize.c:969-1091) and the final edge
+   log-likelihood, all candidates in one persistent kernel.  The caller
+   flattens recomp_iterative's recursion (pll_optimize.c:771-934) into a step
+   list of the same shape for every candidate: `n_prologue` steps run once,
+   then `n_body` steps per smoothing, given TWICE: rows [n_prologue,
+   n_prologue + n_body) are the first smoothing (nodes the recursion has not
+   re-oriented yet are still read from the engine's CLVs), rows
+   [n_prologue + n_body, n_prologue + 2 n_body) every later one (all touched
+   nodes are private copies by then).  steps[k * count + i] is step k of
+   candidate i and step_types[k] (n_prologue + 2 n_body entries) its type for
+   all candidates (a candidate without that step has PTGPU_BLO_NOP there).
+     PTGPU_BLO_OP : CLV a <- (CLV b through matrix b) x (CLV c through matrix c)
+     PTGPU_BLO_OPT: optimise the edge between CLV a ("parent" of the sumtable,
+                    tr_p) and CLV b (tr_p->back) whose P matrix is b_matrix and
+                    whose length lives in length_slot: safeguarded Newton in
+                    [bl_min, bl_max], tolerance bl_min/10, <= 30 evaluations
+   Nothing in the engine's own CLV / scaler / P-matrix state is modified:
+   candidate i writes only PRIVATE slots, addressed above the engine's ranges:
+     CLV     tips + clv_buffers + i * n_private_clvs + j   (scaler: scale_buffers + same offset)
+     matrix  prob_matrices + i * n_lengths + slot          (initialised from lengths0[i][slot])
+   smooth_edges[i] is the edge whose lnL ends every smoothing (parent tree->back,
+   child tree; pll_optimize.c:1049-1056), final_edges[i] the edge of the final
+   Partition::LogLikelihood(node).  status_out[i]: 0, or PTGPU_NEWTON_DERIV /
+   PTGPU_NEWTON_LIMIT if a solve failed (the reference stops optimising that
+   candidate; its lnL is then taken on the state it was left in). */
+#define PTGPU_BLO_NOP 0
+#define PTGPU_BLO_OP 1
+#define PTGPU_BLO_OPT 2
+typedef struct ptgpu_blo_step
+{
+  int type;
+  unsigned int a_clv;
+  int a_scaler;
+  unsigned int b_clv, b_matrix;
+  int b_scaler;
+  unsigned int c_clv, c_matrix;
+  int c_scaler;
+  unsigned int length_slot;
+} ptgpu_blo_step_t;
+typedef struct ptgpu_blo_edge
+{
+  unsigned int parent_clv;
+  int parent_scaler;
+  unsigned int child_clv;
+  int child_scaler;
+  unsigned int matrix;
+  unsigned int reserved;
+} ptgpu_blo_edge_t;
+int ptgpu_optimize_local_batch(ptgpu_engine *e, unsigned int count, unsigned int n_private_clvs,
+                               unsigned int n_lengths, unsigned int n_prologue, unsigned int n_body,
+                               const int *step_types, const ptgpu_blo_step_t *steps,
+                               const ptgpu_blo_edge_t *smooth_edges,
+                               const ptgpu_blo_edge_t *final_edges, const double *lengths0,
+                               double bl_min, double bl_max, double tolerance,
+                               unsigned int smoothings, double *lengths_out, double *lnl_out,
+                               int *status_out, int *smoothings_out);
+
 /* ---- site shards: one engine per GPU holds a contiguous range
    of the alignment's sites.  CLV updates, P matrices and sumtables are purely
    local; every reduction over sites (edge lnL; d1/d2 of each Newton step; the

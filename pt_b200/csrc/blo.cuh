@@ -1,0 +1,469 @@
+// pt_b200/csrc/blo.cuh -- batched local branch-length optimisation on the device.
+//
+// BranchNeighborhoodOptimizer::EvaluateMove
+// (/root/reference/src/move_tester/branch_neighborhood_optimizer.cpp:27-80) scores
+// ONE NNI candidate with ~100 libpll calls: two CLV updates, then pll-modules'
+// pllmod_opt_optimize_branch_lengths_local (PLLMOD/optimize/pll_optimize.c:969-1091:
+// up to 32 smoothings of recomp_iterative, :771-934 -- sumtable, safeguarded
+// Newton, P matrix, re-orient the node's CLV, recurse), an edge lnL per smoothing,
+// and finally a FULL traversal to undo the damage.  Here ALL candidates of a tree
+// run that procedure at once in one persistent cooperative kernel:
+//
+//  * the host flattens recomp_iterative's recursion for the requested radius into
+//    a short step list per candidate (CLV update / optimise edge), identical in
+//    shape for all candidates (missing subtrees become no-ops);
+//  * every candidate owns private CLV, scaler, P-matrix and length slots, so the
+//    engine's own state is never touched (no resynchronising traversal);
+//  * the kernel walks the step list in lock step for all live candidates, each
+//    phase spread over the whole grid as (candidate, tile) work items, with the
+//    same elementwise arithmetic and the same fixed-order reductions as the
+//    single-edge kernels -- a candidate's numbers do not depend on its batch.
+#pragma once
+
+#include "kernels.cuh"
+
+namespace ptgpu {
+
+// index spaces seen by the batch: [0, *_total) are the engine's, above that the
+// candidates' private slots
+struct BloView
+{
+  DevState s;
+  unsigned int clv_total;   // tips + clv_buffers
+  unsigned int scal_total;  // scale_buffers
+  unsigned int mat_total;   // prob_matrices
+  double *pclv;             // [private clvs][clv_stride]
+  unsigned int *pscal;      // [private scalers][scaler_stride]
+  double *pmat;             // [private matrices][C][16]
+};
+
+enum : int { BLO_NOP = 0, BLO_OP = 1, BLO_OPT = 2 };
+
+struct BloStep
+{
+  int type;
+  // BLO_OP : parent (a) <- child1 (b via b_mat) x child2 (c via c_mat)
+  // BLO_OPT: edge with "parent" side a and "child" side b (sumtable order of
+  //          recomp_iterative: tr_p, tr_p->back), its P matrix b_mat and length slot
+  unsigned int a_clv;
+  int a_scal;
+  unsigned int b_clv, b_mat;
+  int b_scal;
+  unsigned int c_clv, c_mat;
+  int c_scal;
+  unsigned int slot;
+};
+
+struct BloEdge  // an edge whose log-likelihood is taken: parent side, child side, matrix
+{
+  unsigned int p_clv;
+  int p_scal;
+  unsigned int c_clv;
+  int c_scal;
+  unsigned int mat;
+  unsigned int pad;
+};
+
+struct BloCand
+{
+  double lnl;        // lnL after the last completed smoothing (start: before the first)
+  double final_lnl;  // LogLikelihood(node) at the end
+  int active;        // still smoothing
+  int failed;        // a Newton solve failed (pll_errno set in the reference): no further steps
+  int smoothings;    // completed smoothings
+  int newton_evals;  // statistics
+};
+
+struct BloArgs
+{
+  BloView v;
+  ModelConst m;
+  const BloStep *steps;      // [n_pro + 2 n_body][B]: prologue, first smoothing, later smoothings
+  const BloEdge *smooth_edge; // [B] parent q, child p  (pll_optimize.c:1000-1007,1049-1056)
+  const BloEdge *final_edge;  // [B] parent p, child q  (Partition::LogLikelihood(node))
+  BloCand *cand;             // [B]
+  double *lens;              // [B][NL] private branch lengths
+  NewtonState *nst;          // [B]
+  double *sumtables;         // [B][entry_stride]
+  size_t entry_stride;
+  double *partials;          // [B][nchunks][3] Newton chunk partials
+  double *tile_partials;     // [B][ntiles] edge-lnL tile partials
+  const int *step_type;      // [n_pro + 2 n_body] the (uniform) type of each step position
+  unsigned int B, NL, n_pro, n_body;
+  unsigned int sites, ntiles, chunk_tiles, nchunks;
+  unsigned int smoothings, max_newton;
+  double xmin, xmax, xtol, tolerance;
+  unsigned long long vec_end;
+};
+
+// ---- loaders over the combined index spaces ---------------------------------
+// Private CLVs, scalers and matrices are rewritten between phases by other SMs:
+// all their reads go to L2 (ld.global.cg), never through L1 or the read-only path.
+__device__ __forceinline__ void ld256_cg(const double *p, double v[4])
+{
+  asm volatile("ld.global.cg.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+               : "l"(p));
+}
+
+template <int C>
+__device__ __forceinline__ const double *blo_clv_ptr(const BloView &v, unsigned int idx)
+{
+  return idx < v.clv_total ? v.s.clv + (size_t)(idx - v.s.n_tips) * v.s.clv_stride
+                           : v.pclv + (size_t)(idx - v.clv_total) * v.s.clv_stride;
+}
+
+template <int C>
+__device__ __forceinline__ void blo_load_entry(const BloView &v, unsigned int idx, unsigned int site,
+                                               int cat, double x[4])
+{
+  if (idx < v.s.n_tips)
+  {
+    const unsigned int mk = v.s.tips[(size_t)idx * v.s.tip_stride + site];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = ((mk >> j) & 1u) ? 1.0 : 0.0;
+  }
+  else
+    ld256_cg(blo_clv_ptr<C>(v, idx) + ((size_t)site * C + cat) * 4, x);
+}
+
+__device__ __forceinline__ unsigned int *blo_scal_ptr(const BloView &v, int idx)
+{
+  return (unsigned int)idx < v.scal_total ? v.s.scalers + (size_t)idx * v.s.scaler_stride
+                                          : v.pscal + (size_t)(idx - v.scal_total) * v.s.scaler_stride;
+}
+
+__device__ __forceinline__ unsigned int blo_load_scaler(const BloView &v, int idx, unsigned int site)
+{
+  return idx < 0 ? 0u : __ldcg(blo_scal_ptr(v, idx) + site);
+}
+
+template <int C>
+__device__ __forceinline__ double *blo_mat_ptr(const BloView &v, unsigned int idx)
+{
+  return idx < v.mat_total ? v.s.pmat + (size_t)idx * C * 16
+                           : v.pmat + (size_t)(idx - v.mat_total) * C * 16;
+}
+
+template <int C>
+__device__ __forceinline__ void blo_load_matrix(const BloView &v, unsigned int idx, int cat, double m[16])
+{
+  const double *pm = blo_mat_ptr<C>(v, idx) + cat * 16;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) ld256_cg(pm + 4 * i, m + 4 * i);
+}
+
+// ---- tile bodies (T = kSitesPerPass*C threads, tile = kTileSites sites) --------
+
+// one CLV update on one tile: LIBPLL/core_partials_avx.c:366-529 (as partials_kernel)
+template <int C>
+__device__ __forceinline__ void blo_op_tile(const BloView &v, const BloStep &st, unsigned int tile)
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  double lm[16], rm[16];
+  blo_load_matrix<C>(v, st.b_mat, cat, lm);
+  blo_load_matrix<C>(v, st.c_mat, cat, rm);
+  double *dst = const_cast<double *>(blo_clv_ptr<C>(v, st.a_clv));
+  unsigned int *sdst = st.a_scal >= 0 ? blo_scal_ptr(v, st.a_scal) : nullptr;
+#pragma unroll 1
+  for (int half = 0; half < kPasses; half += 2)
+  {
+    double l[2][4], r[2][4], p[2][4];
+    unsigned int sc[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      const unsigned int site = min(site0 + (half + j) * kSitesPerPass, v.s.sites - 1);
+      blo_load_entry<C>(v, st.b_clv, site, cat, l[j]);
+      blo_load_entry<C>(v, st.c_clv, site, cat, r[j]);
+      sc[j] = blo_load_scaler(v, st.b_scal, site) + blo_load_scaler(v, st.c_scal, site);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      combine_entry(lm, rm, l[j], r[j], p[j]);
+      const unsigned int site = site0 + (half + j) * kSitesPerPass;
+      bool small = (p[j][0] < PT_SCALE_THRESHOLD) & (p[j][1] < PT_SCALE_THRESHOLD) &
+                   (p[j][2] < PT_SCALE_THRESHOLD) & (p[j][3] < PT_SCALE_THRESHOLD);
+      small = site_all<C>(small) && sdst != nullptr;
+      if (small)
+      {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) p[j][i] = __dmul_rn(p[j][i], PT_SCALE_FACTOR);
+      }
+      if (site < v.s.sites)
+      {
+        st256(dst + ((size_t)site * C + cat) * 4, p[j]);
+        if (cat == 0 && sdst) sdst[site] = sc[j] + (small ? 1u : 0u);
+      }
+    }
+  }
+}
+
+// sumtable of one edge on one tile (as sumtable_kernel)
+template <int C>
+__device__ __forceinline__ void blo_sumtable_tile(const BloView &v, const ModelConst &m,
+                                                  unsigned int pclv, unsigned int cclv,
+                                                  double *sumtable, unsigned int tile)
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  double p[kPasses][4], c[kPasses][4];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = min(site0 + ps * kSitesPerPass, v.s.sites - 1);
+    blo_load_entry<C>(v, pclv, site, cat, p[ps]);
+    blo_load_entry<C>(v, cclv, site, cat, c[ps]);
+  }
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = site0 + ps * kSitesPerPass;
+    double out[4];
+    sumtable_entry<C>(m, p[ps], c[ps], out);
+    if (site < v.s.sites) st256(sumtable + ((size_t)site * C + cat) * 4, out);
+  }
+}
+
+// edge log-likelihood of one tile (as edge_lnl_kernel); returns this thread's share
+template <int C>
+__device__ __forceinline__ double blo_lnl_tile(const BloView &v, const ModelConst &m, const BloEdge &e,
+                                               unsigned int tile)
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  double pm[16];
+  blo_load_matrix<C>(v, e.mat, cat, pm);
+  double p[kPasses][4], c[kPasses][4];
+  unsigned int sc[kPasses];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = min(site0 + ps * kSitesPerPass, v.s.sites - 1);
+    blo_load_entry<C>(v, e.p_clv, site, cat, p[ps]);
+    blo_load_entry<C>(v, e.c_clv, site, cat, c[ps]);
+    sc[ps] = blo_load_scaler(v, e.p_scal, site) + blo_load_scaler(v, e.c_scal, site);
+  }
+  double acc = 0.0;
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int site = site0 + ps * kSitesPerPass;
+    double f[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      f[i] = __dmul_rn(__dmul_rn(m.freqs[i], dot4(pm + 4 * i, c[ps])), p[ps][i]);
+    const double tk = __dadd_rn(__dadd_rn(f[0], f[1]), __dadd_rn(f[2], f[3]));
+    const double term = (tk > 0.0) ? __dmul_rn(tk, m.rate_weight) : 0.0;
+    double terma = term;
+#pragma unroll
+    for (int k = 1; k < C; ++k)
+      terma = __dadd_rn(terma, __shfl_down_sync(0xffffffffu, term, k, C));
+    if (cat == 0 && site < v.s.sites)
+    {
+      double lk = log(terma);
+      if (sc[ps]) lk = __dadd_rn(lk, __dmul_rn((double)sc[ps], m.log_scale_thr));
+      acc = __dadd_rn(acc, lk);
+    }
+  }
+  return acc;
+}
+
+// ---- the persistent kernel ----------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel(BloArgs a)
+{
+  constexpr int T = kSitesPerPass * C;
+  cg::grid_group grid = cg::this_grid();
+  extern __shared__ __align__(16) double ring[];
+  __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  const int cat = threadIdx.x % C;
+
+  NewtonArgs na{};
+  na.m = a.m;
+  na.sumtables = a.sumtables;
+  na.entry_stride = a.entry_stride;
+  na.sclr = nullptr;
+  na.st = a.nst;
+  na.partials = a.partials;
+  na.sites = a.sites; na.B = a.B; na.ntiles = a.ntiles; na.chunk_tiles = a.chunk_tiles;
+  na.nchunks = a.nchunks; na.max_iter = a.max_newton;
+  na.eps = a.xtol; na.lambda = 0.0; na.want_lnl = 0; na.mode = 1;
+  na.xmin = a.xmin; na.xmax = a.xmax; na.lnl_margin = 0.0; na.vec_end = a.vec_end;
+
+  auto live = [&](unsigned int e) {
+    return __ldcg(&a.cand[e].active) && !__ldcg(&a.cand[e].failed);
+  };
+
+  // edge log-likelihood of every candidate for which want(e) holds -> store(e, value)
+  auto lnl_phase = [&](const BloEdge *edges, auto want, auto store) {
+    for (unsigned int w = blockIdx.x; w < a.B * a.ntiles; w += gridDim.x)
+    {
+      const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+      if (!want(e)) continue;
+      const double part = block_sum<T>(blo_lnl_tile<C>(a.v, a.m, edges[e], tile), red);
+      if (threadIdx.x == 0) a.tile_partials[(size_t)e * a.ntiles + tile] = part;
+    }
+    grid.sync();
+    for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+    {
+      if (!want(e)) continue;
+      double acc = 0.0;
+      for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
+        acc = __dadd_rn(acc, __ldcg(a.tile_partials + (size_t)e * a.ntiles + t));
+      acc = block_sum<T>(acc, red);
+      if (threadIdx.x == 0) store(e, acc);
+    }
+    grid.sync();
+  };
+
+  auto run_step = [&](unsigned int k) {
+    const BloStep *row = a.steps + (size_t)k * a.B;
+    const int type = a.step_type[k];
+    if (type == BLO_OP)
+    {
+      for (unsigned int w = blockIdx.x; w < a.B * a.ntiles; w += gridDim.x)
+      {
+        const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+        const BloStep st = row[e];
+        if (st.type == BLO_OP && live(e)) blo_op_tile<C>(a.v, st, tile);
+      }
+      grid.sync();
+      return;
+    }
+    if (type != BLO_OPT) return;
+    // (1) arm the Newton state, build the sumtables
+    for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+    {
+      if (threadIdx.x != 0) continue;
+      NewtonState ns{};
+      const BloStep st = row[e];
+      if (st.type == BLO_OPT && live(e))
+      {
+        double guess = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
+        if (guess < a.xmin || guess > a.xmax) guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
+        ns.len = guess;
+      }
+      else
+        ns.done = 1;
+      a.nst[e] = ns;
+    }
+    for (unsigned int w = blockIdx.x; w < a.B * a.ntiles; w += gridDim.x)
+    {
+      const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+      const BloStep st = row[e];
+      if (st.type == BLO_OPT && live(e))
+        blo_sumtable_tile<C>(a.v, a.m, st.a_clv, st.b_clv, a.sumtables + (size_t)e * a.entry_stride, tile);
+    }
+    grid.sync();
+    // (2) safeguarded Newton, all candidates in lock step (as newton_kernel, mode 1)
+    for (unsigned int it = 0; it < a.max_newton; ++it)
+    {
+      for (unsigned int w = blockIdx.x; w < a.B * a.nchunks; w += gridDim.x)
+      {
+        const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
+        if (__ldcg(&a.nst[e].done)) continue;
+        double dg[4][3];
+        diag_regs<C>(a.m, __ldcg(&a.nst[e].len), cat, dg);
+        double out[3] = {0.0, 0.0, 0.0};
+        LnlProd lp;
+        const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
+        sweep_chunk<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
+        const double s1 = block_sum<T>(out[0], red);
+        const double s2 = block_sum<T>(out[1], red);
+        if (threadIdx.x == 0)
+        {
+          a.partials[(size_t)w * 3 + 0] = s1;
+          a.partials[(size_t)w * 3 + 1] = s2;
+        }
+      }
+      grid.sync();
+      for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+      {
+        if (__ldcg(&a.nst[e].done)) continue;
+        double a1 = 0.0, a2 = 0.0;
+        for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+        {
+          a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 0));
+          a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 1));
+        }
+        a1 = block_sum<T>(a1, red);
+        a2 = block_sum<T>(a2, red);
+        if (threadIdx.x == 0) newton_scalar_update(na, e, a1, a2, 0.0);
+      }
+      grid.sync();
+      int running = 0;
+      for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= !__ldcg(&a.nst[e].done);
+      if (!__syncthreads_or(running)) break;
+    }
+    // (3) accept the result: length slot + private P matrix (pll_optimize.c:824-868)
+    for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+    {
+      const BloStep st = row[e];
+      if (st.type != BLO_OPT || !live(e)) continue;
+      const int status = __ldcg(&a.nst[e].status);
+      const double neu = __ldcg(&a.nst[e].len);
+      const double old = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
+      if (status != 0)
+      {
+        if (threadIdx.x == 0) a.cand[e].failed = 1;
+        continue;
+      }
+      __syncthreads();  // everybody has read the old length before thread 0 replaces it
+      if (fabs(old - neu) > 1e-10 && threadIdx.x < C)
+        pmatrix_block(a.m, neu, threadIdx.x, blo_mat_ptr<C>(a.v, st.b_mat) + threadIdx.x * 16);
+      if (threadIdx.x == 0)
+      {
+        a.lens[(size_t)e * a.NL + st.slot] = neu;
+        a.cand[e].newton_evals += __ldcg(&a.nst[e].iters);
+      }
+    }
+    grid.sync();
+  };
+
+  // private P matrices at the start lengths
+  for (unsigned int w = blockIdx.x * T + threadIdx.x; w < a.B * a.NL * C; w += gridDim.x * T)
+  {
+    const unsigned int c = w % C, slot = (w / C) % a.NL, e = w / (C * a.NL);
+    pmatrix_block(a.m, a.lens[(size_t)e * a.NL + slot], c,
+                  a.v.pmat + ((size_t)(e * a.NL + slot) * C + c) * 16);
+  }
+  grid.sync();
+  for (unsigned int k = 0; k < a.n_pro; ++k) run_step(k);
+
+  // lnL before the first smoothing (pll_optimize.c:1000-1007)
+  lnl_phase(a.smooth_edge, [&](unsigned int) { return true; },
+            [&](unsigned int e, double v) { a.cand[e].lnl = v; });
+
+  for (unsigned int sm = 0; sm < a.smoothings; ++sm)
+  {
+    // the first smoothing still reads CLVs the engine holds; from the second on every
+    // CLV and matrix the body has touched is the candidate's private copy
+    for (unsigned int k = 0; k < a.n_body; ++k) run_step(a.n_pro + (sm ? a.n_body : 0u) + k);
+    lnl_phase(a.smooth_edge, live, [&](unsigned int e, double now) {
+      BloCand c = a.cand[e];
+      // pll_optimize.c:1058-1076
+      if (!(now - c.lnl > now * 1e-14))
+        c.active = 0;
+      else
+      {
+        c.smoothings += 1;
+        if (fabs(now - c.lnl) < a.tolerance || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
+      }
+      c.lnl = now;
+      a.cand[e] = c;
+    });
+    int running = 0;
+    for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= live(e);
+    if (!__syncthreads_or(running)) break;
+  }
+
+  // Partition::LogLikelihood(node) on whatever state the candidate ended in
+  lnl_phase(a.final_edge, [&](unsigned int) { return true; },
+            [&](unsigned int e, double v) { a.cand[e].final_lnl = v; });
+}
+
+} // namespace ptgpu

@@ -297,15 +297,9 @@ __global__ void tip_encode_kernel(const unsigned char *__restrict__ raw, uint8_t
 // (LIBPLL/core_pmatrix_avx.c:42-310).  One thread per (branch, category).
 // lengths/indices live in device memory so that the Newton kernel's result
 // can feed this kernel without a host round trip.
-template <int C>
-__global__ void pmatrix_kernel(DevState s, ModelConst m, const unsigned int *idx,
-                               const double *len, unsigned int count)
+// one (branch, category) block of 16 doubles
+__device__ __forceinline__ void pmatrix_block(const ModelConst &m, double bl, unsigned int c, double *pm)
 {
-  const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= count * C) return;
-  const unsigned int b = t / C, c = t % C;
-  const double bl = len[b];
-  double *pm = s.pmat + ((size_t)idx[b] * C + c) * 16;
   if (bl == 0.0)
   {
 #pragma unroll
@@ -332,6 +326,16 @@ __global__ void pmatrix_kernel(DevState s, ModelConst m, const unsigned int *idx
     }
     st256(pm + 4 * i, row);
   }
+}
+
+template <int C>
+__global__ void pmatrix_kernel(DevState s, ModelConst m, const unsigned int *idx,
+                               const double *len, unsigned int count)
+{
+  const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count * C) return;
+  const unsigned int b = t / C, c = t % C;
+  pmatrix_block(m, len[b], c, s.pmat + ((size_t)idx[b] * C + c) * 16);
 }
 
 // ------------------------------------------------------------ kernel 1

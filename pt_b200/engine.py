@@ -185,6 +185,27 @@ class Engine:
             st.ctypes.data_as(C.POINTER(C.c_int))))
         return lens, lnl, st
 
+    def optimize_local_batch(self, prog, bl_min=1e-4, bl_max=100.0, tolerance=1e-6, smoothings=32):
+        """all NNI candidates of a tree through pllmod_opt_optimize_branch_lengths_local;
+        `prog` is a pt_b200.local_blo.Program.  Returns (lengths [B][NL], lnl, status,
+        smoothings)."""
+        n = prog.count
+        types = np.ascontiguousarray(prog.step_types, dtype=np.int32)
+        steps = np.ascontiguousarray(prog.steps)
+        se = np.ascontiguousarray(prog.smooth_edges); fe = np.ascontiguousarray(prog.final_edges)
+        l0 = np.ascontiguousarray(prog.lengths0, dtype=np.float64)
+        lens = np.empty_like(l0); lnl = np.empty(n)
+        st = np.zeros(n, dtype=np.int32); sm = np.zeros(n, dtype=np.int32)
+        ip = C.POINTER(C.c_int)
+        self._chk(self.lib.ptgpu_optimize_local_batch(
+            self.h, C.c_uint(n), C.c_uint(prog.n_private_clvs), C.c_uint(prog.n_lengths),
+            C.c_uint(prog.n_prologue), C.c_uint(prog.n_body), types.ctypes.data_as(ip),
+            steps.ctypes.data_as(C.c_void_p), se.ctypes.data_as(C.c_void_p),
+            fe.ctypes.data_as(C.c_void_p), _d(l0), C.c_double(bl_min), C.c_double(bl_max),
+            C.c_double(tolerance), C.c_uint(smoothings), _d(lens), _d(lnl),
+            st.ctypes.data_as(ip), sm.ctypes.data_as(ip)))
+        return lens, lnl, st, sm
+
     # --- test hooks -----------------------------------------------------------
     def get_clv(self, idx):
         out = np.empty(self.sites * self.cats * 4)
