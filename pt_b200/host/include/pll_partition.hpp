@@ -107,7 +107,11 @@ class Partition
     double length;       // optimised length of the central branch
     double lnl;          // log-likelihood at that length
   };
-  std::vector<NniScore> ScoreNniNeighborhood(pll_utree_t* tree);
+  // radius >= 1: BranchNeighborhoodOptimizer semantics instead
+  // (src/move_tester/branch_neighborhood_optimizer.cpp:27-80: pll-modules' local
+  // branch-length optimisation around the moved edge, then the log-likelihood);
+  // `length` is then the optimised length of the central branch.
+  std::vector<NniScore> ScoreNniNeighborhood(pll_utree_t* tree, int radius = 0);
 
   int device() const { return device_; }
   ptgpu_engine* engine() { return engine_; }
@@ -121,6 +125,10 @@ class Partition
   void AllocateScratchBuffers();
   void Check(int rc) const;
   double MapLogPrior(pll_unode_t* tree);
+  unsigned int DirectionalClv(const pll_unode_t* record) const;
+  int DirectionalScaler(const pll_unode_t* record) const;
+  void UpdateDirectionalClvs(pll_utree_t* tree);
+  std::vector<NniScore> ScoreNniNeighborhoodLocal(pll_utree_t* tree, int radius);
   double LocalBranchOptimization(pll_unode_t* tree, double bl_min, double bl_max,
                                  double tolerance, int smoothings, int radius);
   bool OptimizeEdgeBounded(pll_unode_t* edge, double bl_min, double bl_max,

@@ -1,0 +1,96 @@
+// pt_b200/host/ptw/ptw_batched.cpp -- ptw_threads with batched move testing.
+//
+// Same command line, same inputs and the same three output tables as the
+// reference's driver (/root/reference/src/ptw_threads.cpp:33-98); the one difference
+// is the move tester: for --optimization-radius >= 0 the wanderers get a
+// pt::move_tester::BatchedNeighborhood, which scores a tree's whole NNI
+// neighbourhood in one engine call instead of one move at a time.  Everything else
+// (option parsing, guru, wanderers, authority, tables) is pt's own code, linked
+// unchanged.
+#include <cstdio>
+#include <exception>
+#include <fstream>
+#include <iostream>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <libpll/pll.h>
+#include <model.hpp>
+#include <pll_partition.hpp>
+#include <pll_util.hpp>
+
+#include "batched_neighborhood.hpp"
+#include "compressed_tree.hpp"
+#include "guru.hpp"
+#include "options.hpp"
+
+namespace {
+
+// one "<lnl>\t<newick>" line per table entry
+void DumpTable(pt::TreeTable& table, const std::string& path)
+{
+  if (path.empty()) return;
+  std::ofstream out(path);
+  if (!out) throw std::invalid_argument("could not open " + path + " for writing");
+  auto locked = table.lock_table();
+  for (auto& entry : locked) out << entry.second << "\t" << entry.first << "\n";
+}
+
+struct TreeSet {
+  std::vector<pll_utree_t*> trees;
+  ~TreeSet()
+  {
+    for (pll_utree_t* t : trees) pll_utree_destroy(t, pt::pll::cb_erase_data);
+  }
+};
+
+int Run(int argc, const char* argv[])
+{
+  pt::Options options = pt::ParseArguments(argc, argv);
+
+  std::shared_ptr<const pt::move_tester::BatchedNeighborhood> batched;
+  if (options.optimization_radius >= 0) {
+    batched = std::make_shared<pt::move_tester::BatchedNeighborhood>(options);
+    options.move_tester = batched;
+  }
+
+  TreeSet input;
+  input.trees = pt::pll::ParseMultiNewick(options.newick_path);
+  if (input.trees.empty())
+    throw std::invalid_argument("No valid trees found in " + options.newick_path);
+
+  std::vector<std::string> labels, sequences;
+  pt::pll::ParseFasta(options.fasta_path, input.trees[0]->tip_count, labels, sequences);
+  pt::CompressedTree::BuildDictionary(labels);
+  const pt::pll::Model model = pt::pll::ParseRaxmlInfo(options.raxml_path, options.rate_categories);
+
+  pt::Guru guru(options, input.trees, model, labels, sequences);
+  guru.Start();
+  guru.Wait(options.poll_ms);
+  if (!options.skip_filtering) guru.FilterGoodTreeTable();
+
+  DumpTable(guru.GetGoodTreeTable(), options.good_trees_path);
+  DumpTable(guru.GetVisitedTreeTable(), options.visited_trees_path);
+  DumpTable(guru.GetTestedTreeTable(), options.tested_trees_path);
+
+  if (batched) {
+    const auto stats = batched->Statistics();
+    std::fprintf(stderr, "batched move testing: %llu moves answered from %llu engine batches\n",
+                 static_cast<unsigned long long>(stats.second),
+                 static_cast<unsigned long long>(stats.first));
+  }
+  return 0;
+}
+
+} // namespace
+
+int main(int argc, const char* argv[])
+{
+  try {
+    return Run(argc, argv);
+  } catch (const std::exception& e) {
+    std::cerr << "ptw_batched: " << e.what() << "\n";
+    return 1;
+  }
+}

@@ -444,21 +444,29 @@ double Partition::OptimizeAllBranchesAndModel(pll_unode_t*, bool)
 // Batched NNI neighbourhood (the north-star path): all candidates of one
 // Wanderer::QueueMoves in one engine call.
 // ---------------------------------------------------------------------------
-std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree)
+// directional buffer of an inner-node record: the CLV of its node seen from
+// record->back, kept for all three records of every inner node
+unsigned int Partition::DirectionalClv(const pll_unode_t* r) const
+{
+  return r->next ? tip_node_count_ + directional_base_ + (r->node_index - tip_node_count_)
+                 : r->clv_index;
+}
+
+int Partition::DirectionalScaler(const pll_unode_t* r) const
+{
+  return r->next ? static_cast<int>(directional_base_ + (r->node_index - tip_node_count_)) : -1;
+}
+
+// All P matrices at the tree's current lengths and all 3(n-2) directional CLVs
+// (one engine call each).
+void Partition::UpdateDirectionalClvs(pll_utree_t* tree)
 {
   if (!directional_base_)
     throw std::logic_error("directional CLV buffers were disabled (PTGPU_NO_DIRECTIONAL)");
   const unsigned int tips = tip_node_count_;
   const unsigned int inner = inner_node_count();
-
-  // directional buffer of an inner-node record: the CLV of its node seen from
-  // record->back, kept for all three records of every inner node
-  auto dir_clv = [&](const pll_unode_t* r) -> unsigned int {
-    return r->next ? tips + directional_base_ + (r->node_index - tips) : r->clv_index;
-  };
-  auto dir_scaler = [&](const pll_unode_t* r) -> int {
-    return r->next ? static_cast<int>(directional_base_ + (r->node_index - tips)) : -1;
-  };
+  auto dir_clv = [&](const pll_unode_t* r) { return DirectionalClv(r); };
+  auto dir_scaler = [&](const pll_unode_t* r) { return DirectionalScaler(r); };
 
   // all P matrices at the tree's current lengths
   std::vector<unsigned int> midx;
@@ -516,6 +524,18 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tr
     schedule(n->next->next);
   }
   Check(ptgpu_update_partials(engine_, plan.data(), static_cast<unsigned int>(plan.size())));
+}
+
+std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree, int radius)
+{
+  if (radius < 0) throw std::invalid_argument("optimization radius must not be negative");
+  UpdateDirectionalClvs(tree);
+  if (radius > 0) return ScoreNniNeighborhoodLocal(tree, radius);
+
+  const unsigned int tips = tip_node_count_;
+  const unsigned int inner = inner_node_count();
+  auto dir_clv = [&](const pll_unode_t* r) { return DirectionalClv(r); };
+  auto dir_scaler = [&](const pll_unode_t* r) { return DirectionalScaler(r); };
 
   // candidates in QueueMoves order (src/wanderer.cpp:242-285); after
   // pll_utree_nni(p, type) (LIBPLL/utree_moves.c:72-109) p's node joins
@@ -569,6 +589,267 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tr
     out[i].lnl = lnl[i];
     if (map_mode_)  // swap the central branch's prior term for the one at its new length
       out[i].lnl += prior + kMapLambda * out[i].node->length - kMapLambda * len[i];
+  }
+  return out;
+}
+
+// ---------------------------------------------------------------------------
+// radius >= 1: every candidate through pll-modules' local branch-length
+// optimisation, all candidates in one persistent kernel
+// (ptgpu_optimize_local_batch).  The host's part is integer bookkeeping: unroll
+// recomp_iterative's recursion (PLLMOD/optimize/pll_optimize.c:771-934) around the
+// moved edge into a flat step list of one common shape.
+// ---------------------------------------------------------------------------
+namespace {
+
+struct ClvRef { bool is_private; unsigned int index; int scaler; };
+struct MatRef { bool is_private; unsigned int index; };
+struct SymStep {
+  int type;
+  ClvRef a, b, c;
+  MatRef bm, cm;
+  unsigned int slot;
+};
+
+// steps of recomp_iterative(., radius): one optimisation, and per level three
+// re-orientations around two recursive calls
+size_t RecompSize(int radius)
+{
+  size_t n = 1;
+  for (int r = 0; r < radius; ++r) n = 4 + 2 * n;
+  return n;
+}
+
+void RecompTypes(int radius, std::vector<int>& out)
+{
+  out.push_back(PTGPU_BLO_OPT);
+  if (!radius) return;
+  out.push_back(PTGPU_BLO_OP);
+  RecompTypes(radius - 1, out);
+  out.push_back(PTGPU_BLO_OP);
+  RecompTypes(radius - 1, out);
+  out.push_back(PTGPU_BLO_OP);
+}
+
+// symbolic program of one candidate; the reference keeps ONE CLV buffer per node,
+// so "the CLV of a record's node" is the candidate's private copy once the
+// recursion has written it, and the engine's directional CLV before that
+class CandidateProgram {
+ public:
+  CandidateProgram(const Partition& part,
+                   unsigned int (Partition::*clv)(const pll_unode_t*) const,
+                   int (Partition::*scaler)(const pll_unode_t*) const)
+      : part_(part), dir_clv_(clv), dir_scaler_(scaler) {}
+
+  void ForgetSteps() { steps.clear(); private_nodes_.clear(); }
+
+  ClvRef Clv(const pll_unode_t* r) const
+  {
+    if (!r->next) return ClvRef{false, r->clv_index, -1};
+    for (size_t j = 0; j < private_nodes_.size(); ++j)
+      if (private_nodes_[j] == r->clv_index) return ClvRef{true, static_cast<unsigned int>(j), 0};
+    return ClvRef{false, (part_.*dir_clv_)(r), (part_.*dir_scaler_)(r)};
+  }
+
+  ClvRef Own(const pll_unode_t* r)
+  {
+    for (size_t j = 0; j < private_nodes_.size(); ++j)
+      if (private_nodes_[j] == r->clv_index) return ClvRef{true, static_cast<unsigned int>(j), 0};
+    private_nodes_.push_back(r->clv_index);
+    return ClvRef{true, static_cast<unsigned int>(private_nodes_.size() - 1), 0};
+  }
+
+  MatRef Matrix(const pll_unode_t* r) const
+  {
+    for (size_t k = 0; k < slot_edges.size(); ++k)
+      if (slot_edges[k] == r->pmatrix_index) return MatRef{true, static_cast<unsigned int>(k)};
+    return MatRef{false, r->pmatrix_index};
+  }
+
+  unsigned int Slot(const pll_unode_t* r)
+  {
+    for (size_t k = 0; k < slot_edges.size(); ++k)
+      if (slot_edges[k] == r->pmatrix_index) return static_cast<unsigned int>(k);
+    slot_edges.push_back(r->pmatrix_index);
+    lengths.push_back(r->length);
+    return static_cast<unsigned int>(slot_edges.size() - 1);
+  }
+
+  // update_partials_and_scalers(parent, right, left), pll_optimize.c:741-768
+  void Op(const pll_unode_t* parent, const pll_unode_t* c1, const pll_unode_t* c2)
+  {
+    SymStep st{};
+    st.type = PTGPU_BLO_OP;
+    st.a = Own(parent);
+    st.b = Clv(c1->back);
+    st.bm = Matrix(c1->back);
+    st.c = Clv(c2->back);
+    st.cm = Matrix(c2->back);
+    steps.push_back(st);
+  }
+
+  void Opt(const pll_unode_t* r)
+  {
+    SymStep st{};
+    st.type = PTGPU_BLO_OPT;
+    st.slot = Slot(r);
+    st.a = Clv(r);
+    st.b = Clv(r->back);
+    st.bm = MatRef{true, st.slot};
+    steps.push_back(st);
+  }
+
+  void Nop(size_t n)
+  {
+    SymStep st{};
+    st.type = PTGPU_BLO_NOP;
+    steps.insert(steps.end(), n, st);
+  }
+
+  void Recomp(const pll_unode_t* r, int radius)
+  {
+    const size_t size = RecompSize(radius);
+    if (!r) { Nop(size); return; }
+    Opt(r);
+    if (!radius) return;
+    const pll_unode_t* q = r->next;
+    if (!q) { Nop(size - 1); return; }
+    const pll_unode_t* z = q->next;
+    Op(q, r, z);
+    Recomp(q->back, radius - 1);
+    Op(z, q, r);
+    Recomp(z->back, radius - 1);
+    Op(r, z, q);
+  }
+
+  size_t private_count() const { return private_nodes_.size(); }
+
+  std::vector<SymStep> steps;
+  std::vector<unsigned int> slot_edges;  // slot -> pmatrix_index of the edge
+  std::vector<double> lengths;           // slot -> length before the optimisation
+  ClvRef smooth_parent, smooth_child, final_parent, final_child;
+  MatRef edge_matrix;
+
+ private:
+  const Partition& part_;
+  unsigned int (Partition::*dir_clv_)(const pll_unode_t*) const;
+  int (Partition::*dir_scaler_)(const pll_unode_t*) const;
+  std::vector<unsigned int> private_nodes_;  // private buffer -> clv_index of the node
+};
+
+} // namespace
+
+std::vector<Partition::NniScore> Partition::ScoreNniNeighborhoodLocal(pll_utree_t* tree, int radius)
+{
+  const unsigned int tips = tip_node_count_;
+  const unsigned int inner = inner_node_count();
+
+  std::vector<int> body;
+  RecompTypes(radius, body);
+  RecompTypes(radius - 1, body);
+  std::vector<int> types{PTGPU_BLO_OP, PTGPU_BLO_OP};
+  types.insert(types.end(), body.begin(), body.end());
+  types.insert(types.end(), body.begin(), body.end());
+
+  std::vector<NniScore> out;
+  std::vector<CandidateProgram> progs;
+  for (unsigned int i = tips; i < tips + inner; ++i) {
+    pll_unode_t* p = tree->nodes[i];
+    pll_unode_t* q = p->back;
+    if (!q->next) continue;
+    for (int type : {PLL_UTREE_MOVE_NNI_LEFT, PLL_UTREE_MOVE_NNI_RIGHT}) {
+      // the program is read off the tree WITH the move applied; the move is its own
+      // inverse (LIBPLL/utree_moves.c:60-109) and leaves the CLV flags alone
+      pll_utree_nni(p, type, nullptr);
+      CandidateProgram c(*this, &Partition::DirectionalClv, &Partition::DirectionalScaler);
+      // dry run: which edges get a private length / matrix slot
+      c.Recomp(p, radius);
+      c.Recomp(q, radius - 1);
+      c.ForgetSteps();
+      // TraversalUpdate(node, PARTIAL) after InvalidateEdgeClvs: q's node, then p's
+      c.Op(q, q->next, q->next->next);
+      c.Op(p, p->next, p->next->next);
+      // first smoothing: nodes not re-oriented yet are read from the directional
+      // CLVs; later smoothings: from the private copies the first one left behind
+      for (int pass = 0; pass < 2; ++pass) {
+        c.Recomp(p, radius);
+        c.Recomp(q, radius - 1);
+      }
+      if (c.steps.size() != types.size()) throw std::logic_error("local program shape mismatch");
+      c.smooth_parent = c.final_child = c.Clv(q);
+      c.smooth_child = c.final_parent = c.Clv(p);
+      c.edge_matrix = c.Matrix(p);
+      pll_utree_nni(p, type, nullptr);
+      out.push_back(NniScore{p, type, p->length, 0.0});
+      progs.push_back(std::move(c));
+    }
+  }
+  if (progs.empty()) return out;
+
+  const unsigned int count = static_cast<unsigned int>(progs.size());
+  unsigned int n_private = 1, n_lengths = 1;
+  for (const CandidateProgram& c : progs) {
+    n_private = std::max<unsigned int>(n_private, static_cast<unsigned int>(c.private_count()));
+    n_lengths = std::max<unsigned int>(n_lengths, static_cast<unsigned int>(c.lengths.size()));
+  }
+  // private index spaces (include/ptgpu.h): above the engine's own ranges
+  const unsigned int clv_total = tips + inner + (directional_base_ ? 3 * inner : 0);
+  const unsigned int scaler_total = inner + (directional_base_ ? 3 * inner : 0);
+  const unsigned int matrix_total = branch_count();
+
+  std::vector<ptgpu_blo_step_t> steps(types.size() * count);
+  std::vector<ptgpu_blo_edge_t> smooth(count), final_edge(count);
+  std::vector<double> lengths0(static_cast<size_t>(count) * n_lengths, 0.1);
+  for (unsigned int i = 0; i < count; ++i) {
+    const CandidateProgram& c = progs[i];
+    auto clv = [&](const ClvRef& r) {
+      return r.is_private ? clv_total + i * n_private + r.index : r.index;
+    };
+    auto scaler = [&](const ClvRef& r) {
+      return r.is_private ? static_cast<int>(scaler_total + i * n_private + r.index) : r.scaler;
+    };
+    auto matrix = [&](const MatRef& m) {
+      return m.is_private ? matrix_total + i * n_lengths + m.index : m.index;
+    };
+    for (size_t k = 0; k < c.lengths.size(); ++k) lengths0[i * n_lengths + k] = c.lengths[k];
+    for (size_t k = 0; k < c.steps.size(); ++k) {
+      const SymStep& st = c.steps[k];
+      ptgpu_blo_step_t& d = steps[k * count + i];
+      std::memset(&d, 0, sizeof d);
+      d.type = st.type;
+      if (st.type == PTGPU_BLO_NOP) continue;
+      d.a_clv = clv(st.a); d.a_scaler = scaler(st.a);
+      d.b_clv = clv(st.b); d.b_scaler = scaler(st.b); d.b_matrix = matrix(st.bm);
+      if (st.type == PTGPU_BLO_OP) {
+        d.c_clv = clv(st.c); d.c_scaler = scaler(st.c); d.c_matrix = matrix(st.cm);
+      }
+      d.length_slot = st.slot;
+    }
+    smooth[i] = ptgpu_blo_edge_t{clv(c.smooth_parent), scaler(c.smooth_parent), clv(c.smooth_child),
+                                 scaler(c.smooth_child), matrix(c.edge_matrix), 0};
+    final_edge[i] = ptgpu_blo_edge_t{clv(c.final_parent), scaler(c.final_parent), clv(c.final_child),
+                                     scaler(c.final_child), matrix(c.edge_matrix), 0};
+  }
+
+  std::vector<double> lengths(lengths0.size()), lnl(count);
+  std::vector<int> status(count);
+  // PLLMOD_OPT_MIN/MAX_BRANCH_LEN, EPSILON, MAX_ITER: PTPLL/pll_partition.cpp:629-637
+  Check(ptgpu_optimize_local_batch(engine_, count, n_private, n_lengths, 2,
+                                   static_cast<unsigned int>(body.size()), types.data(), steps.data(),
+                                   smooth.data(), final_edge.data(), lengths0.data(), 1.0e-4, 100.0,
+                                   EPSILON, MAX_ITER, lengths.data(), lnl.data(), status.data(),
+                                   nullptr));
+  double prior = 0.0;
+  if (map_mode_) prior = MapLogPrior(GetVirtualRoot(tree));
+  for (unsigned int i = 0; i < count; ++i) {
+    out[i].length = lengths[i * n_lengths];  // slot 0 is the central branch
+    out[i].lnl = lnl[i];
+    if (map_mode_) {  // LogLikelihood's prior (PTPLL/pll_partition.cpp:307-325) at the new lengths
+      double p = prior;
+      for (size_t k = 0; k < progs[i].lengths.size(); ++k)
+        p += kMapLambda * progs[i].lengths[k] - kMapLambda * lengths[i * n_lengths + k];
+      out[i].lnl += p;
+    }
   }
   return out;
 }

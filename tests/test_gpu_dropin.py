@@ -71,3 +71,27 @@ def test_ptw_threads_good_trees_identical(config):
     assert got["good"] == gold["good"]
     assert got["visited_sha"] == gold["visited_sha"]
     assert got["tested_sha"] == gold["tested_sha"]
+
+
+@pytest.mark.parametrize("config", ["config1", "config2"])
+def test_ptw_batched_tables_identical_and_faster(config):
+    """The same two configs through ptw_batched (pt_b200/host/ptw): the wanderer's 2(n-3)
+    EvaluateMove calls per tree are answered from ONE batched engine call (radius 0:
+    ptgpu_score_nni_batch, radius 1: ptgpu_optimize_local_batch).  The three tables must still
+    be the reference's, and the run must not be slower than the move-at-a-time drop-in."""
+    import time
+    from make_ptw_golden import run, summarise
+    seq, bat = need("ptw_threads_gpu"), need("ptw_batched")
+    with open(os.path.join(ROOT, "tests", "golden", "ptw_golden.json")) as f:
+        gold = json.load(f)[config]
+    t0 = time.time()
+    got = summarise(run(bat, gold["args"]))
+    t_batched = time.time() - t0
+    for key in ("counts", "good_topologies_sha", "visited_topologies_sha", "tested_topologies_sha",
+                "good", "visited_sha", "tested_sha"):
+        assert got[key] == gold[key], key
+    t0 = time.time()
+    run(seq, gold["args"])
+    t_sequential = time.time() - t0
+    print(f"{config}: batched {t_batched:.2f}s, move-at-a-time {t_sequential:.2f}s")
+    assert t_batched < t_sequential * 1.1
