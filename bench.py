@@ -88,6 +88,18 @@ class ClockSampler(threading.Thread):
                     samples=len(sm))
 
 
+def ncu_traffic(kernel, taxa, sites):
+    """dram__bytes_read + dram__bytes_write per launch of `kernel` from the committed
+    `ncu --set full` capture (profiles/r1_traffic.json), valid for the default workload only"""
+    if (taxa, sites) != (64, 1000000):
+        return None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return json.load(f)[kernel]["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -115,11 +127,37 @@ class RefWorker:
     call sequence for every candidate of one tree
     (src/move_tester/single_branch_optimizer.cpp:23-64)"""
 
-    def __init__(self, R, newick, labels, seqs):
+    def __init__(self, R, newick, labels, seqs, radius=0):
         self.p = R.open_mem(newick, labels, seqs, FREQS, SUBST, RATES)
         self.cands = Tree(newick).nni_candidates()
+        self.radius = radius
+        self.nrec = len(self.p.records())
+
+    def run_pass_neighborhood(self):
+        """BranchNeighborhoodOptimizer::EvaluateMove per candidate
+        (src/move_tester/branch_neighborhood_optimizer.cpp:27-80); the clone the reference
+        works on is replaced by undoing the move and restoring the changed lengths"""
+        p = self.p
+        t0 = time.perf_counter()
+        p.traversal_update(p.root, True)
+        base = [p.length(i) for i in range(self.nrec)]
+        for (pidx, kind, _, _, _) in self.cands:
+            p.nni(pidx, kind)
+            p.invalidate_edge(pidx)
+            p.traversal_update(pidx, False)
+            p.optimize_branch_neighborhood(pidx, self.radius)
+            p.traversal_update(pidx, False)
+            p.loglikelihood(pidx)
+            p.nni(pidx, kind)
+            for i in range(self.nrec):
+                if p.length(i) != base[i]:
+                    p.update_branch_length(i, base[i])
+            p.traversal_update(pidx, True)
+        return time.perf_counter() - t0
 
     def run_pass(self):
+        if self.radius > 0:
+            return self.run_pass_neighborhood()
         p = self.p
         t0 = time.perf_counter()
         p.traversal_update(p.root, True)
@@ -138,6 +176,11 @@ class RefWorker:
         self.p.close()
 
 
+def tester_name(radius):
+    return ("SingleBranchOptimizer (radius 0)" if radius == 0
+            else f"BranchNeighborhoodOptimizer (radius {radius})")
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -145,14 +188,14 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_baseline_single(taxa, sites_full, aln_sample, tree, sample_sites):
+def cpu_baseline_single(taxa, sites_full, aln_sample, tree, sample_sites, radius=0):
     from oracle.pyoracle import RefLib, have_ref
     if not have_ref():
         return None
     R = RefLib()
     labels = tree.labels()
     seqs = [bytes(aln_sample[l][:sample_sites]) for l in labels]
-    w = RefWorker(R, tree.newick(), labels, seqs)
+    w = RefWorker(R, tree.newick(), labels, seqs, radius)
     times = [w.run_pass() for _ in range(3)]
     ncand = len(w.cands)
     w.close()
@@ -181,7 +224,7 @@ def run_reference(args):
     aln = simulate(base, sample, np.random.default_rng(SEED_ALN))
     R = RefLib()
     trees = [parent_tree(args.taxa, r) for r in range(T)]
-    workers = [RefWorker(R, t.newick(), t.labels(), [bytes(aln[l]) for l in t.labels()])
+    workers = [RefWorker(R, t.newick(), t.labels(), [bytes(aln[l]) for l in t.labels()], args.radius)
                for t in trees]
     ncand = sum(len(w.cands) for w in workers)
     step_s = []
@@ -202,7 +245,7 @@ def run_reference(args):
                 vs_baseline=None, dtype="f64", data="synthetic",
                 config=dict(workload=f"synthetic {args.taxa} taxa x {args.sites} sites GTR+G4, "
                                      f"all {ncand // T} NNI candidates of one tree per thread, "
-                                     "SingleBranchOptimizer (radius 0)",
+                                     + tester_name(args.radius),
                             taxa=args.taxa, sites=args.sites, rate_cats=4),
                 cpu_baseline=dict(value=value, unit="candidates/s", cores=T, kind="reference",
                                   sample=f"{T} threads x one tree ({ncand // T} candidates) x {sample} "
@@ -259,10 +302,20 @@ def run_ours(args):
     cands = cand_array(cand_rows)
     ncand = len(cands)
 
+    prog = None
+    if args.radius > 0:
+        from pt_b200.local_blo import Program
+        prog = Program(tree, args.radius, n, nbuf, nbuf, 2 * n - 3)
+    last = {}
+
     def step():
         e.update_prob_matrices(midx, mlen)
         e.update_partials(plan)
-        return e.score_nni_batch(cands)
+        if prog is None:
+            return e.score_nni_batch(cands)
+        lens, lnl, status, sm = e.optimize_local_batch(prog)
+        last["smoothings"] = sm
+        return lens, lnl, status
 
     for _ in range(args.warmup):
         lens, lnls, status = step()
@@ -329,6 +382,17 @@ def run_ours(args):
         # sweeps that also sum the site lnL read the scaler word too; rare extra lnL-only sweeps
         newton=(passes * 128 + lnl_sweeps * 4 + final_sweeps * 132) / steps * S,
     )
+    if prog is not None:
+        # the persistent local-optimisation kernel (timed under the "newton" slot): per
+        # candidate 2 prologue CLV updates + 2 edge lnL, and per executed smoothing the body's
+        # CLV updates (396 B/site), sumtables (384 B/site), one edge lnL (268 B/site); every
+        # derivative sweep 128 B/site.  Smoothings that ended on "no improvement" are not in
+        # the counter, so this is a lower bound of the bytes (and of `achieved`).
+        body = prog.step_types[prog.n_prologue:prog.n_prologue + prog.n_body]
+        per_body = int((body == 1).sum()) * 396 + int((body == 2).sum()) * 384 + 268
+        algo = dict(partials=algo["partials"],
+                    newton=(ncand * (2 * 396 + 2 * 268) + int(last["smoothings"].sum()) * per_body
+                            + passes / steps * 128) * S)
     kernels = {}
     for k, bytes_per_launch in algo.items():
         tot_ms, nl = kt[k]
@@ -341,7 +405,7 @@ def run_ours(args):
     dom = max(kernels, key=lambda k: kernels[k]["share_of_step"])
     roof = dict(bound="hbm", kernel=dom, achieved=kernels[dom]["achieved_gbs"], peak=peak,
                 unit="GB/s", frac=kernels[dom]["achieved_gbs"] / peak, peak_source=peak_kind,
-                traffic=None)
+                traffic=ncu_traffic(dom, n, S) if prog is None else None)
     h2d = n * S + midx.nbytes + mlen.nbytes + plan.nbytes + cands.nbytes
     d2h = ncand * (8 + 8 + 4)
     line = dict(
@@ -350,7 +414,7 @@ def run_ours(args):
         higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
         config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]/[3] shape): "
                              f"per step all {ncand} NNI candidates of one parent tree per GPU, "
-                             "SingleBranchOptimizer (radius 0) semantics, incl. P matrices and "
+                             + tester_name(args.radius) + " semantics, incl. P matrices and "
                              "all directional CLVs", taxa=n, sites=S, rate_cats=4,
                     candidates_per_step_per_gpu=ncand, parallelism=f"candidate-parallel x{world}",
                     l2="inputs (>20 GB of CLVs per step) far exceed the 126 MB L2; no flush needed"),
@@ -365,7 +429,7 @@ def run_ours(args):
         lnl_checksum=float(np.sum(lnls)),
     )
     if world == 1 and not args.no_cpu_baseline:
-        cb = cpu_baseline_single(n, S, aln, tree, min(S, args.cpu_sample_sites))
+        cb = cpu_baseline_single(n, S, aln, tree, min(S, args.cpu_sample_sites), args.radius)
         if cb:
             line["cpu_baseline"] = cb
     print(json.dumps(line))
@@ -381,6 +445,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--taxa", type=int, default=64)
     ap.add_argument("--sites", type=int, default=1000000)
+    ap.add_argument("--radius", type=int, default=0,
+                    help="0: SingleBranchOptimizer semantics (the headline workload); >= 1: "
+                         "BranchNeighborhoodOptimizer semantics (BASELINE configs[1]'s tester)")
     ap.add_argument("--cpu-sample-sites", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

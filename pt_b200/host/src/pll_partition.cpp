@@ -9,7 +9,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -54,6 +56,41 @@ int pick_device()
 }
 
 int visit_all(pll_unode_t*) { return 1; }
+
+// PTGPU_HOST_STATS=1: wall time and call counts of the Partition entry points,
+// printed when a Partition dies (where does a ptw run spend its time?)
+struct HostStat { std::atomic<unsigned long long> ns{0}, calls{0}; };
+enum { kStatTraversal, kStatOptimizeBranch, kStatLogLikelihood, kStatNeighborhood, kStatAllBranches, kStatCount };
+HostStat g_stats[kStatCount];
+const char* const kStatNames[kStatCount] = {"TraversalUpdate", "OptimizeBranch", "LogLikelihood",
+                                            "ScoreNniNeighborhood", "OptimizeAllBranches(total)"};
+const bool g_stats_on = std::getenv("PTGPU_HOST_STATS") != nullptr;
+
+class StatScope {
+ public:
+  explicit StatScope(int which) : which_(which)
+  {
+    if (g_stats_on) t0_ = std::chrono::steady_clock::now();
+  }
+  ~StatScope()
+  {
+    if (!g_stats_on) return;
+    const auto dt = std::chrono::steady_clock::now() - t0_;
+    g_stats[which_].ns += std::chrono::duration_cast<std::chrono::nanoseconds>(dt).count();
+    g_stats[which_].calls += 1;
+  }
+ private:
+  int which_;
+  std::chrono::steady_clock::time_point t0_;
+};
+
+void PrintStats()
+{
+  if (!g_stats_on) return;
+  for (int k = 0; k < kStatCount; ++k)
+    std::fprintf(stderr, "[ptgpu host] %-28s %10llu calls %10.3f s\n", kStatNames[k],
+                 g_stats[k].calls.load(), g_stats[k].ns.load() * 1e-9);
+}
 
 } // namespace
 
@@ -120,7 +157,10 @@ Partition::Partition(Partition&& rhs) :
 
 Partition::~Partition()
 {
-  if (engine_) ptgpu_destroy(engine_);
+  if (engine_) {
+    PrintStats();
+    ptgpu_destroy(engine_);
+  }
 }
 
 void Partition::AllocateScratchBuffers()
@@ -199,6 +239,7 @@ double Partition::MapLogPrior(pll_unode_t* tree)
 // PTPLL/pll_partition.cpp:309-346
 double Partition::LogLikelihood(pll_unode_t* tree, double* per_site_lnl)
 {
+  StatScope stat(kStatLogLikelihood);
   double lnl = 0.0;
   Check(ptgpu_compute_edge_loglikelihood(engine_, tree->clv_index, tree->scaler_index,
                                          tree->back->clv_index, tree->back->scaler_index,
@@ -229,6 +270,7 @@ double Partition::LogMarginalLikelihood(pll_unode_t*)
 // PTPLL/pll_partition.cpp:348-393
 unsigned int Partition::TraversalUpdate(pll_unode_t* root, TraversalType type)
 {
+  StatScope stat(kStatTraversal);
   unsigned int traversal_size = 0;
   int ok;
   if (type == TraversalType::FULL)
@@ -266,6 +308,7 @@ void Partition::UpdateBranchLength(pll_unode_t* node, double length)
 // device-resident sequence; only the optimised length comes back.
 double Partition::OptimizeBranch(pll_unode_t* node)
 {
+  StatScope stat(kStatOptimizeBranch);
   pll_unode_t* child = node->back;
   double len = node->length;
   Check(ptgpu_optimize_branch(engine_, node->clv_index, node->scaler_index, child->clv_index,
@@ -302,6 +345,7 @@ void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
 // PTPLL/pll_partition.cpp:542-582
 void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 {
+  StatScope stat(kStatAllBranches);
   TraversalUpdate(tree, TraversalType::PARTIAL);
 
   if (use_pllmod) {
@@ -529,6 +573,7 @@ void Partition::UpdateDirectionalClvs(pll_utree_t* tree)
 std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree, int radius)
 {
   if (radius < 0) throw std::invalid_argument("optimization radius must not be negative");
+  StatScope stat(kStatNeighborhood);
   UpdateDirectionalClvs(tree);
   if (radius > 0) return ScoreNniNeighborhoodLocal(tree, radius);
 
