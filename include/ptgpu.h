@@ -207,6 +207,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
 #define PTGPU_BLO_NOP 0
 #define PTGPU_BLO_OP 1
 #define PTGPU_BLO_OPT 2
+#define PTGPU_BLO_MAT 3 /* ptgpu_optimize_all_branches only: P matrix b_matrix at the length in length_slot */
 typedef struct ptgpu_blo_step
 {
   int type;
@@ -235,6 +236,42 @@ int ptgpu_optimize_local_batch(ptgpu_engine *e, unsigned int count, unsigned int
                                double bl_min, double bl_max, double tolerance,
                                unsigned int smoothings, double *lengths_out, double *lnl_out,
                                int *status_out, int *smoothings_out);
+
+/* Partition::OptimizeAllBranches (lib/libptpll/src/pll_partition.cpp:542-582, the
+   non-pllmod branch) as ONE persistent kernel instead of ~10 engine calls per
+   branch and pass.  The reference's procedure is: orient the CLVs towards the
+   tree's node, lnL; then passes of OptimizeAllBranchesOnce (:490-540: for every
+   node in post-order a PARTIAL TraversalUpdate towards it and OptimizeBranch,
+   :408-488) each followed by a PARTIAL traversal back and lnL, while the lnL
+   still moves by more than `epsilon` (at most 1 + max_passes - 1 passes).
+   Which CLVs and matrices each traversal recomputes depends only on the
+   orientation flags, so the caller (who owns the flags) unrolls the procedure
+   into steps on the ENGINE'S OWN buffers -- unlike ptgpu_optimize_local_batch
+   nothing is private here, the engine ends in the state the call sequence
+   would have left:
+     PTGPU_BLO_MAT  matrix b_matrix := P(length of edge length_slot); b_matrix == length_slot
+     PTGPU_BLO_OP   CLV update, as ptgpu_update_partials
+     PTGPU_BLO_OPT  OptimizeBranch on the edge (a = node, b = node->back, matrix
+                    b_matrix == length_slot): sumtable, <= max_iter Newton steps
+                    with the reference's stopping rules and exponential prior
+                    rate map_lambda (0 = ML), new length into the slot, matrix
+                    recomputed
+   steps[0 .. n_prologue) run once (the first traversal); then pass k runs rows
+   n_prologue + min(k, n_bodies-1) * n_body .. + n_body (the traversals of a pass
+   depend on the orientation the previous pass left behind; from some pass on
+   they repeat).  Length slots are the engine's matrix indices; lengths0 /
+   lengths_out have prob_matrices entries.  lnl_edge is the edge of
+   Partition::LogLikelihood(tree); with n_prior > 0 every lnL also gets the MAP
+   prior terms of the listed edges, added in that order.  *lnl_out is the last
+   lnL, *passes_out the passes run; *status_out 0, 1 (d1 not finite) or 2 (d2),
+   in which case PTGPU_ERR_NOT_FINITE is returned as well. */
+int ptgpu_optimize_all_branches(ptgpu_engine *e, unsigned int n_prologue, unsigned int n_body,
+                                unsigned int n_bodies, const ptgpu_blo_step_t *steps,
+                                const ptgpu_blo_edge_t *lnl_edge, const double *lengths0,
+                                const unsigned int *prior_edges, unsigned int n_prior,
+                                unsigned int max_iter, double epsilon, double map_lambda,
+                                unsigned int max_passes, double *lengths_out, double *lnl_out,
+                                int *status_out, int *passes_out);
 
 /* ---- site shards: one engine per GPU holds a contiguous range
    of the alignment's sites.  CLV updates, P matrices and sumtables are purely

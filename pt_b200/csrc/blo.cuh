@@ -37,7 +37,7 @@ struct BloView
   double *pmat;             // [private matrices][C][16]
 };
 
-enum : int { BLO_NOP = 0, BLO_OP = 1, BLO_OPT = 2 };
+enum : int { BLO_NOP = 0, BLO_OP = 1, BLO_OPT = 2, BLO_MAT = 3 };
 
 struct BloStep
 {
@@ -90,10 +90,20 @@ struct BloArgs
   double *tile_partials;     // [B][ntiles] edge-lnL tile partials
   const int *step_type;      // [n_pro + 2 n_body] the (uniform) type of each step position
   unsigned int B, NL, n_pro, n_body;
+  unsigned int n_bodies;     // body variants: smoothing k runs variant min(k, n_bodies - 1)
   unsigned int sites, ntiles, chunk_tiles, nchunks;
   unsigned int smoothings, max_newton;
   double xmin, xmax, xtol, tolerance;
   unsigned long long vec_end;
+  // what the procedure is:
+  //  0  pllmod_opt_optimize_branch_lengths_local (PLLMOD/optimize/pll_optimize.c:969-1091):
+  //     safeguarded Newton per edge (:771-827), stop on a worse or converged lnL
+  //  1  pt's Partition::OptimizeAllBranches (PTPLL/pll_partition.cpp:542-582): plain Newton of
+  //     Partition::OptimizeBranch (:408-488), stop when |lnL change| <= tolerance
+  int procedure;
+  double lambda;             // MAP prior rate (procedure 1), 0 = ML
+  const unsigned int *prior_slots;  // length slots whose prior terms LogLikelihood adds, in its order
+  unsigned int n_prior;
 };
 
 // ---- loaders over the combined index spaces ---------------------------------
@@ -290,7 +300,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
   na.partials = a.partials;
   na.sites = a.sites; na.B = a.B; na.ntiles = a.ntiles; na.chunk_tiles = a.chunk_tiles;
   na.nchunks = a.nchunks; na.max_iter = a.max_newton;
-  na.eps = a.xtol; na.lambda = 0.0; na.want_lnl = 0; na.mode = 1;
+  na.eps = a.xtol; na.lambda = a.lambda; na.want_lnl = 0; na.mode = a.procedure == 0 ? 1 : 0;
   na.xmin = a.xmin; na.xmax = a.xmax; na.lnl_margin = 0.0; na.vec_end = a.vec_end;
 
   auto live = [&](unsigned int e) {
@@ -314,7 +324,15 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
       for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
         acc = __dadd_rn(acc, __ldcg(a.tile_partials + (size_t)e * a.ntiles + t));
       acc = block_sum<T>(acc, red);
-      if (threadIdx.x == 0) store(e, acc);
+      if (threadIdx.x == 0)
+      {
+        // MAP: log(lambda) - lambda t per branch, added one by one in LogLikelihood's order
+        // (PTPLL/pll_partition.cpp:318-341)
+        for (unsigned int k = 0; k < a.n_prior; ++k)
+          acc = __dadd_rn(acc, __dadd_rn(log(a.lambda),
+                                         -__dmul_rn(a.lambda, __ldcg(a.lens + (size_t)e * a.NL + a.prior_slots[k]))));
+        store(e, acc);
+      }
     }
     grid.sync();
   };
@@ -333,6 +351,20 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
       grid.sync();
       return;
     }
+    if (type == BLO_MAT)
+    {
+      // P matrix of an edge at its current length (a traversal's pll_update_prob_matrices)
+      for (unsigned int w = blockIdx.x * T + threadIdx.x; w < a.B * C; w += gridDim.x * T)
+      {
+        const unsigned int e = w / C, c = w % C;
+        const BloStep st = row[e];
+        if (st.type == BLO_MAT && live(e))
+          pmatrix_block(a.m, __ldcg(a.lens + (size_t)e * a.NL + st.slot), c,
+                        blo_mat_ptr<C>(a.v, st.b_mat) + c * 16);
+      }
+      grid.sync();
+      return;
+    }
     if (type != BLO_OPT) return;
     // (1) arm the Newton state, build the sumtables
     for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
@@ -343,7 +375,8 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
       if (st.type == BLO_OPT && live(e))
       {
         double guess = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
-        if (guess < a.xmin || guess > a.xmax) guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
+        if (a.procedure == 0 && (guess < a.xmin || guess > a.xmax))
+          guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
         ns.len = guess;
       }
       else
@@ -409,11 +442,12 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
       const double old = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
       if (status != 0)
       {
-        if (threadIdx.x == 0) a.cand[e].failed = 1;
+        if (threadIdx.x == 0) a.cand[e].failed = status;
         continue;
       }
       __syncthreads();  // everybody has read the old length before thread 0 replaces it
-      if (fabs(old - neu) > 1e-10 && threadIdx.x < C)
+      // procedure 1: UpdateBranchLength always recomputes the matrix (PTPLL/pll_partition.cpp:395-406)
+      if ((a.procedure == 1 || fabs(old - neu) > 1e-10) && threadIdx.x < C)
         pmatrix_block(a.m, neu, threadIdx.x, blo_mat_ptr<C>(a.v, st.b_mat) + threadIdx.x * 16);
       if (threadIdx.x == 0)
       {
@@ -424,8 +458,9 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
     grid.sync();
   };
 
-  // private P matrices at the start lengths
-  for (unsigned int w = blockIdx.x * T + threadIdx.x; w < a.B * a.NL * C; w += gridDim.x * T)
+  // private P matrices at the start lengths (in-place programs use the engine's matrices as
+  // they are: a stale one stays stale until a step recomputes it, as in the call sequence)
+  for (unsigned int w = blockIdx.x * T + threadIdx.x; a.v.pmat && w < a.B * a.NL * C; w += gridDim.x * T)
   {
     const unsigned int c = w % C, slot = (w / C) % a.NL, e = w / (C * a.NL);
     pmatrix_block(a.m, a.lens[(size_t)e * a.NL + slot], c,
@@ -440,18 +475,29 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
 
   for (unsigned int sm = 0; sm < a.smoothings; ++sm)
   {
-    // the first smoothing still reads CLVs the engine holds; from the second on every
-    // CLV and matrix the body has touched is the candidate's private copy
-    for (unsigned int k = 0; k < a.n_body; ++k) run_step(a.n_pro + (sm ? a.n_body : 0u) + k);
+    // local optimisation: the first smoothing still reads CLVs the engine holds, from the
+    // second on every CLV the body has touched is the candidate's private copy; whole-tree
+    // optimisation: the traversals of a pass depend on the orientation the previous one left
+    const unsigned int variant = min(sm, a.n_bodies - 1);
+    for (unsigned int k = 0; k < a.n_body; ++k) run_step(a.n_pro + variant * a.n_body + k);
     lnl_phase(a.smooth_edge, live, [&](unsigned int e, double now) {
       BloCand c = a.cand[e];
-      // pll_optimize.c:1058-1076
-      if (!(now - c.lnl > now * 1e-14))
-        c.active = 0;
+      if (a.procedure == 0)
+      {
+        // pll_optimize.c:1058-1076
+        if (!(now - c.lnl > now * 1e-14))
+          c.active = 0;
+        else
+        {
+          c.smoothings += 1;
+          if (fabs(now - c.lnl) < a.tolerance || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
+        }
+      }
       else
       {
+        // PTPLL/pll_partition.cpp:566-581: another pass while |before - after| > EPSILON
         c.smoothings += 1;
-        if (fabs(now - c.lnl) < a.tolerance || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
+        if (!(fabs(c.lnl - now) > a.tolerance) || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
       }
       c.lnl = now;
       a.cand[e] = c;

@@ -92,8 +92,8 @@ struct ptgpu_engine
   double *d_lclv = nullptr; unsigned int *d_lscal = nullptr; double *d_lmat = nullptr;
   double *d_lsum = nullptr, *d_llens = nullptr, *d_lpart = nullptr, *d_ltile = nullptr;
   BloStep *d_lsteps = nullptr; BloEdge *d_ledges = nullptr; BloCand *d_lcand = nullptr;
-  NewtonState *d_lnst = nullptr; int *d_ltypes = nullptr;
-  size_t lcap_cand = 0, lcap_clvs = 0, lcap_lens = 0, lcap_steps = 0;
+  NewtonState *d_lnst = nullptr; int *d_ltypes = nullptr; unsigned int *d_lprior = nullptr;
+  size_t lcap_cand = 0, lcap_clvs = 0, lcap_lens = 0, lcap_steps = 0, lcap_types = 0, lcap_prior = 0;
   int blo_blocks_per_sm = 0;
   // op / matrix upload buffers
   DevOp *d_ops = nullptr;
@@ -334,7 +334,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials);
   cudaFree(e->d_lclv); cudaFree(e->d_lscal); cudaFree(e->d_lmat); cudaFree(e->d_lsum); cudaFree(e->d_llens);
   cudaFree(e->d_lpart); cudaFree(e->d_ltile); cudaFree(e->d_lsteps); cudaFree(e->d_ledges); cudaFree(e->d_lcand);
-  cudaFree(e->d_lnst); cudaFree(e->d_ltypes);
+  cudaFree(e->d_lnst); cudaFree(e->d_ltypes); cudaFree(e->d_lprior);
   cudaFree(e->d_bcands); cudaFree(e->d_ops); cudaFree(e->d_midx); cudaFree(e->d_mlen);
   for (auto &p : e->pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
   for (auto ev : e->event_pool) cudaEventDestroy(ev);
@@ -1067,6 +1067,243 @@ int launch_blo(ptgpu_engine *e, BloArgs &a, unsigned int grid)
   return PTGPU_OK;
 }
 
+// one request to the persistent step-program kernel (blo.cuh)
+struct BloRequest
+{
+  unsigned int count, n_private_clvs, n_lengths, n_prologue, n_body, n_bodies;
+  const int *step_types;
+  const ptgpu_blo_step_t *steps;
+  const ptgpu_blo_edge_t *smooth_edges, *final_edges;
+  const double *lengths0;
+  int procedure;             // BloArgs::procedure
+  double xmin, xmax, xtol, tolerance, lambda;
+  unsigned int smoothings, max_newton;
+  const unsigned int *prior_slots;
+  unsigned int n_prior;
+  double *lengths_out, *lnl_out;
+  int *status_out, *smoothings_out;
+};
+
+int blo_prepare_kernel(ptgpu_engine *e)
+{
+  if (e->blo_blocks_per_sm) return PTGPU_OK;
+  int occ = 0, rc = PTGPU_OK;
+  cudaError_t ea = cudaSuccess;
+  switch (e->cats)
+  {
+    case 1: ea = cudaFuncSetAttribute(blo_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<1>()); rc = blo_occupancy<1>(&occ); break;
+    case 2: ea = cudaFuncSetAttribute(blo_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<2>()); rc = blo_occupancy<2>(&occ); break;
+    case 4: ea = cudaFuncSetAttribute(blo_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<4>()); rc = blo_occupancy<4>(&occ); break;
+    default: ea = cudaFuncSetAttribute(blo_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<8>()); rc = blo_occupancy<8>(&occ); break;
+  }
+  if (ea != cudaSuccess) return fail(PTGPU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(ea));
+  if (rc) return rc;
+  if (occ < 1) return fail(PTGPU_ERR_CUDA, "step-program kernel does not fit an SM");
+  e->blo_blocks_per_sm = occ;
+  return PTGPU_OK;
+}
+
+// Every index of the program against the engine's and the candidate's own ranges.
+// Local optimisation (procedure 0) may write private slots only; the whole-tree
+// procedure works on the engine's own buffers, like the calls it replaces.
+int blo_validate(ptgpu_engine *e, const BloRequest &r)
+{
+  const unsigned int count = r.count, npriv = r.n_private_clvs, nlen = r.n_lengths;
+  const unsigned int nsteps = r.n_prologue + r.n_bodies * r.n_body;
+  const unsigned int clv_total = e->tips + e->clv_buffers;
+  const bool in_place = r.procedure == 1;
+  auto clv_ok = [&](unsigned int idx, unsigned int i, bool writable) {
+    if (idx < clv_total) return !writable || (in_place && idx >= e->tips);
+    return idx - clv_total >= i * npriv && idx - clv_total < (i + 1) * npriv;
+  };
+  auto scal_ok = [&](int idx, unsigned int i, bool writable) {
+    if (idx == PTGPU_SCALE_BUFFER_NONE) return true;
+    if (idx < 0) return false;
+    if ((unsigned int)idx < e->scale_buffers) return !writable || in_place;
+    const unsigned int off = (unsigned int)idx - e->scale_buffers;
+    return off >= i * npriv && off < (i + 1) * npriv;
+  };
+  auto mat_ok = [&](unsigned int idx, unsigned int i, bool writable) {
+    if (idx < e->prob_matrices) return !writable || in_place;
+    if (in_place) return false;
+    const unsigned int off = idx - e->prob_matrices;
+    return off >= i * nlen && off < (i + 1) * nlen;
+  };
+  // the matrix an optimised / recomputed edge owns: its private slot, or (in place) the
+  // engine matrix with the slot's number
+  auto owns = [&](unsigned int mat, unsigned int slot, unsigned int i) {
+    if (slot >= nlen) return false;
+    return in_place ? mat == slot && mat < e->prob_matrices : mat == e->prob_matrices + i * nlen + slot;
+  };
+  for (unsigned int k = 0; k < nsteps; ++k)
+    for (unsigned int i = 0; i < count; ++i)
+    {
+      const ptgpu_blo_step_t &st = r.steps[(size_t)k * count + i];
+      if (st.type == PTGPU_BLO_NOP) continue;
+      if (st.type != r.step_types[k])
+        return fail(PTGPU_ERR_ARG, "step %u of candidate %u has type %d, expected %d", k, i, st.type, r.step_types[k]);
+      bool ok;
+      if (st.type == PTGPU_BLO_OP)
+        ok = clv_ok(st.a_clv, i, true) && scal_ok(st.a_scaler, i, true) && clv_ok(st.b_clv, i, false) &&
+             clv_ok(st.c_clv, i, false) && scal_ok(st.b_scaler, i, false) && scal_ok(st.c_scaler, i, false) &&
+             mat_ok(st.b_matrix, i, false) && mat_ok(st.c_matrix, i, false) && st.a_clv != st.b_clv &&
+             st.a_clv != st.c_clv;
+      else if (st.type == PTGPU_BLO_OPT)
+        ok = clv_ok(st.a_clv, i, false) && clv_ok(st.b_clv, i, false) && owns(st.b_matrix, st.length_slot, i);
+      else if (st.type == PTGPU_BLO_MAT)
+        ok = owns(st.b_matrix, st.length_slot, i);
+      else
+        ok = false;
+      if (!ok) return fail(PTGPU_ERR_ARG, "step %u of candidate %u: index out of range", k, i);
+    }
+  for (unsigned int i = 0; i < count; ++i)
+    for (const ptgpu_blo_edge_t *ed : {&r.smooth_edges[i], &r.final_edges[i]})
+      if (!clv_ok(ed->parent_clv, i, false) || !clv_ok(ed->child_clv, i, false) ||
+          !scal_ok(ed->parent_scaler, i, false) || !scal_ok(ed->child_scaler, i, false) ||
+          !mat_ok(ed->matrix, i, false))
+        return fail(PTGPU_ERR_ARG, "edge of candidate %u: index out of range", i);
+  for (size_t i = 0; i < (size_t)count * nlen; ++i)
+    if (!(r.lengths0[i] >= 0)) return fail(PTGPU_ERR_ARG, "bad start length");
+  for (unsigned int k = 0; k < r.n_prior; ++k)
+    if (r.prior_slots[k] >= nlen) return fail(PTGPU_ERR_ARG, "prior slot out of range");
+  return PTGPU_OK;
+}
+
+int run_blo(ptgpu_engine *e, const BloRequest &r)
+{
+  int rc;
+  if (e->allreduce) return fail(PTGPU_ERR_STATE, "step programs are not available on a site shard");
+  if ((rc = blo_validate(e, r))) return rc;
+  CU(cudaSetDevice(e->device));
+  if ((rc = blo_prepare_kernel(e))) return rc;
+
+  const unsigned int count = r.count, npriv = r.n_private_clvs, nlen = r.n_lengths;
+  const unsigned int nsteps = r.n_prologue + r.n_bodies * r.n_body;
+  const unsigned int clv_total = e->tips + e->clv_buffers;
+  const bool in_place = r.procedure == 1;
+
+  // ---- scratch: private CLVs / scalers / matrices / sumtables for a chunk of candidates
+  const size_t stride = e->dev.clv_stride;
+  const size_t clv_bytes = stride * sizeof(double) + e->dev.scaler_stride * sizeof(unsigned int);
+  const size_t per_cand = (size_t)npriv * clv_bytes + stride * sizeof(double) +
+                          (size_t)(e->nchunks * 3 + e->ntiles) * sizeof(double) +
+                          (size_t)nlen * (e->cats * 16 + 1) * sizeof(double);
+  size_t free_b = 0, total_b = 0;
+  CU(cudaMemGetInfo(&free_b, &total_b));
+  const size_t have = e->lcap_cand * ((size_t)e->lcap_clvs * clv_bytes + stride * sizeof(double));
+  const size_t chunk = std::min<size_t>(count, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
+  if (chunk > e->lcap_cand || npriv > e->lcap_clvs || nlen > e->lcap_lens)
+  {
+    const size_t nc = std::max<size_t>(chunk, e->lcap_cand), ncl = std::max<size_t>(npriv, e->lcap_clvs),
+                 nl = std::max<size_t>(nlen, e->lcap_lens);
+    cudaFree(e->d_lclv); cudaFree(e->d_lscal); cudaFree(e->d_lmat); cudaFree(e->d_lsum); cudaFree(e->d_llens);
+    cudaFree(e->d_lpart); cudaFree(e->d_ltile); cudaFree(e->d_ledges); cudaFree(e->d_lcand); cudaFree(e->d_lnst);
+    e->d_lclv = e->d_lsum = e->d_lmat = e->d_llens = e->d_lpart = e->d_ltile = nullptr;
+    e->d_lscal = nullptr; e->d_ledges = nullptr; e->d_lcand = nullptr; e->d_lnst = nullptr;
+    e->lcap_cand = e->lcap_clvs = e->lcap_lens = 0;
+    CU(cudaMalloc(&e->d_lclv, std::max<size_t>(1, nc * ncl) * stride * sizeof(double)));
+    CU(cudaMalloc(&e->d_lscal, std::max<size_t>(1, nc * ncl) * e->dev.scaler_stride * sizeof(unsigned int)));
+    CU(cudaMalloc(&e->d_lmat, nc * nl * e->cats * 16 * sizeof(double)));
+    CU(cudaMalloc(&e->d_lsum, nc * stride * sizeof(double)));
+    CU(cudaMalloc(&e->d_llens, nc * nl * sizeof(double)));
+    CU(cudaMalloc(&e->d_lpart, nc * e->nchunks * 3 * sizeof(double)));
+    CU(cudaMalloc(&e->d_ltile, nc * e->ntiles * sizeof(double)));
+    CU(cudaMalloc(&e->d_ledges, nc * 2 * sizeof(BloEdge)));
+    CU(cudaMalloc(&e->d_lcand, nc * sizeof(BloCand)));
+    CU(cudaMalloc(&e->d_lnst, nc * sizeof(NewtonState)));
+    e->lcap_cand = nc; e->lcap_clvs = ncl; e->lcap_lens = nl;
+  }
+  if ((rc = ensure(&e->d_lsteps, &e->lcap_steps, (size_t)nsteps * chunk))) return rc;
+  if ((rc = ensure(&e->d_ltypes, &e->lcap_types, (size_t)nsteps))) return rc;
+  if ((rc = ensure(&e->d_lprior, &e->lcap_prior, (size_t)std::max(1u, r.n_prior)))) return rc;
+  CU(cudaStreamSynchronize(e->stream));  // nothing in flight still reads the descriptor buffers
+  CU(cudaMemcpyAsync(e->d_ltypes, r.step_types, nsteps * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  if (r.n_prior)
+    CU(cudaMemcpyAsync(e->d_lprior, r.prior_slots, r.n_prior * sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+
+  std::vector<BloStep> hsteps;
+  std::vector<BloEdge> hedges;
+  std::vector<BloCand> hcand;
+  std::vector<double> hlens;
+  for (unsigned int base = 0; base < count; base += (unsigned int)chunk)
+  {
+    const unsigned int nb = (unsigned int)std::min<size_t>(chunk, count - base);
+    // re-pack this chunk's columns; private indices are rebased to the chunk
+    const unsigned int dclv = base * npriv, dmat = base * nlen;
+    auto rb_clv = [&](unsigned int idx) { return idx >= clv_total ? idx - dclv : idx; };
+    auto rb_scal = [&](int idx) { return (idx >= 0 && (unsigned int)idx >= e->scale_buffers) ? (int)(idx - dclv) : idx; };
+    auto rb_mat = [&](unsigned int idx) { return idx >= e->prob_matrices ? idx - dmat : idx; };
+    hsteps.assign((size_t)nsteps * nb, BloStep{});
+    for (unsigned int k = 0; k < nsteps; ++k)
+      for (unsigned int i = 0; i < nb; ++i)
+      {
+        const ptgpu_blo_step_t &st = r.steps[(size_t)k * count + base + i];
+        BloStep d{};
+        d.type = st.type;
+        d.a_clv = rb_clv(st.a_clv); d.a_scal = rb_scal(st.a_scaler);
+        d.b_clv = rb_clv(st.b_clv); d.b_mat = rb_mat(st.b_matrix); d.b_scal = rb_scal(st.b_scaler);
+        d.c_clv = rb_clv(st.c_clv); d.c_mat = rb_mat(st.c_matrix); d.c_scal = rb_scal(st.c_scaler);
+        d.slot = st.length_slot;
+        hsteps[(size_t)k * nb + i] = d;
+      }
+    hedges.assign((size_t)2 * nb, BloEdge{});
+    for (unsigned int i = 0; i < nb; ++i)
+      for (int w = 0; w < 2; ++w)
+      {
+        const ptgpu_blo_edge_t &ed = w ? r.final_edges[base + i] : r.smooth_edges[base + i];
+        BloEdge d{};
+        d.p_clv = rb_clv(ed.parent_clv); d.p_scal = rb_scal(ed.parent_scaler);
+        d.c_clv = rb_clv(ed.child_clv); d.c_scal = rb_scal(ed.child_scaler);
+        d.mat = rb_mat(ed.matrix);
+        hedges[(size_t)w * nb + i] = d;
+      }
+    hcand.assign(nb, BloCand{});
+    for (auto &c : hcand) c.active = 1;
+    hlens.assign(r.lengths0 + (size_t)base * nlen, r.lengths0 + (size_t)(base + nb) * nlen);
+    CU(cudaMemcpyAsync(e->d_lsteps, hsteps.data(), hsteps.size() * sizeof(BloStep), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->d_ledges, hedges.data(), hedges.size() * sizeof(BloEdge), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->d_lcand, hcand.data(), hcand.size() * sizeof(BloCand), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->d_llens, hlens.data(), hlens.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+
+    BloArgs a{};
+    a.v.s = e->dev;
+    a.v.clv_total = clv_total; a.v.scal_total = e->scale_buffers; a.v.mat_total = e->prob_matrices;
+    a.v.pclv = e->d_lclv; a.v.pscal = e->d_lscal;
+    a.v.pmat = in_place ? nullptr : e->d_lmat;   // in place: the engine's own matrices, untouched until a step writes them
+    a.m = e->model;
+    a.steps = e->d_lsteps; a.step_type = e->d_ltypes;
+    a.smooth_edge = e->d_ledges; a.final_edge = e->d_ledges + nb;
+    a.cand = e->d_lcand; a.lens = e->d_llens; a.nst = e->d_lnst;
+    a.sumtables = e->d_lsum; a.entry_stride = stride;
+    a.partials = e->d_lpart; a.tile_partials = e->d_ltile;
+    a.B = nb; a.NL = nlen; a.n_pro = r.n_prologue; a.n_body = r.n_body; a.n_bodies = r.n_bodies;
+    a.sites = e->sites; a.ntiles = e->ntiles; a.chunk_tiles = e->chunk_tiles; a.nchunks = e->nchunks;
+    a.smoothings = r.smoothings; a.max_newton = r.max_newton;
+    a.xmin = r.xmin; a.xmax = r.xmax; a.xtol = r.xtol; a.tolerance = r.tolerance;
+    a.vec_end = e->vec_end;
+    a.procedure = r.procedure; a.lambda = r.lambda;
+    a.prior_slots = e->d_lprior; a.n_prior = r.n_prior;
+    const unsigned int work = std::max(1u, nb * e->ntiles);
+    const unsigned int grid = std::min(work, (unsigned int)(e->blo_blocks_per_sm * e->sm_count));
+    DISPATCH_CATS(e, rc = launch_blo<C>(e, a, grid));
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(hcand.data(), e->d_lcand, nb * sizeof(BloCand), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(hlens.data(), e->d_llens, hlens.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    for (unsigned int i = 0; i < nb; ++i)
+    {
+      r.lnl_out[base + i] = hcand[i].final_lnl;
+      if (r.status_out) r.status_out[base + i] = hcand[i].failed;
+      if (r.smoothings_out) r.smoothings_out[base + i] = hcand[i].smoothings;
+      e->counters[2] += (unsigned long long)hcand[i].newton_evals;
+    }
+    if (r.lengths_out)
+      memcpy(r.lengths_out + (size_t)base * nlen, hlens.data(), hlens.size() * sizeof(double));
+    if (!in_place) e->counters[3] += nb;
+  }
+  return PTGPU_OK;
+}
+
 } // namespace
 
 extern "C" int ptgpu_optimize_local_batch(ptgpu_engine *e, unsigned int count,
@@ -1085,192 +1322,56 @@ extern "C" int ptgpu_optimize_local_batch(ptgpu_engine *e, unsigned int count,
   if (!count) return PTGPU_OK;
   if (!n_private_clvs || !n_lengths || !smoothings)
     return fail(PTGPU_ERR_ARG, "ptgpu_optimize_local_batch: empty program");
-  const unsigned int nsteps = n_prologue + 2 * n_body;
-  const unsigned int clv_total = e->tips + e->clv_buffers;
+  BloRequest r{};
+  r.count = count; r.n_private_clvs = n_private_clvs; r.n_lengths = n_lengths;
+  r.n_prologue = n_prologue; r.n_body = n_body; r.n_bodies = 2;
+  r.step_types = step_types; r.steps = steps;
+  r.smooth_edges = smooth_edges; r.final_edges = final_edges; r.lengths0 = lengths0;
+  r.procedure = 0;
+  // pll_optimize.c:1011-1021
+  r.xmin = bl_min > 0 ? bl_min : 1.0e-4;
+  r.xmax = bl_max > 0 ? bl_max : 100.0;
+  r.xtol = bl_min > 0 ? bl_min / 10.0 : 1.0e-4;
+  r.tolerance = tolerance; r.lambda = 0.0;
+  r.smoothings = smoothings; r.max_newton = 30;
+  r.lengths_out = lengths_out; r.lnl_out = lnl_out; r.status_out = status_out;
+  r.smoothings_out = smoothings_out;
+  return run_blo(e, r);
+}
 
-  // ---- validate every index against the engine's and the candidate's own ranges
-  auto clv_ok = [&](unsigned int idx, unsigned int i, bool writable) {
-    if (idx < clv_total) return !writable;
-    return idx - clv_total >= i * n_private_clvs && idx - clv_total < (i + 1) * n_private_clvs;
-  };
-  auto scal_ok = [&](int idx, unsigned int i, bool writable) {
-    if (idx == PTGPU_SCALE_BUFFER_NONE) return true;
-    if (idx < 0) return false;
-    if ((unsigned int)idx < e->scale_buffers) return !writable;
-    const unsigned int off = (unsigned int)idx - e->scale_buffers;
-    return off >= i * n_private_clvs && off < (i + 1) * n_private_clvs;
-  };
-  auto mat_ok = [&](unsigned int idx, unsigned int i, bool writable) {
-    if (idx < e->prob_matrices) return !writable;
-    const unsigned int off = idx - e->prob_matrices;
-    return off >= i * n_lengths && off < (i + 1) * n_lengths;
-  };
-  for (unsigned int k = 0; k < nsteps; ++k)
-    for (unsigned int i = 0; i < count; ++i)
-    {
-      const ptgpu_blo_step_t &st = steps[(size_t)k * count + i];
-      if (st.type == PTGPU_BLO_NOP) continue;
-      if (st.type != step_types[k])
-        return fail(PTGPU_ERR_ARG, "step %u of candidate %u has type %d, expected %d", k, i, st.type, step_types[k]);
-      bool ok;
-      if (st.type == PTGPU_BLO_OP)
-        ok = clv_ok(st.a_clv, i, true) && scal_ok(st.a_scaler, i, true) && clv_ok(st.b_clv, i, false) &&
-             clv_ok(st.c_clv, i, false) && scal_ok(st.b_scaler, i, false) && scal_ok(st.c_scaler, i, false) &&
-             mat_ok(st.b_matrix, i, false) && mat_ok(st.c_matrix, i, false) && st.a_clv != st.b_clv &&
-             st.a_clv != st.c_clv;
-      else if (st.type == PTGPU_BLO_OPT)
-        ok = clv_ok(st.a_clv, i, false) && clv_ok(st.b_clv, i, false) && mat_ok(st.b_matrix, i, true) &&
-             st.length_slot < n_lengths &&
-             st.b_matrix == e->prob_matrices + i * n_lengths + st.length_slot;
-      else
-        ok = false;
-      if (!ok) return fail(PTGPU_ERR_ARG, "step %u of candidate %u: index out of range", k, i);
-    }
-  for (unsigned int i = 0; i < count; ++i)
-    for (const ptgpu_blo_edge_t *ed : {&smooth_edges[i], &final_edges[i]})
-      if (!clv_ok(ed->parent_clv, i, false) || !clv_ok(ed->child_clv, i, false) ||
-          !scal_ok(ed->parent_scaler, i, false) || !scal_ok(ed->child_scaler, i, false) ||
-          !mat_ok(ed->matrix, i, false))
-        return fail(PTGPU_ERR_ARG, "edge of candidate %u: index out of range", i);
-  for (size_t i = 0; i < (size_t)count * n_lengths; ++i)
-    if (!(lengths0[i] >= 0)) return fail(PTGPU_ERR_ARG, "bad start length");
-
-  CU(cudaSetDevice(e->device));
-  if (!e->blo_blocks_per_sm)
-  {
-    int occ = 0, rc2 = PTGPU_OK;
-    cudaError_t ea = cudaSuccess;
-    switch (e->cats)
-    {
-      case 1: ea = cudaFuncSetAttribute(blo_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<1>()); rc2 = blo_occupancy<1>(&occ); break;
-      case 2: ea = cudaFuncSetAttribute(blo_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<2>()); rc2 = blo_occupancy<2>(&occ); break;
-      case 4: ea = cudaFuncSetAttribute(blo_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<4>()); rc2 = blo_occupancy<4>(&occ); break;
-      default: ea = cudaFuncSetAttribute(blo_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<8>()); rc2 = blo_occupancy<8>(&occ); break;
-    }
-    if (ea != cudaSuccess) return fail(PTGPU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(ea));
-    if (rc2) return rc2;
-    if (occ < 1) return fail(PTGPU_ERR_CUDA, "local BLO kernel does not fit an SM");
-    e->blo_blocks_per_sm = occ;
-  }
-
-  // ---- scratch: private CLVs / scalers / matrices / sumtables for a chunk of candidates
-  const size_t stride = e->dev.clv_stride;
-  const size_t per_cand = (size_t)n_private_clvs * (stride * sizeof(double) + e->dev.scaler_stride * sizeof(unsigned int)) +
-                          stride * sizeof(double) + (size_t)(e->nchunks * 3 + e->ntiles) * sizeof(double) +
-                          (size_t)n_lengths * (e->cats * 16 + 1) * sizeof(double);
-  size_t free_b = 0, total_b = 0;
-  CU(cudaMemGetInfo(&free_b, &total_b));
-  const size_t have = e->lcap_cand * ((size_t)e->lcap_clvs * (stride * sizeof(double) + e->dev.scaler_stride * sizeof(unsigned int)) + stride * sizeof(double));
-  size_t chunk = std::min<size_t>(count, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
-  if (chunk > e->lcap_cand || n_private_clvs > e->lcap_clvs || n_lengths > e->lcap_lens)
-  {
-    cudaFree(e->d_lclv); cudaFree(e->d_lscal); cudaFree(e->d_lmat); cudaFree(e->d_lsum); cudaFree(e->d_llens);
-    cudaFree(e->d_lpart); cudaFree(e->d_ltile); cudaFree(e->d_ledges); cudaFree(e->d_lcand); cudaFree(e->d_lnst);
-    e->d_lclv = e->d_lsum = e->d_lmat = e->d_llens = e->d_lpart = e->d_ltile = nullptr;
-    e->d_lscal = nullptr; e->d_ledges = nullptr; e->d_lcand = nullptr; e->d_lnst = nullptr;
-    e->lcap_cand = 0;
-    const size_t nc = std::max<size_t>(chunk, e->lcap_cand), ncl = std::max<unsigned int>(n_private_clvs, (unsigned int)e->lcap_clvs),
-                 nl = std::max<unsigned int>(n_lengths, (unsigned int)e->lcap_lens);
-    CU(cudaMalloc(&e->d_lclv, nc * ncl * stride * sizeof(double)));
-    CU(cudaMalloc(&e->d_lscal, nc * ncl * e->dev.scaler_stride * sizeof(unsigned int)));
-    CU(cudaMalloc(&e->d_lmat, nc * nl * e->cats * 16 * sizeof(double)));
-    CU(cudaMalloc(&e->d_lsum, nc * stride * sizeof(double)));
-    CU(cudaMalloc(&e->d_llens, nc * nl * sizeof(double)));
-    CU(cudaMalloc(&e->d_lpart, nc * e->nchunks * 3 * sizeof(double)));
-    CU(cudaMalloc(&e->d_ltile, nc * e->ntiles * sizeof(double)));
-    CU(cudaMalloc(&e->d_ledges, nc * 2 * sizeof(BloEdge)));
-    CU(cudaMalloc(&e->d_lcand, nc * sizeof(BloCand)));
-    CU(cudaMalloc(&e->d_lnst, nc * sizeof(NewtonState)));
-    e->lcap_cand = nc; e->lcap_clvs = ncl; e->lcap_lens = nl;
-  }
-  int rc;
-  if ((rc = ensure(&e->d_lsteps, &e->lcap_steps, (size_t)nsteps * chunk))) return rc;
-  if (!e->d_ltypes) CU(cudaMalloc(&e->d_ltypes, 4096 * sizeof(int)));
-  if (nsteps > 4096) return fail(PTGPU_ERR_ARG, "program too long (%u steps)", nsteps);
-  CU(cudaMemcpyAsync(e->d_ltypes, step_types, nsteps * sizeof(int), cudaMemcpyHostToDevice, e->stream));
-  CU(cudaStreamSynchronize(e->stream));
-
-  std::vector<BloStep> hsteps;
-  std::vector<BloEdge> hedges;
-  std::vector<BloCand> hcand;
-  std::vector<double> hlens;
-  for (unsigned int base = 0; base < count; base += (unsigned int)chunk)
-  {
-    const unsigned int nb = (unsigned int)std::min<size_t>(chunk, count - base);
-    // re-pack this chunk's columns; private indices are rebased to the chunk
-    const unsigned int dclv = base * n_private_clvs, dmat = base * n_lengths;
-    auto rb_clv = [&](unsigned int idx) { return idx >= clv_total ? idx - dclv : idx; };
-    auto rb_scal = [&](int idx) { return (idx >= 0 && (unsigned int)idx >= e->scale_buffers) ? (int)(idx - dclv) : idx; };
-    auto rb_mat = [&](unsigned int idx) { return idx >= e->prob_matrices ? idx - dmat : idx; };
-    hsteps.assign((size_t)nsteps * nb, BloStep{});
-    for (unsigned int k = 0; k < nsteps; ++k)
-      for (unsigned int i = 0; i < nb; ++i)
-      {
-        const ptgpu_blo_step_t &st = steps[(size_t)k * count + base + i];
-        BloStep d{};
-        d.type = st.type;
-        d.a_clv = rb_clv(st.a_clv); d.a_scal = rb_scal(st.a_scaler);
-        d.b_clv = rb_clv(st.b_clv); d.b_mat = rb_mat(st.b_matrix); d.b_scal = rb_scal(st.b_scaler);
-        d.c_clv = rb_clv(st.c_clv); d.c_mat = rb_mat(st.c_matrix); d.c_scal = rb_scal(st.c_scaler);
-        d.slot = st.length_slot;
-        hsteps[(size_t)k * nb + i] = d;
-      }
-    hedges.assign((size_t)2 * nb, BloEdge{});
-    for (unsigned int i = 0; i < nb; ++i)
-      for (int w = 0; w < 2; ++w)
-      {
-        const ptgpu_blo_edge_t &ed = w ? final_edges[base + i] : smooth_edges[base + i];
-        BloEdge d{};
-        d.p_clv = rb_clv(ed.parent_clv); d.p_scal = rb_scal(ed.parent_scaler);
-        d.c_clv = rb_clv(ed.child_clv); d.c_scal = rb_scal(ed.child_scaler);
-        d.mat = rb_mat(ed.matrix);
-        hedges[(size_t)w * nb + i] = d;
-      }
-    hcand.assign(nb, BloCand{});
-    for (auto &c : hcand) c.active = 1;
-    hlens.assign(lengths0 + (size_t)base * n_lengths, lengths0 + (size_t)(base + nb) * n_lengths);
-    CU(cudaMemcpyAsync(e->d_lsteps, hsteps.data(), hsteps.size() * sizeof(BloStep), cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(e->d_ledges, hedges.data(), hedges.size() * sizeof(BloEdge), cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(e->d_lcand, hcand.data(), hcand.size() * sizeof(BloCand), cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(e->d_llens, hlens.data(), hlens.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
-
-    BloArgs a{};
-    a.v.s = e->dev;
-    a.v.clv_total = clv_total; a.v.scal_total = e->scale_buffers; a.v.mat_total = e->prob_matrices;
-    a.v.pclv = e->d_lclv; a.v.pscal = e->d_lscal; a.v.pmat = e->d_lmat;
-    a.m = e->model;
-    a.steps = e->d_lsteps; a.step_type = e->d_ltypes;
-    a.smooth_edge = e->d_ledges; a.final_edge = e->d_ledges + nb;
-    a.cand = e->d_lcand; a.lens = e->d_llens; a.nst = e->d_lnst;
-    a.sumtables = e->d_lsum; a.entry_stride = stride;
-    a.partials = e->d_lpart; a.tile_partials = e->d_ltile;
-    a.B = nb; a.NL = n_lengths; a.n_pro = n_prologue; a.n_body = n_body;
-    a.sites = e->sites; a.ntiles = e->ntiles; a.chunk_tiles = e->chunk_tiles; a.nchunks = e->nchunks;
-    a.smoothings = smoothings; a.max_newton = 30;
-    // pll_optimize.c:1011-1021
-    a.xmin = bl_min > 0 ? bl_min : 1.0e-4;
-    a.xmax = bl_max > 0 ? bl_max : 100.0;
-    a.xtol = bl_min > 0 ? bl_min / 10.0 : 1.0e-4;
-    a.tolerance = tolerance;
-    a.vec_end = e->vec_end;
-    if (e->allreduce) return fail(PTGPU_ERR_STATE, "ptgpu_optimize_local_batch is not available on a site shard");
-    const unsigned int work = std::max(1u, nb * e->ntiles);
-    const unsigned int grid = std::min(work, (unsigned int)(e->blo_blocks_per_sm * e->sm_count));
-    DISPATCH_CATS(e, rc = launch_blo<C>(e, a, grid));
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(hcand.data(), e->d_lcand, nb * sizeof(BloCand), cudaMemcpyDeviceToHost, e->stream));
-    CU(cudaMemcpyAsync(hlens.data(), e->d_llens, hlens.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
-    CU(cudaStreamSynchronize(e->stream));
-    for (unsigned int i = 0; i < nb; ++i)
-    {
-      lnl_out[base + i] = hcand[i].final_lnl;
-      if (status_out) status_out[base + i] = hcand[i].failed;
-      if (smoothings_out) smoothings_out[base + i] = hcand[i].smoothings;
-      e->counters[2] += (unsigned long long)hcand[i].newton_evals;
-    }
-    if (lengths_out)
-      memcpy(lengths_out + (size_t)base * n_lengths, hlens.data(), hlens.size() * sizeof(double));
-    e->counters[3] += nb;
-  }
+extern "C" int ptgpu_optimize_all_branches(ptgpu_engine *e, unsigned int n_prologue,
+                                           unsigned int n_body, unsigned int n_bodies,
+                                           const ptgpu_blo_step_t *steps,
+                                           const ptgpu_blo_edge_t *lnl_edge, const double *lengths0,
+                                           const unsigned int *prior_edges, unsigned int n_prior,
+                                           unsigned int max_iter, double epsilon, double map_lambda,
+                                           unsigned int max_passes, double *lengths_out,
+                                           double *lnl_out, int *status_out, int *passes_out)
+{
+  if (!e || !steps || !lnl_edge || !lengths0 || !lengths_out || !lnl_out)
+    return fail(PTGPU_ERR_ARG, "ptgpu_optimize_all_branches: null argument");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  if (!n_body || !n_bodies || !max_passes || !max_iter)
+    return fail(PTGPU_ERR_ARG, "ptgpu_optimize_all_branches: empty program");
+  if (n_prior && (!prior_edges || !(map_lambda > 0)))
+    return fail(PTGPU_ERR_ARG, "ptgpu_optimize_all_branches: prior edges without a prior rate");
+  const unsigned int nsteps = n_prologue + n_bodies * n_body;
+  std::vector<int> types(nsteps);
+  for (unsigned int k = 0; k < nsteps; ++k) types[k] = steps[k].type;
+  BloRequest r{};
+  r.count = 1; r.n_private_clvs = 0; r.n_lengths = e->prob_matrices;
+  r.n_prologue = n_prologue; r.n_body = n_body; r.n_bodies = n_bodies;
+  r.step_types = types.data(); r.steps = steps;
+  r.smooth_edges = lnl_edge; r.final_edges = lnl_edge; r.lengths0 = lengths0;
+  r.procedure = 1;
+  r.xmin = 0.0; r.xmax = 0.0; r.xtol = epsilon; r.tolerance = epsilon; r.lambda = map_lambda;
+  r.smoothings = max_passes; r.max_newton = max_iter;
+  r.prior_slots = prior_edges; r.n_prior = n_prior;
+  r.lengths_out = lengths_out; r.lnl_out = lnl_out; r.status_out = status_out;
+  r.smoothings_out = passes_out;
+  int rc = run_blo(e, r);
+  if (rc) return rc;
+  if (status_out && *status_out)
+    return fail(PTGPU_ERR_NOT_FINITE, *status_out == 1 ? "d1 is not finite" : "d2 is not finite");
   return PTGPU_OK;
 }

@@ -119,12 +119,14 @@ class Partition
  private:
   int device_;
   unsigned int directional_base_;  // first extra CLV / scaler buffer (0 = none allocated)
+  bool stepwise_all_branches_ = false;  // PTGPU_STEPWISE_ALL_BRANCHES: one engine call per step (A/B testing)
 
   void SetTipStates(pll_utree_t* tree, const std::vector<std::string>& labels,
                     const std::vector<std::string>& sequences);
   void AllocateScratchBuffers();
   void Check(int rc) const;
   double MapLogPrior(pll_unode_t* tree);
+  void OptimizeAllBranchesFused(pll_unode_t* tree);
   unsigned int DirectionalClv(const pll_unode_t* record) const;
   int DirectionalScaler(const pll_unode_t* record) const;
   void UpdateDirectionalClvs(pll_utree_t* tree);

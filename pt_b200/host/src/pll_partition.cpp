@@ -126,6 +126,7 @@ Partition::Partition(pll_utree_t* tree,
   const bool directional = !std::getenv("PTGPU_NO_DIRECTIONAL");
   const unsigned int extra = directional ? 3 * inner_node_count() : 0;
   directional_base_ = directional ? inner_node_count() : 0;
+  stepwise_all_branches_ = std::getenv("PTGPU_STEPWISE_ALL_BRANCHES") != nullptr;
   device_ = pick_device();
   Check(ptgpu_create(tip_node_count_, inner_node_count() + extra, site_count_,
                      static_cast<unsigned int>(model.category_rates.size()), branch_count(),
@@ -149,7 +150,8 @@ Partition::Partition(Partition&& rhs) :
     model_(std::move(rhs.model_)),
     site_count_(rhs.site_count_),
     device_(rhs.device_),
-    directional_base_(rhs.directional_base_)
+    directional_base_(rhs.directional_base_),
+    stepwise_all_branches_(rhs.stepwise_all_branches_)
 {
   rhs.engine_ = nullptr;
   AllocateScratchBuffers();
@@ -346,6 +348,10 @@ void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
 void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 {
   StatScope stat(kStatAllBranches);
+  if (!use_pllmod && !stepwise_all_branches_) {
+    OptimizeAllBranchesFused(tree);
+    return;
+  }
   TraversalUpdate(tree, TraversalType::PARTIAL);
 
   if (use_pllmod) {
@@ -461,6 +467,161 @@ double Partition::LocalBranchOptimization(pll_unode_t* tree, double bl_min, doub
     lnl = now;
   }
   return -1 * lnl;
+}
+
+// The same procedure as one persistent kernel (ptgpu_optimize_all_branches).  Which
+// matrices and CLVs each PARTIAL traversal recomputes depends only on the orientation
+// flags, which live on the host: the traversals are run here for their flag updates
+// and their operation lists are RECORDED instead of launched; the device then walks
+// the recorded steps, does the Newton solves and decides after every pass whether
+// another one is needed.  The engine ends in the state the call sequence would have
+// left (same buffers written by the same operations), the tree gets the optimised
+// lengths, the flags are those of the last traversal.
+void Partition::OptimizeAllBranchesFused(pll_unode_t* tree)
+{
+  std::vector<pll_unode_t*> nodes(node_count(), nullptr);
+  unsigned int found = 0;
+  if (!pll_utree_traverse(tree, PLL_TREE_TRAVERSE_POSTORDER, visit_all, nodes.data(), &found))
+    throw std::invalid_argument("OptimizeAllBranches() requires an inner node");
+  if (found != nodes.size()) throw std::invalid_argument("Unexpected number of nodes");
+
+  // orientation flags of every inner-node record, for the fix-point test below
+  auto flags = [&nodes]() {
+    std::vector<int> f;
+    for (pll_unode_t* n : nodes) {
+      if (!n->next) continue;
+      pll_unode_t* r = n;
+      do {
+        f.push_back(r->data ? static_cast<node_info_t*>(r->data)->clv_valid : -1);
+        r = r->next;
+      } while (r != n);
+    }
+    return f;
+  };
+  auto restore = [&nodes](const std::vector<int>& f) {
+    size_t k = 0;
+    for (pll_unode_t* n : nodes) {
+      if (!n->next) continue;
+      pll_unode_t* r = n;
+      do {
+        if (r->data) static_cast<node_info_t*>(r->data)->clv_valid = f[k];
+        ++k;
+        r = r->next;
+      } while (r != n);
+    }
+  };
+
+  // fresh[i]: the engine's matrix i is known to be P(current length of edge i), so a
+  // traversal's recomputation of it would write the same bits and is left out
+  std::vector<char> fresh(branch_count(), 0);
+  std::vector<ptgpu_blo_step_t> current;
+  auto record_traversal = [&](pll_unode_t* root) {
+    unsigned int size = 0, matrix_count = 0, ops_count = 0;
+    if (!pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, cb_partial_traversal,
+                            travbuffer_.data(), &size))
+      throw std::invalid_argument("TraversalUpdate() requires an inner node");
+    pll_utree_create_operations(travbuffer_.data(), size, branch_lengths_.data(),
+                                matrix_indices_.data(), operations_.data(), &matrix_count,
+                                &ops_count);
+    for (unsigned int k = 0; k < matrix_count; ++k) {
+      const unsigned int m = matrix_indices_[k];
+      if (fresh[m]) continue;
+      fresh[m] = 1;
+      ptgpu_blo_step_t st;
+      std::memset(&st, 0, sizeof st);
+      st.type = PTGPU_BLO_MAT;
+      st.b_matrix = st.length_slot = m;
+      current.push_back(st);
+    }
+    for (unsigned int k = 0; k < ops_count; ++k) {
+      const pll_operation_t& op = operations_[k];
+      ptgpu_blo_step_t st;
+      std::memset(&st, 0, sizeof st);
+      st.type = PTGPU_BLO_OP;
+      st.a_clv = op.parent_clv_index; st.a_scaler = op.parent_scaler_index;
+      st.b_clv = op.child1_clv_index; st.b_matrix = op.child1_matrix_index;
+      st.b_scaler = op.child1_scaler_index;
+      st.c_clv = op.child2_clv_index; st.c_matrix = op.child2_matrix_index;
+      st.c_scaler = op.child2_scaler_index;
+      current.push_back(st);
+    }
+  };
+  auto record_pass = [&]() {  // OptimizeAllBranchesOnce + the traversal back to `tree`
+    for (pll_unode_t* node : nodes) {
+      if (!node->next) node = node->back;
+      record_traversal(node);
+      ptgpu_blo_step_t st;
+      std::memset(&st, 0, sizeof st);
+      st.type = PTGPU_BLO_OPT;
+      st.a_clv = node->clv_index; st.a_scaler = node->scaler_index;
+      st.b_clv = node->back->clv_index; st.b_scaler = node->back->scaler_index;
+      st.b_matrix = st.length_slot = node->pmatrix_index;
+      current.push_back(st);
+      fresh[node->pmatrix_index] = 1;
+    }
+    record_traversal(tree);
+  };
+
+  record_traversal(tree);
+  std::vector<ptgpu_blo_step_t> prologue;
+  prologue.swap(current);
+
+  // pass k's traversals start from the flags pass k-1 left; record passes until that
+  // state repeats (in practice the second pass already does)
+  const unsigned int max_passes = MAX_ITER + 1;
+  std::vector<std::vector<ptgpu_blo_step_t>> bodies;
+  std::vector<std::vector<int>> flags_after;
+  std::vector<std::vector<char>> fresh_after;
+  while (bodies.size() < max_passes) {
+    record_pass();
+    bodies.emplace_back();
+    bodies.back().swap(current);
+    flags_after.push_back(flags());
+    fresh_after.push_back(fresh);
+    const size_t k = bodies.size();
+    if (k >= 2 && flags_after[k - 1] == flags_after[k - 2] && fresh_after[k - 1] == fresh_after[k - 2])
+      break;
+  }
+  size_t n_body = 0;
+  for (const auto& b : bodies) n_body = std::max(n_body, b.size());
+  std::vector<ptgpu_blo_step_t> steps(prologue);
+  for (const auto& b : bodies) {
+    steps.insert(steps.end(), b.begin(), b.end());
+    ptgpu_blo_step_t nop;
+    std::memset(&nop, 0, sizeof nop);
+    steps.insert(steps.end(), n_body - b.size(), nop);
+  }
+
+  // lengths by matrix index; LogLikelihood's edge and, in MAP mode, its prior terms
+  std::vector<double> lengths(branch_count(), 0.0), optimised(branch_count(), 0.0);
+  std::vector<unsigned int> prior;
+  for (pll_unode_t* n : nodes) {
+    lengths[n->pmatrix_index] = n->length;
+    if (n->next) {
+      lengths[n->next->pmatrix_index] = n->next->length;
+      lengths[n->next->next->pmatrix_index] = n->next->next->length;
+    }
+    if (map_mode_ && n != tree->back) prior.push_back(n->pmatrix_index);
+  }
+  ptgpu_blo_edge_t edge{tree->clv_index, tree->scaler_index, tree->back->clv_index,
+                        tree->back->scaler_index, tree->pmatrix_index, 0};
+  double lnl = 0.0;
+  int status = 0, passes = 0;
+  Check(ptgpu_optimize_all_branches(engine_, static_cast<unsigned int>(prologue.size()),
+                                    static_cast<unsigned int>(n_body),
+                                    static_cast<unsigned int>(bodies.size()), steps.data(), &edge,
+                                    lengths.data(), prior.data(), static_cast<unsigned int>(prior.size()),
+                                    MAX_ITER, EPSILON, map_mode_ ? kMapLambda : 0.0, max_passes,
+                                    optimised.data(), &lnl, &status, &passes));
+
+  for (pll_unode_t* n : nodes) {
+    pll_unode_t* r = n;
+    do {
+      r->length = optimised[r->pmatrix_index];
+      r = r->next;
+    } while (r && r != n);
+  }
+  if (passes >= 1 && static_cast<size_t>(passes) < bodies.size()) restore(flags_after[passes - 1]);
 }
 
 // Model-parameter optimisation is pll-modules' Brent / L-BFGS-B machinery
