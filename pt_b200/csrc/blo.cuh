@@ -83,10 +83,11 @@ struct BloArgs
   const BloEdge *final_edge;  // [B] parent p, child q  (Partition::LogLikelihood(node))
   BloCand *cand;             // [B]
   double *lens;              // [B][NL] private branch lengths
-  NewtonState *nst;          // [B]
+  NewtonState *nst;          // [2][B]: Newton state, double-buffered by evaluation parity
+  int *fin;                  // [B]: the current OPT step's solve of this candidate has finished
   double *sumtables;         // [B][entry_stride]
   size_t entry_stride;
-  double *partials;          // [B][nchunks][3] Newton chunk partials
+  double *partials;          // [2][B][nchunks][3] Newton chunk partials, double-buffered likewise
   double *tile_partials;     // [B][ntiles] edge-lnL tile partials
   const int *step_type;      // [n_pro + 2 n_body] the (uniform) type of each step position
   unsigned int B, NL, n_pro, n_body;
@@ -237,6 +238,45 @@ __device__ __forceinline__ void blo_sumtable_tile(const BloView &v, const ModelC
   }
 }
 
+// sumtable of one tile AND its contribution to the first derivative evaluation: the
+// entries go to memory for the later sweeps and, still in registers, through the same
+// arithmetic a sweep applies to them after reading them back
+template <int C>
+__device__ __forceinline__ void blo_sumtable_sweep_tile(const BloView &v, const ModelConst &m,
+                                                        unsigned int pclv, unsigned int cclv,
+                                                        double *sumtable, unsigned int tile,
+                                                        const double (&dg)[4][3], double out[3],
+                                                        unsigned long long vec_end)
+{
+  const int cat = threadIdx.x % C;
+  const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
+  double sv[kPasses][4];
+#pragma unroll
+  for (int half = 0; half < kPasses; half += 2)
+  {
+    double p[2][4], c[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      const unsigned int site = min(site0 + (half + j) * kSitesPerPass, v.s.sites - 1);
+      blo_load_entry<C>(v, pclv, site, cat, p[j]);
+      blo_load_entry<C>(v, cclv, site, cat, c[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      const unsigned int site = site0 + (half + j) * kSitesPerPass;
+      sumtable_entry<C>(m, p[j], c[j], sv[half + j]);
+      if (site < v.s.sites) st256(sumtable + ((size_t)site * C + cat) * 4, sv[half + j]);
+    }
+  }
+  unsigned int scv[kPasses];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps) scv[ps] = 0u;
+  LnlProd lp;
+  sweep_tile_compute<C, false>(m, sv, scv, v.s.sites, tile, dg, out, lp, vec_end);
+}
+
 // edge log-likelihood of one tile (as edge_lnl_kernel); returns this thread's share
 template <int C>
 __device__ __forceinline__ double blo_lnl_tile(const BloView &v, const ModelConst &m, const BloEdge &e,
@@ -282,14 +322,35 @@ __device__ __forceinline__ double blo_lnl_tile(const BloView &v, const ModelCons
 }
 
 // ---- the persistent kernel ----------------------------------------------------
-template <int C>
-__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel(BloArgs a)
+// CLUSTER = false: cooperative launch, phases separated by grid barriers.
+// CLUSTER = true : the whole grid is ONE thread-block cluster (<= 8 CTAs) and phases are
+// separated by the hardware cluster barrier (release/acquire at cluster scope, ~0.2 us
+// instead of a ~2 us round of global atomics): for programs whose (candidate, tile) work
+// fits a handful of CTAs -- OptimizeAllBranches on an alignment of a few thousand sites is
+// several thousand barriers per call, and nothing else.
+template <int C, bool CLUSTER>
+__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)) blo_kernel(BloArgs a)
 {
   constexpr int T = kSitesPerPass * C;
-  cg::grid_group grid = cg::this_grid();
   extern __shared__ __align__(16) double ring[];
   __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  __shared__ double sh_len;
+  __shared__ int sh_done, sh_status;
+  // fin[e] >= epoch <=> candidate e's solve of the current OPT step has finished.  The mark
+  // only ever grows (one epoch per executed OPT step), so a CTA still testing "anybody
+  // running?" for step k cannot be confused by a faster CTA arming step k+1.
+  int epoch = 0;
   const int cat = threadIdx.x % C;
+  struct Barrier
+  {
+    __device__ __forceinline__ void sync() const
+    {
+      if (CLUSTER)
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+      else
+        cg::this_grid().sync();
+    }
+  } grid;
 
   NewtonArgs na{};
   na.m = a.m;
@@ -366,40 +427,115 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
       return;
     }
     if (type != BLO_OPT) return;
-    // (1) arm the Newton state, build the sumtables
+    // Edge optimisation, one grid barrier per derivative evaluation.
+    // Phase 0 arms the solve, builds the sumtable and evaluates the derivatives at the
+    // start length from the entries while they are still in registers.  Phase p >= 1:
+    // EVERY CTA that holds a chunk of candidate e first redoes e's reduction and scalar
+    // Newton step from evaluation p-1 (same inputs, same code => same result in all of
+    // them; only the CTA of chunk 0 publishes it), then sweeps its chunk at the new
+    // length.  Partials and Newton state alternate between two buffers so that a fast CTA
+    // never overwrites what a slow one still reads.
+    auto wants = [&](unsigned int e, const BloStep &st) { return st.type == BLO_OPT && live(e); };
+    auto start_length = [&](unsigned int e, const BloStep &st) {
+      double guess = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
+      if (a.procedure == 0 && (guess < a.xmin || guess > a.xmax))
+        guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
+      return guess;
+    };
+    const size_t pstride = (size_t)a.B * a.nchunks * 3;
+    epoch += 1;
     for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
     {
       if (threadIdx.x != 0) continue;
       NewtonState ns{};
       const BloStep st = row[e];
-      if (st.type == BLO_OPT && live(e))
-      {
-        double guess = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
-        if (a.procedure == 0 && (guess < a.xmin || guess > a.xmax))
-          guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
-        ns.len = guess;
-      }
-      else
-        ns.done = 1;
+      const bool on = wants(e, st);
+      if (on) ns.len = start_length(e, st); else ns.done = 1;
       a.nst[e] = ns;
+      if (!on) a.fin[e] = epoch;
     }
-    for (unsigned int w = blockIdx.x; w < a.B * a.ntiles; w += gridDim.x)
+    for (unsigned int w = blockIdx.x; w < a.B * a.nchunks; w += gridDim.x)
     {
-      const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
+      const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
       const BloStep st = row[e];
-      if (st.type == BLO_OPT && live(e))
-        blo_sumtable_tile<C>(a.v, a.m, st.a_clv, st.b_clv, a.sumtables + (size_t)e * a.entry_stride, tile);
+      if (!wants(e, st)) continue;
+      double dg[4][3];
+      diag_regs<C>(a.m, start_length(e, st), cat, dg);
+      double out[3] = {0.0, 0.0, 0.0};
+      const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
+      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+        blo_sumtable_sweep_tile<C>(a.v, a.m, st.a_clv, st.b_clv, a.sumtables + (size_t)e * a.entry_stride,
+                                   tile, dg, out, a.vec_end);
+      const double s1 = block_sum<T>(out[0], red);
+      const double s2 = block_sum<T>(out[1], red);
+      if (threadIdx.x == 0)
+      {
+        a.partials[(size_t)w * 3 + 0] = s1;
+        a.partials[(size_t)w * 3 + 1] = s2;
+      }
     }
     grid.sync();
-    // (2) safeguarded Newton, all candidates in lock step (as newton_kernel, mode 1)
-    for (unsigned int it = 0; it < a.max_newton; ++it)
+    for (unsigned int p = 1; p <= a.max_newton; ++p)
     {
+      const double *prd = a.partials + ((p - 1) & 1) * pstride;
+      double *pwr = a.partials + (p & 1) * pstride;
+      const NewtonState *srd = a.nst + ((p - 1) & 1) * (size_t)a.B;
+      NewtonState *swr = a.nst + (p & 1) * (size_t)a.B;
       for (unsigned int w = blockIdx.x; w < a.B * a.nchunks; w += gridDim.x)
       {
         const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
-        if (__ldcg(&a.nst[e].done)) continue;
+        // finished in an earlier phase -- or in this one, already published by the CTA of
+        // chunk 0: either way there is nothing left to sweep
+        // (the mark may be written while we look: one thread reads, the CTA follows it)
+        if (__syncthreads_or(threadIdx.x == 0 && __ldcg(a.fin + e) >= epoch)) continue;
+        double a1 = 0.0, a2 = 0.0;
+        for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+        {
+          a1 = __dadd_rn(a1, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 0));
+          a2 = __dadd_rn(a2, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 1));
+        }
+        a1 = block_sum<T>(a1, red);
+        a2 = block_sum<T>(a2, red);
+        NewtonState ns;
+        if (threadIdx.x == 0)
+        {
+          ns = newton_scalar_step(na, srd + e, a1, a2, 0.0);
+          sh_len = ns.len;
+          sh_done = ns.done;
+          sh_status = ns.status;
+          if (chunk == 0) swr[e] = ns;
+        }
+        __syncthreads();
+        const double len = sh_len;
+        const int done = sh_done;
+        if (done)
+        {
+          if (chunk == 0)
+          {
+            // accept the result (pll_optimize.c:824-868 / PTPLL/pll_partition.cpp:483-487):
+            // length slot + P matrix, or the failure (pll_errno / std::range_error)
+            const BloStep st = row[e];
+            const double old = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
+            const int status = sh_status;
+            __syncthreads();  // everybody has read the old length before thread 0 replaces it
+            // procedure 1: UpdateBranchLength always recomputes the matrix (PTPLL/pll_partition.cpp:395-406)
+            if (status == 0 && (a.procedure == 1 || fabs(old - len) > 1e-10) && threadIdx.x < C)
+              pmatrix_block(a.m, len, threadIdx.x, blo_mat_ptr<C>(a.v, st.b_mat) + threadIdx.x * 16);
+            if (threadIdx.x == 0)
+            {
+              if (status != 0)
+                a.cand[e].failed = status;
+              else
+                a.lens[(size_t)e * a.NL + st.slot] = len;
+              a.cand[e].newton_evals += ns.iters;
+              a.fin[e] = epoch;
+            }
+          }
+          __syncthreads();   // sh_len / sh_done are rewritten by the next work item
+          continue;
+        }
         double dg[4][3];
-        diag_regs<C>(a.m, __ldcg(&a.nst[e].len), cat, dg);
+        diag_regs<C>(a.m, len, cat, dg);
         double out[3] = {0.0, 0.0, 0.0};
         LnlProd lp;
         const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
@@ -409,55 +545,18 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
         const double s2 = block_sum<T>(out[1], red);
         if (threadIdx.x == 0)
         {
-          a.partials[(size_t)w * 3 + 0] = s1;
-          a.partials[(size_t)w * 3 + 1] = s2;
+          pwr[(size_t)w * 3 + 0] = s1;
+          pwr[(size_t)w * 3 + 1] = s2;
         }
-      }
-      grid.sync();
-      for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
-      {
-        if (__ldcg(&a.nst[e].done)) continue;
-        double a1 = 0.0, a2 = 0.0;
-        for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
-        {
-          a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 0));
-          a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 1));
-        }
-        a1 = block_sum<T>(a1, red);
-        a2 = block_sum<T>(a2, red);
-        if (threadIdx.x == 0) newton_scalar_update(na, e, a1, a2, 0.0);
       }
       grid.sync();
       int running = 0;
-      for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= !__ldcg(&a.nst[e].done);
+      for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= __ldcg(a.fin + e) < epoch;
       if (!__syncthreads_or(running)) break;
     }
-    // (3) accept the result: length slot + private P matrix (pll_optimize.c:824-868)
-    for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
-    {
-      const BloStep st = row[e];
-      if (st.type != BLO_OPT || !live(e)) continue;
-      const int status = __ldcg(&a.nst[e].status);
-      const double neu = __ldcg(&a.nst[e].len);
-      const double old = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
-      if (status != 0)
-      {
-        if (threadIdx.x == 0) a.cand[e].failed = status;
-        continue;
-      }
-      __syncthreads();  // everybody has read the old length before thread 0 replaces it
-      // procedure 1: UpdateBranchLength always recomputes the matrix (PTPLL/pll_partition.cpp:395-406)
-      if ((a.procedure == 1 || fabs(old - neu) > 1e-10) && threadIdx.x < C)
-        pmatrix_block(a.m, neu, threadIdx.x, blo_mat_ptr<C>(a.v, st.b_mat) + threadIdx.x * 16);
-      if (threadIdx.x == 0)
-      {
-        a.lens[(size_t)e * a.NL + st.slot] = neu;
-        a.cand[e].newton_evals += __ldcg(&a.nst[e].iters);
-      }
-    }
-    grid.sync();
   };
 
+  for (unsigned int e = blockIdx.x * T + threadIdx.x; e < a.B; e += gridDim.x * T) a.fin[e] = 0;
   // private P matrices at the start lengths (in-place programs use the engine's matrices as
   // they are: a stale one stays stale until a step recomputes it, as in the call sequence)
   for (unsigned int w = blockIdx.x * T + threadIdx.x; a.v.pmat && w < a.B * a.NL * C; w += gridDim.x * T)
@@ -467,49 +566,59 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? 2 : 1)) blo_kernel
                   a.v.pmat + ((size_t)(e * a.NL + slot) * C + c) * 16);
   }
   grid.sync();
-  for (unsigned int k = 0; k < a.n_pro; ++k) run_step(k);
-
-  // lnL before the first smoothing (pll_optimize.c:1000-1007)
-  lnl_phase(a.smooth_edge, [&](unsigned int) { return true; },
-            [&](unsigned int e, double v) { a.cand[e].lnl = v; });
-
-  for (unsigned int sm = 0; sm < a.smoothings; ++sm)
+  // round -1: the prologue and the lnL before the first smoothing (pll_optimize.c:1000-1007);
+  // rounds 0..: one smoothing / pass each, its lnL and the stop decision; last: the final lnL
+  // (Partition::LogLikelihood(node)) on whatever state each candidate ended in.  One loop so
+  // that run_step and lnl_phase have a single call site each (they inline; BloArgs stays in
+  // the parameter bank instead of being copied to the stack).
+  bool finishing = false;
+  for (int round = -1;; ++round)
   {
-    // local optimisation: the first smoothing still reads CLVs the engine holds, from the
-    // second on every CLV the body has touched is the candidate's private copy; whole-tree
-    // optimisation: the traversals of a pass depend on the orientation the previous one left
-    const unsigned int variant = min(sm, a.n_bodies - 1);
-    for (unsigned int k = 0; k < a.n_body; ++k) run_step(a.n_pro + variant * a.n_body + k);
-    lnl_phase(a.smooth_edge, live, [&](unsigned int e, double now) {
-      BloCand c = a.cand[e];
-      if (a.procedure == 0)
-      {
-        // pll_optimize.c:1058-1076
-        if (!(now - c.lnl > now * 1e-14))
-          c.active = 0;
-        else
-        {
-          c.smoothings += 1;
-          if (fabs(now - c.lnl) < a.tolerance || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
-        }
-      }
-      else
-      {
-        // PTPLL/pll_partition.cpp:566-581: another pass while |before - after| > EPSILON
-        c.smoothings += 1;
-        if (!(fabs(c.lnl - now) > a.tolerance) || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
-      }
-      c.lnl = now;
-      a.cand[e] = c;
-    });
-    int running = 0;
-    for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= live(e);
-    if (!__syncthreads_or(running)) break;
+    if (!finishing)
+    {
+      // local optimisation: the first smoothing still reads CLVs the engine holds, from the
+      // second on every CLV the body has touched is the candidate's private copy; whole-tree
+      // optimisation: the traversals of a pass depend on the orientation the previous one left
+      const unsigned int variant = round < 0 ? 0u : min((unsigned int)round, a.n_bodies - 1);
+      const unsigned int k0 = round < 0 ? 0u : a.n_pro + variant * a.n_body;
+      const unsigned int k1 = k0 + (round < 0 ? a.n_pro : a.n_body);
+      for (unsigned int k = k0; k < k1; ++k) run_step(k);
+    }
+    lnl_phase(finishing ? a.final_edge : a.smooth_edge,
+              [&](unsigned int e) { return round < 0 || finishing || live(e); },
+              [&](unsigned int e, double now) {
+                if (finishing) { a.cand[e].final_lnl = now; return; }
+                if (round < 0) { a.cand[e].lnl = now; return; }
+                BloCand c = a.cand[e];
+                if (a.procedure == 0)
+                {
+                  // pll_optimize.c:1058-1076
+                  if (!(now - c.lnl > now * 1e-14))
+                    c.active = 0;
+                  else
+                  {
+                    c.smoothings += 1;
+                    if (fabs(now - c.lnl) < a.tolerance || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
+                  }
+                }
+                else
+                {
+                  // PTPLL/pll_partition.cpp:566-581: another pass while |before - after| > EPSILON
+                  c.smoothings += 1;
+                  if (!(fabs(c.lnl - now) > a.tolerance) || (unsigned int)c.smoothings >= a.smoothings) c.active = 0;
+                }
+                c.lnl = now;
+                a.cand[e] = c;
+              });
+    if (finishing) break;
+    if (round >= 0)
+    {
+      int running = 0;
+      for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= live(e);
+      if (!__syncthreads_or(running)) finishing = true;
+    }
+    if (round + 1 >= (int)a.smoothings) finishing = true;
   }
-
-  // Partition::LogLikelihood(node) on whatever state the candidate ended in
-  lnl_phase(a.final_edge, [&](unsigned int) { return true; },
-            [&](unsigned int e, double v) { a.cand[e].final_lnl = v; });
 }
 
 } // namespace ptgpu

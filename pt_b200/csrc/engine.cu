@@ -92,7 +92,8 @@ struct ptgpu_engine
   double *d_lclv = nullptr; unsigned int *d_lscal = nullptr; double *d_lmat = nullptr;
   double *d_lsum = nullptr, *d_llens = nullptr, *d_lpart = nullptr, *d_ltile = nullptr;
   BloStep *d_lsteps = nullptr; BloEdge *d_ledges = nullptr; BloCand *d_lcand = nullptr;
-  NewtonState *d_lnst = nullptr; int *d_ltypes = nullptr; unsigned int *d_lprior = nullptr;
+  NewtonState *d_lnst = nullptr; int *d_ltypes = nullptr, *d_lfin = nullptr; unsigned int *d_lprior = nullptr;
+  unsigned int blo_cluster_work = 2 * 8;   // largest (candidates x tiles) run as one cluster; env PTGPU_BLO_CLUSTER_WORK
   size_t lcap_cand = 0, lcap_clvs = 0, lcap_lens = 0, lcap_steps = 0, lcap_types = 0, lcap_prior = 0;
   int blo_blocks_per_sm = 0;
   // op / matrix upload buffers
@@ -254,6 +255,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   if (const char *pv = getenv("PTGPU_PARTIALS")) e->partials_version = atoi(pv);
   if (const char *pv = getenv("PTGPU_PREPARE")) e->prepare_version = atoi(pv);
   if (const char *pv = getenv("PTGPU_LNL_MARGIN")) e->lnl_margin = atof(pv);
+  if (const char *pv = getenv("PTGPU_BLO_CLUSTER_WORK")) e->blo_cluster_work = (unsigned int)atoi(pv);
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
@@ -334,7 +336,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials);
   cudaFree(e->d_lclv); cudaFree(e->d_lscal); cudaFree(e->d_lmat); cudaFree(e->d_lsum); cudaFree(e->d_llens);
   cudaFree(e->d_lpart); cudaFree(e->d_ltile); cudaFree(e->d_lsteps); cudaFree(e->d_ledges); cudaFree(e->d_lcand);
-  cudaFree(e->d_lnst); cudaFree(e->d_ltypes); cudaFree(e->d_lprior);
+  cudaFree(e->d_lnst); cudaFree(e->d_ltypes); cudaFree(e->d_lprior); cudaFree(e->d_lfin);
   cudaFree(e->d_bcands); cudaFree(e->d_ops); cudaFree(e->d_midx); cudaFree(e->d_mlen);
   for (auto &p : e->pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
   for (auto ev : e->event_pool) cudaEventDestroy(ev);
@@ -1049,10 +1051,12 @@ int ptgpu_synchronize(ptgpu_engine *e)
 
 namespace {
 
+constexpr unsigned int kBloCluster = 8;   // CTAs of the single-cluster variant (portable maximum)
+
 template <int C>
 int blo_occupancy(int *out)
 {
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, blo_kernel<C>, kSitesPerPass * C,
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, blo_kernel<C, false>, kSitesPerPass * C,
                                                    sweep_ring_bytes<C>()));
   return PTGPU_OK;
 }
@@ -1062,8 +1066,29 @@ int launch_blo(ptgpu_engine *e, BloArgs &a, unsigned int grid)
 {
   void *params[] = {&a};
   LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-  CU(cudaLaunchCooperativeKernel((void *)blo_kernel<C>, dim3(grid), dim3(kSitesPerPass * C), params,
+  CU(cudaLaunchCooperativeKernel((void *)blo_kernel<C, false>, dim3(grid), dim3(kSitesPerPass * C), params,
                                  sweep_ring_bytes<C>(), e->stream));
+  return PTGPU_OK;
+}
+
+// the whole grid as one thread-block cluster; barriers are the hardware cluster barrier
+template <int C>
+int launch_blo_cluster(ptgpu_engine *e, BloArgs &a)
+{
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(kBloCluster);
+  cfg.blockDim = dim3(kSitesPerPass * C);
+  cfg.dynamicSmemBytes = sweep_ring_bytes<C>();
+  cfg.stream = e->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kBloCluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
+  CU(cudaLaunchKernelEx(&cfg, blo_kernel<C, true>, a));
   return PTGPU_OK;
 }
 
@@ -1091,10 +1116,10 @@ int blo_prepare_kernel(ptgpu_engine *e)
   cudaError_t ea = cudaSuccess;
   switch (e->cats)
   {
-    case 1: ea = cudaFuncSetAttribute(blo_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<1>()); rc = blo_occupancy<1>(&occ); break;
-    case 2: ea = cudaFuncSetAttribute(blo_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<2>()); rc = blo_occupancy<2>(&occ); break;
-    case 4: ea = cudaFuncSetAttribute(blo_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<4>()); rc = blo_occupancy<4>(&occ); break;
-    default: ea = cudaFuncSetAttribute(blo_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<8>()); rc = blo_occupancy<8>(&occ); break;
+    case 1: ea = cudaFuncSetAttribute(blo_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<1>()); rc = blo_occupancy<1>(&occ); break;
+    case 2: ea = cudaFuncSetAttribute(blo_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<2>()); rc = blo_occupancy<2>(&occ); break;
+    case 4: ea = cudaFuncSetAttribute(blo_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<4>()); rc = blo_occupancy<4>(&occ); break;
+    default: ea = cudaFuncSetAttribute(blo_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<8>()); rc = blo_occupancy<8>(&occ); break;
   }
   if (ea != cudaSuccess) return fail(PTGPU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(ea));
   if (rc) return rc;
@@ -1198,19 +1223,21 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
                  nl = std::max<size_t>(nlen, e->lcap_lens);
     cudaFree(e->d_lclv); cudaFree(e->d_lscal); cudaFree(e->d_lmat); cudaFree(e->d_lsum); cudaFree(e->d_llens);
     cudaFree(e->d_lpart); cudaFree(e->d_ltile); cudaFree(e->d_ledges); cudaFree(e->d_lcand); cudaFree(e->d_lnst);
+    cudaFree(e->d_lfin);
     e->d_lclv = e->d_lsum = e->d_lmat = e->d_llens = e->d_lpart = e->d_ltile = nullptr;
-    e->d_lscal = nullptr; e->d_ledges = nullptr; e->d_lcand = nullptr; e->d_lnst = nullptr;
+    e->d_lscal = nullptr; e->d_ledges = nullptr; e->d_lcand = nullptr; e->d_lnst = nullptr; e->d_lfin = nullptr;
     e->lcap_cand = e->lcap_clvs = e->lcap_lens = 0;
     CU(cudaMalloc(&e->d_lclv, std::max<size_t>(1, nc * ncl) * stride * sizeof(double)));
     CU(cudaMalloc(&e->d_lscal, std::max<size_t>(1, nc * ncl) * e->dev.scaler_stride * sizeof(unsigned int)));
     CU(cudaMalloc(&e->d_lmat, nc * nl * e->cats * 16 * sizeof(double)));
     CU(cudaMalloc(&e->d_lsum, nc * stride * sizeof(double)));
     CU(cudaMalloc(&e->d_llens, nc * nl * sizeof(double)));
-    CU(cudaMalloc(&e->d_lpart, nc * e->nchunks * 3 * sizeof(double)));
+    CU(cudaMalloc(&e->d_lpart, 2 * nc * e->nchunks * 3 * sizeof(double)));
     CU(cudaMalloc(&e->d_ltile, nc * e->ntiles * sizeof(double)));
     CU(cudaMalloc(&e->d_ledges, nc * 2 * sizeof(BloEdge)));
     CU(cudaMalloc(&e->d_lcand, nc * sizeof(BloCand)));
-    CU(cudaMalloc(&e->d_lnst, nc * sizeof(NewtonState)));
+    CU(cudaMalloc(&e->d_lnst, 2 * nc * sizeof(NewtonState)));
+    CU(cudaMalloc(&e->d_lfin, nc * sizeof(int)));
     e->lcap_cand = nc; e->lcap_clvs = ncl; e->lcap_lens = nl;
   }
   if ((rc = ensure(&e->d_lsteps, &e->lcap_steps, (size_t)nsteps * chunk))) return rc;
@@ -1273,7 +1300,7 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     a.m = e->model;
     a.steps = e->d_lsteps; a.step_type = e->d_ltypes;
     a.smooth_edge = e->d_ledges; a.final_edge = e->d_ledges + nb;
-    a.cand = e->d_lcand; a.lens = e->d_llens; a.nst = e->d_lnst;
+    a.cand = e->d_lcand; a.lens = e->d_llens; a.nst = e->d_lnst; a.fin = e->d_lfin;
     a.sumtables = e->d_lsum; a.entry_stride = stride;
     a.partials = e->d_lpart; a.tile_partials = e->d_ltile;
     a.B = nb; a.NL = nlen; a.n_pro = r.n_prologue; a.n_body = r.n_body; a.n_bodies = r.n_bodies;
@@ -1285,7 +1312,15 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     a.prior_slots = e->d_lprior; a.n_prior = r.n_prior;
     const unsigned int work = std::max(1u, nb * e->ntiles);
     const unsigned int grid = std::min(work, (unsigned int)(e->blo_blocks_per_sm * e->sm_count));
-    DISPATCH_CATS(e, rc = launch_blo<C>(e, a, grid));
+    // a program whose phases are a couple of tiles per CTA is all barriers: one cluster
+    if (work <= e->blo_cluster_work && !PT_SWEEP_RING)
+    {
+      DISPATCH_CATS(e, rc = launch_blo_cluster<C>(e, a));
+    }
+    else
+    {
+      DISPATCH_CATS(e, rc = launch_blo<C>(e, a, grid));
+    }
     if (rc) return rc;
     CU(cudaMemcpyAsync(hcand.data(), e->d_lcand, nb * sizeof(BloCand), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaMemcpyAsync(hlens.data(), e->d_llens, hlens.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));

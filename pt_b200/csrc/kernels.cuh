@@ -983,24 +983,24 @@ __device__ __forceinline__ void bounded_newton_step(NewtonState &st, double f, d
 // The per-branch scalar step after one derivative evaluation: mode 0 is the
 // loop body of Partition::OptimizeBranch (PTPLL/pll_partition.cpp:433-481),
 // mode 1 one step of pllmod_opt_minimize_newton.
-__device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsigned int e, double a1,
-                                                     double a2, double a3 = 0.0)
+__device__ __forceinline__ NewtonState newton_scalar_step(const NewtonArgs &a, const NewtonState *in,
+                                                          double a1, double a2, double a3 = 0.0)
 {
   NewtonState st;
-  st.len = __ldcg(&a.st[e].len);
+  st.len = __ldcg(&in->len);
   const double evaluated_at = st.len;
   st.lnl = 0.0;
   st.lnl_valid = 0;
-  const int had_lnl = __ldcg(&a.st[e].try_lnl);
+  const int had_lnl = __ldcg(&in->try_lnl);
   st.try_lnl = 0;
-  st.lnl_sweeps = __ldcg(&a.st[e].lnl_sweeps) + (had_lnl ? 1 : 0);
+  st.lnl_sweeps = __ldcg(&in->lnl_sweeps) + (had_lnl ? 1 : 0);
   st.final_sweeps = 0;
-  st.iters = __ldcg(&a.st[e].iters);
+  st.iters = __ldcg(&in->iters);
   st.done = 0;
-  st.maybe_decreasing = __ldcg(&a.st[e].maybe_decreasing);
+  st.maybe_decreasing = __ldcg(&in->maybe_decreasing);
   st.status = 0;
-  st.xl = __ldcg(&a.st[e].xl);
-  st.xh = __ldcg(&a.st[e].xh);
+  st.xl = __ldcg(&in->xl);
+  st.xh = __ldcg(&in->xh);
   if (a.mode == 1)
     bounded_newton_step(st, a1, a2, a);
   else
@@ -1023,7 +1023,7 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
       // sweep also sums the site log-likelihoods (a wrong guess costs either
       // one cheap extra log pass or one extra sweep at the end, never accuracy).
       {
-        const double prev = __ldcg(&a.st[e].d1);
+        const double prev = __ldcg(&in->d1);
         const double pred = (st.iters > 1 && prev != 0.0)
                                 ? fabs(d1) * (fabs(d1) / fabs(prev)) * (fabs(d1) / fabs(prev))
                                 : fabs(d1);
@@ -1046,7 +1046,13 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
     st.lnl = a3;
     st.lnl_valid = 1;
   }
-  a.st[e] = st;
+  return st;
+}
+
+__device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsigned int e, double a1,
+                                                     double a2, double a3 = 0.0)
+{
+  a.st[e] = newton_scalar_step(a, &a.st[e], a1, a2, a3);
 }
 
 // Persistent cooperative kernel: the whole Newton-Raphson loop of

@@ -78,7 +78,7 @@ def test_ptw_batched_tables_identical_and_faster(config):
     """The same two configs through ptw_batched (pt_b200/host/ptw): the wanderer's 2(n-3)
     EvaluateMove calls per tree are answered from ONE batched engine call (radius 0:
     ptgpu_score_nni_batch, radius 1: ptgpu_optimize_local_batch).  The three tables must still
-    be the reference's, and the run must not be slower than the move-at-a-time drop-in."""
+    be the reference's, and the radius-1 run must be faster than the move-at-a-time drop-in."""
     import time
     from make_ptw_golden import run, summarise
     seq, bat = need("ptw_threads_gpu"), need("ptw_batched")
@@ -94,4 +94,5 @@ def test_ptw_batched_tables_identical_and_faster(config):
     run(seq, gold["args"])
     t_sequential = time.time() - t0
     print(f"{config}: batched {t_batched:.2f}s, move-at-a-time {t_sequential:.2f}s")
-    assert t_batched < t_sequential * 1.1
+    if config == "config2":   # config 1 is nine trees: mostly process start-up
+        assert t_batched < t_sequential
