@@ -385,14 +385,17 @@ def run_ours(args):
     if prog is not None:
         # the persistent local-optimisation kernel (timed under the "newton" slot): per
         # candidate 2 prologue CLV updates + 2 edge lnL, and per executed smoothing the body's
-        # CLV updates (396 B/site), sumtables (384 B/site), one edge lnL (268 B/site); every
-        # derivative sweep 128 B/site.  Smoothings that ended on "no improvement" are not in
-        # the counter, so this is a lower bound of the bytes (and of `achieved`).
+        # CLV updates (396 B/site), sumtables (384 B/site, the first derivative evaluation rides
+        # on the build), one edge lnL (268 B/site); every further derivative sweep 128 B/site.
+        # Smoothings that ended on "no improvement" are not in the counter, so this is a lower
+        # bound of the bytes (and of `achieved`).
         body = prog.step_types[prog.n_prologue:prog.n_prologue + prog.n_body]
-        per_body = int((body == 1).sum()) * 396 + int((body == 2).sum()) * 384 + 268
+        n_op, n_opt = int((body == 1).sum()), int((body == 2).sum())
+        per_body = n_op * 396 + n_opt * 384 + 268
+        smoothings = int(last["smoothings"].sum())
         algo = dict(partials=algo["partials"],
-                    newton=(ncand * (2 * 396 + 2 * 268) + int(last["smoothings"].sum()) * per_body
-                            + passes / steps * 128) * S)
+                    newton=(ncand * (2 * 396 + 2 * 268) + smoothings * per_body
+                            + max(0.0, passes / steps - smoothings * n_opt) * 128) * S)
     kernels = {}
     for k, bytes_per_launch in algo.items():
         tot_ms, nl = kt[k]
