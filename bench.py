@@ -288,9 +288,11 @@ def run_ours(args):
     e = Engine(n, nbuf, S, 4, 2 * n - 3, nbuf, device=local)
     e.set_model(FREQS, SUBST, RATES)
 
+    tip_ids = np.arange(n, dtype=np.uint32)
+    tip_ptrs = [host_aln[t].data_ptr() for t in range(n)]
+
     def upload_tips():
-        for t in range(n):
-            e.set_tip_states_ptr(t, host_aln[t].data_ptr())
+        e.set_tip_states_batch(tip_ids, tip_ptrs)
 
     upload_tips()
     br = tree.branches()

@@ -105,6 +105,16 @@ int ptgpu_get_eigen(ptgpu_engine *e, double evecs[16], double inv_evecs[16],
 int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index,
                          const char *sequence);
 
+/* The loop of Partition::SetTipStates (lib/libptpll/src/pll_partition.cpp:160-199)
+   in one call: sequences[i] (host, `sites` characters each) becomes tip
+   tip_indices[i].  The raw characters go up back to back on the engine's
+   stream (one copy when the sequences are contiguous in memory) and ONE kernel
+   encodes them all; one synchronisation at the end instead of two per tip.
+   An unknown character is PTGPU_ERR_STATE, as above. */
+int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count,
+                               const unsigned int *tip_indices,
+                               const char *const *sequences);
+
 /* pll_update_prob_matrices (LIBPLL/models.c:333-364) */
 int ptgpu_update_prob_matrices(ptgpu_engine *e, const unsigned int *matrix_indices,
                                const double *branch_lengths, unsigned int count);

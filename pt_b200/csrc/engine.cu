@@ -75,6 +75,10 @@ struct ptgpu_engine
   ModelConst model{};
   uint8_t *d_tips = nullptr;
   uint8_t *d_raw = nullptr;         // raw characters of the tip being encoded
+  uint8_t *d_raw_all = nullptr;     // ... of all tips (batched upload)
+  size_t raw_all_cap = 0;
+  unsigned int *d_tip_of = nullptr;
+  unsigned long long *d_bad = nullptr;
   double *d_sumtable = nullptr;
   double *d_persite = nullptr;      // per-site lnL scratch (allocated on first use)
   double *d_partials = nullptr;     // [ntiles * 2] tile partials of single-edge reductions
@@ -330,6 +334,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  cudaFree(e->d_raw_all); cudaFree(e->d_tip_of); cudaFree(e->d_bad);
   cudaFree(e->d_tips); cudaFree(e->d_raw); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
   cudaFree(e->d_sumtable); cudaFree(e->d_persite); cudaFree(e->d_partials); cudaFree(e->d_counter);
   cudaFree(e->d_state); cudaFree(e->d_idx1); cudaFree(e->d_red); cudaFree(e->d_active);
@@ -410,6 +415,71 @@ int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *se
   {
     const unsigned char ch = (unsigned char)sequence[bad];
     return fail(PTGPU_ERR_STATE, "Illegal state code in tip \"%c\" (site %u)", ch ? ch : '?', bad);
+  }
+  return PTGPU_OK;
+}
+
+int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count, const unsigned int *tip_indices,
+                               const char *const *sequences)
+{
+  if (!e || !tip_indices || !sequences) return fail(PTGPU_ERR_ARG, "ptgpu_set_tip_states_batch: null argument");
+  if (!count) return PTGPU_OK;
+  if (count > e->tips) return fail(PTGPU_ERR_ARG, "more sequences (%u) than tips (%u)", count, e->tips);
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    if (tip_indices[i] >= e->tips) return fail(PTGPU_ERR_ARG, "tip index %u out of range", tip_indices[i]);
+    if (!sequences[i]) return fail(PTGPU_ERR_ARG, "ptgpu_set_tip_states_batch: null sequence");
+  }
+  static const TipLut lut = [] {
+    TipLut t;
+    for (int c = 0; c < 256; ++c) t.m[c] = (uint8_t)nucleotide_mask((unsigned char)c);
+    t.m[0] = 0;
+    return t;
+  }();
+  CU(cudaSetDevice(e->device));
+  const size_t S = e->sites;
+  if (e->raw_all_cap < (size_t)count * S)
+  {
+    if (e->d_raw_all) CU(cudaFree(e->d_raw_all));
+    e->d_raw_all = nullptr;
+    e->raw_all_cap = 0;
+    CU(cudaMalloc(&e->d_raw_all, (size_t)e->tips * S));
+    e->raw_all_cap = (size_t)e->tips * S;
+  }
+  if (!e->d_tip_of) CU(cudaMalloc(&e->d_tip_of, e->tips * sizeof(unsigned int)));
+  if (!e->d_bad) CU(cudaMalloc(&e->d_bad, sizeof(unsigned long long)));
+  unsigned long long *bad_h = (unsigned long long *)(e->stg.host + 192);
+  unsigned long long *bad_d = e->d_bad;
+  CU(cudaStreamSynchronize(e->stream));
+  CU(cudaMemsetAsync(bad_d, 0xff, sizeof(unsigned long long), e->stream));
+  CU(cudaMemcpyAsync(e->d_tip_of, tip_indices, count * sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+  // runs of sequences that are adjacent in host memory go up as one copy
+  for (unsigned int i = 0; i < count;)
+  {
+    unsigned int j = i + 1;
+    while (j < count && sequences[j] == sequences[j - 1] + S) ++j;
+    CU(cudaMemcpyAsync(e->d_raw_all + (size_t)i * S, sequences[i], (size_t)(j - i) * S, cudaMemcpyHostToDevice,
+                       e->stream));
+    i = j;
+  }
+  {
+    LaunchScope ls(e, PTGPU_KERNEL_TIP_ENCODE);
+    const unsigned long long n = (unsigned long long)count * S;
+    const unsigned int blocks = (unsigned int)std::min<unsigned long long>((n + 255) / 256, 16ull * e->sm_count);
+    tip_encode_batch_kernel<<<blocks, 256, 0, e->stream>>>((const unsigned char *)e->d_raw_all, e->d_tips,
+                                                           e->d_tip_of, count, (unsigned int)S,
+                                                           e->dev.tip_stride, lut, bad_d);
+  }
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(bad_h, bad_d, sizeof(unsigned long long), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  const unsigned long long bad = *(volatile unsigned long long *)bad_h;
+  if (bad != ~0ull)
+  {
+    const unsigned int k = (unsigned int)(bad / S), site = (unsigned int)(bad % S);
+    const unsigned char ch = (unsigned char)sequences[k][site];
+    return fail(PTGPU_ERR_STATE, "Illegal state code in tip \"%c\" (tip %u, site %u)", ch ? ch : '?',
+                tip_indices[k], site);
   }
   return PTGPU_OK;
 }

@@ -292,6 +292,26 @@ __global__ void tip_encode_kernel(const unsigned char *__restrict__ raw, uint8_t
   }
 }
 
+// several tips at once: raw = [count][sites] characters, tip k goes to row tip_of[k]
+__global__ void tip_encode_batch_kernel(const unsigned char *__restrict__ raw, uint8_t *tips,
+                                        const unsigned int *__restrict__ tip_of, unsigned int count,
+                                        unsigned int sites, size_t tip_stride, TipLut lut,
+                                        unsigned long long *bad)
+{
+  __shared__ uint8_t t[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) t[i] = lut.m[i];
+  __syncthreads();
+  const unsigned long long n = (unsigned long long)count * sites;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (unsigned long long)gridDim.x * blockDim.x)
+  {
+    const unsigned int k = (unsigned int)(i / sites), site = (unsigned int)(i % sites);
+    const uint8_t mk = t[raw[i]];
+    if (!mk) atomicMin(bad, i);
+    tips[(size_t)tip_of[k] * tip_stride + site] = mk;
+  }
+}
+
 // ------------------------------------------------------------ kernel 2
 // P(t) = I + (V^-1 o expm1(lambda r t)) V per branch and category
 // (LIBPLL/core_pmatrix_avx.c:42-310).  One thread per (branch, category).

@@ -126,6 +126,13 @@ class Engine:
         """same call, `host_ptr` = address of `sites` characters (e.g. pinned memory)"""
         self._chk(self.lib.ptgpu_set_tip_states(self.h, C.c_uint(tip), C.c_void_p(host_ptr)))
 
+    def set_tip_states_batch(self, tips, host_ptrs):
+        """all listed tips in one call; host_ptrs[i] = address of tip tips[i]'s characters"""
+        t = np.ascontiguousarray(tips, dtype=np.uint32)
+        ptrs = (C.c_void_p * len(t))(*[int(p) for p in host_ptrs])
+        self._chk(self.lib.ptgpu_set_tip_states_batch(self.h, C.c_uint(len(t)),
+                                                      t.ctypes.data_as(_up), ptrs))
+
     # --- hot path -----------------------------------------------------------
     def update_prob_matrices(self, indices, lengths):
         i = np.ascontiguousarray(indices, dtype=np.uint32)

@@ -210,6 +210,8 @@ void Partition::SetTipStates(pll_utree_t* tree,
       throw std::invalid_argument(std::string("Error inserting tip label ") + tip->label +
                                   " into map (possibly a duplicate)");
   }
+  std::vector<unsigned int> tips(tip_node_count_);
+  std::vector<const char*> raw(tip_node_count_);
   for (unsigned int i = 0; i < tip_node_count_; ++i) {
     auto it = clv_of_label.find(labels[i]);
     if (it == clv_of_label.end())
@@ -217,8 +219,11 @@ void Partition::SetTipStates(pll_utree_t* tree,
                                   " does not appear in the tree");
     if (sequences[i].size() != site_count_)
       throw std::invalid_argument("Sequence " + labels[i] + " has a different length");
-    Check(ptgpu_set_tip_states(engine_, it->second, sequences[i].c_str()));
+    tips[i] = it->second;
+    raw[i] = sequences[i].c_str();
   }
+  // the reference's per-tip pll_set_tip_states loop, as one upload + one encoding kernel
+  Check(ptgpu_set_tip_states_batch(engine_, tip_node_count_, tips.data(), raw.data()));
 }
 
 // sum over all branches of log(lambda) - lambda*length in post-order, the edge

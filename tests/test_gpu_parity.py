@@ -187,6 +187,44 @@ def test_errors_are_loud():
         Engine(4, 2, 10, 3, 5, 2)                         # unsupported category count
 
 
+def test_batched_tip_upload_equals_per_tip_upload():
+    """ptgpu_set_tip_states_batch (the loop of Partition::SetTipStates in one call) against
+    ptgpu_set_tip_states: contiguous and scattered host buffers, illegal characters"""
+    import ctypes
+    from pt_b200.engine import Engine, PtGpuError, ops_array
+    rng = np.random.default_rng(5)
+    tips, sites = 6, 1000
+    aln = rng.choice(np.frombuffer(b"ACGTRYKMSWBDHVN-?acgt", dtype=np.uint8), (tips, sites)).copy()
+    ops = ops_array([(6, 0, 0, 0, -1, 1, 1, -1), (7, 1, 2, 2, -1, 3, 3, -1), (8, 2, 6, 4, 0, 7, 5, 1)])
+
+    def clvs(upload):
+        e = Engine(tips, 4, sites, 4, 9, 4)
+        try:
+            e.set_model([0.25] * 4, [1] * 6, [0.1, 0.5, 1.0, 2.4])
+            upload(e)
+            e.update_prob_matrices(list(range(9)), [0.05 * (i + 1) for i in range(9)])
+            e.update_partials(ops)
+            return e.get_clv(8).copy()
+        finally:
+            e.close()
+
+    one = clvs(lambda e: [e.set_tip_states(t, bytes(aln[t])) for t in range(tips)])
+    order = [3, 0, 5, 1, 4, 2]
+    contiguous = clvs(lambda e: e.set_tip_states_batch(range(tips), [aln[t].ctypes.data for t in range(tips)]))
+    rows = {t: np.ascontiguousarray(aln[t]) for t in order}          # separate buffers, shuffled order
+    scattered = clvs(lambda e: e.set_tip_states_batch(order, [rows[t].ctypes.data for t in order]))
+    assert np.array_equal(one, contiguous) and np.array_equal(one, scattered)
+
+    bad = aln.copy()
+    bad[4, 777] = ord("Z")
+    e = Engine(tips, 4, sites, 4, 9, 4)
+    try:
+        with pytest.raises(PtGpuError, match="Illegal state code"):
+            e.set_tip_states_batch(range(tips), [bad[t].ctypes.data for t in range(tips)])
+    finally:
+        e.close()
+
+
 @pytest.mark.parametrize("cats", [1, 2, 8])
 def test_other_category_counts(oracle, cats):
     from pt_b200.engine import ops_array
