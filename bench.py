@@ -20,6 +20,10 @@ rank scores the candidates of its own parent tree, no data-path collective
 place from /root/reference by oracle/Makefile.ref) timed on the host cores with
 the identical call sequence of SingleBranchOptimizer::EvaluateMove, one private
 partition per thread, on a bounded site sample, scaled to the full site count.
+`--workload ptw-ds1`: BASELINE configs[1] on DS1 instead -- the whole topography walk
+(`--lnl-offset -5 --optimization-radius 1`, one wanderer) through ptw_batched (pt's own
+driver objects + this engine + the batched move tester) next to the reference's
+ptw_threads on the host cores; candidates/s = EvaluateMove questions / wall time.
 """
 import argparse
 import json
@@ -442,6 +446,65 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# --------------------------------------------------------------------------
+# BASELINE configs[1] on DS1: the real drivers, wall clock
+# --------------------------------------------------------------------------
+def run_ptw_ds1(args):
+    ds1 = os.path.join(ROOT, "tests", "golden", "data", "ds1")
+    import tempfile
+
+    def walk(binary, threads):
+        with tempfile.TemporaryDirectory() as d:
+            out = os.path.join(d, "good.tsv")
+            tested = os.path.join(d, "tested.tsv")
+            cmd = [binary, "--raxml-info", os.path.join(ds1, "RAxML_info.DS1"), "--threads", str(threads),
+                   "--lnl-offset", "-5", "--optimization-radius", "1", "--tested-trees", tested,
+                   os.path.join(ds1, "RAxML_bestTree.DS1"), os.path.join(ds1, "DS1.fasta"), out]
+            t0 = time.perf_counter()
+            r = subprocess.run(cmd, capture_output=True, text=True, check=True)
+            dt = time.perf_counter() - t0
+            good = sum(1 for _ in open(out))
+            ntested = sum(1 for _ in open(tested))
+            moves = None
+            for line in r.stderr.splitlines():
+                if line.startswith("batched move testing:"):
+                    moves = int(line.split()[3])
+            return dt, good, ntested, moves
+
+    ours = os.path.join(ROOT, "oracle", "_ref", "gpu", "ptw_batched")
+    ref = os.path.join(ROOT, "oracle", "_ref", "ptw_threads")
+    if not os.path.exists(ours):
+        raise SystemExit("oracle/_ref/gpu/ptw_batched is not built (needs /root/reference at build time)")
+    sampler = ClockSampler(0)
+    sampler.start()
+    for _ in range(args.warmup):
+        walk(ours, 1)
+    wall0 = time.time()
+    runs = [walk(ours, 1) for _ in range(args.steps)]
+    clocks = sampler.stop(wall0, time.time())
+    dt = sum(r[0] for r in runs) / len(runs)
+    _, good, ntested, moves = runs[-1]
+    line = dict(metric="nni_candidates_scored_per_s", value=moves / dt, unit="candidates/s", n_gpus=1,
+                steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * dt, higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype="f64", data="DS1 (27 taxa x 1949 sites)",
+                config=dict(workload="BASELINE configs[1] on DS1: ptw topography walk, --lnl-offset -5 "
+                                     "--optimization-radius 1, one wanderer, batched move testing "
+                                     "(whole process, incl. ~1.1 s CUDA context creation)",
+                            taxa=27, sites=1949, rate_cats=4),
+                good_trees=good, tested_trees=ntested, evaluate_move_calls=moves, clocks=clocks,
+                e2e=dict(value=moves / dt, unit="candidates/s", h2d_bytes_per_step=27 * 1949,
+                         d2h_bytes_per_step=8 * moves,
+                         note="the run IS end to end: files in, tables out"))
+    if os.path.exists(ref) and not args.no_cpu_baseline:
+        T = host_cores()
+        rdt, rgood, rtested, _ = walk(ref, T)
+        line["cpu_baseline"] = dict(value=moves / rdt, unit="candidates/s", cores=T, kind="reference",
+                                    sample=f"the unmodified ptw_threads --threads {T}, same arguments, "
+                                           f"{rdt:.1f} s wall, {rgood} good / {rtested} tested trees "
+                                           "(thread interleaving makes the multi-wanderer counts vary by a few)")
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -455,8 +518,12 @@ def main():
                          "BranchNeighborhoodOptimizer semantics (BASELINE configs[1]'s tester)")
     ap.add_argument("--cpu-sample-sites", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1"])
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.workload == "ptw-ds1":
+        if int(os.environ.get("RANK", "0")) == 0:
+            run_ptw_ds1(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -166,15 +166,31 @@ __device__ __forceinline__ void blo_load_matrix(const BloView &v, unsigned int i
 
 // ---- tile bodies (T = kSitesPerPass*C threads, tile = kTileSites sites) --------
 
-// one CLV update on one tile: LIBPLL/core_partials_avx.c:366-529 (as partials_kernel)
+// The P matrices a work item needs (all C categories of up to two matrices), staged once
+// per work item in shared memory and consumed row by row (as partials_kernel_v4): a thread
+// then holds one 4-double row at a time instead of two 16-double matrices.
 template <int C>
-__device__ __forceinline__ void blo_op_tile(const BloView &v, const BloStep &st, unsigned int tile)
+__device__ __forceinline__ void blo_stage_matrices(const BloView &v, unsigned int m0, unsigned int m1,
+                                                   int count, double *smat)
+{
+  __syncthreads();   // the previous work item's rows are no longer read
+  for (int i = threadIdx.x; i < count * C * 16; i += kSitesPerPass * C)
+  {
+    const int which = i / (C * 16), c = (i / 16) % C, k = i % 16;
+    smat[(which * C + c) * kMatPad + k] = __ldcg(blo_mat_ptr<C>(v, which ? m1 : m0) + c * 16 + k);
+  }
+  __syncthreads();
+}
+
+// one CLV update on one tile: LIBPLL/core_partials_avx.c:366-529 (as partials_kernel_v4)
+template <int C>
+__device__ __forceinline__ void blo_op_tile(const BloView &v, const BloStep &st, unsigned int tile,
+                                            const double *smat)
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
-  double lm[16], rm[16];
-  blo_load_matrix<C>(v, st.b_mat, cat, lm);
-  blo_load_matrix<C>(v, st.c_mat, cat, rm);
+  const double *lmat = smat + cat * kMatPad;
+  const double *rmat = smat + (C + cat) * kMatPad;
   double *dst = const_cast<double *>(blo_clv_ptr<C>(v, st.a_clv));
   unsigned int *sdst = st.a_scal >= 0 ? blo_scal_ptr(v, st.a_scal) : nullptr;
 #pragma unroll 1
@@ -191,9 +207,17 @@ __device__ __forceinline__ void blo_op_tile(const BloView &v, const BloStep &st,
       sc[j] = blo_load_scaler(v, st.b_scal, site) + blo_load_scaler(v, st.c_scal, site);
     }
 #pragma unroll
+    for (int i = 0; i < 4; ++i)
+    {
+      double lrow[4], rrow[4];
+      lds256(lmat + 4 * i, lrow);
+      lds256(rmat + 4 * i, rrow);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) p[j][i] = __dmul_rn(dot4(lrow, l[j]), dot4(rrow, r[j]));
+    }
+#pragma unroll
     for (int j = 0; j < 2; ++j)
     {
-      combine_entry(lm, rm, l[j], r[j], p[j]);
       const unsigned int site = site0 + (half + j) * kSitesPerPass;
       bool small = (p[j][0] < PT_SCALE_THRESHOLD) & (p[j][1] < PT_SCALE_THRESHOLD) &
                    (p[j][2] < PT_SCALE_THRESHOLD) & (p[j][3] < PT_SCALE_THRESHOLD);
@@ -250,8 +274,8 @@ __device__ __forceinline__ void blo_sumtable_sweep_tile(const BloView &v, const 
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
-  double sv[kPasses][4];
-#pragma unroll
+  double ck[kPasses][3];
+#pragma unroll 1
   for (int half = 0; half < kPasses; half += 2)
   {
     double p[2][4], c[2][4];
@@ -266,56 +290,70 @@ __device__ __forceinline__ void blo_sumtable_sweep_tile(const BloView &v, const 
     for (int j = 0; j < 2; ++j)
     {
       const unsigned int site = site0 + (half + j) * kSitesPerPass;
-      sumtable_entry<C>(m, p[j], c[j], sv[half + j]);
-      if (site < v.s.sites) st256(sumtable + ((size_t)site * C + cat) * 4, sv[half + j]);
+      double sv[4];
+      sumtable_entry<C>(m, p[j], c[j], sv);
+      if (site < v.s.sites) st256(sumtable + ((size_t)site * C + cat) * 4, sv);
+      // the entry's terms of the first derivative evaluation, while it is in registers
+      if (half == 0)
+        sweep_entry_terms<C, false>(m, sv, dg, ck[j]);
+      else
+        sweep_entry_terms<C, false>(m, sv, dg, ck[2 + j]);
     }
   }
   unsigned int scv[kPasses];
 #pragma unroll
   for (int ps = 0; ps < kPasses; ++ps) scv[ps] = 0u;
   LnlProd lp;
-  sweep_tile_compute<C, false>(m, sv, scv, v.s.sites, tile, dg, out, lp, vec_end);
+  sweep_tile_finish<C, false>(m, ck, scv, v.s.sites, tile, out, lp, vec_end);
 }
 
 // edge log-likelihood of one tile (as edge_lnl_kernel); returns this thread's share
 template <int C>
 __device__ __forceinline__ double blo_lnl_tile(const BloView &v, const ModelConst &m, const BloEdge &e,
-                                               unsigned int tile)
+                                               unsigned int tile, const double *smat)
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
-  double pm[16];
-  blo_load_matrix<C>(v, e.mat, cat, pm);
-  double p[kPasses][4], c[kPasses][4];
-  unsigned int sc[kPasses];
-#pragma unroll
-  for (int ps = 0; ps < kPasses; ++ps)
-  {
-    const unsigned int site = min(site0 + ps * kSitesPerPass, v.s.sites - 1);
-    blo_load_entry<C>(v, e.p_clv, site, cat, p[ps]);
-    blo_load_entry<C>(v, e.c_clv, site, cat, c[ps]);
-    sc[ps] = blo_load_scaler(v, e.p_scal, site) + blo_load_scaler(v, e.c_scal, site);
-  }
+  const double *pm = smat + cat * kMatPad;
   double acc = 0.0;
-#pragma unroll
-  for (int ps = 0; ps < kPasses; ++ps)
+#pragma unroll 1
+  for (int half = 0; half < kPasses; half += 2)
   {
-    const unsigned int site = site0 + ps * kSitesPerPass;
-    double f[4];
+    double p[2][4], c[2][4];
+    unsigned int sc[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      const unsigned int site = min(site0 + (half + j) * kSitesPerPass, v.s.sites - 1);
+      blo_load_entry<C>(v, e.p_clv, site, cat, p[j]);
+      blo_load_entry<C>(v, e.c_clv, site, cat, c[j]);
+      sc[j] = blo_load_scaler(v, e.p_scal, site) + blo_load_scaler(v, e.c_scal, site);
+    }
+    double f[2][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-      f[i] = __dmul_rn(__dmul_rn(m.freqs[i], dot4(pm + 4 * i, c[ps])), p[ps][i]);
-    const double tk = __dadd_rn(__dadd_rn(f[0], f[1]), __dadd_rn(f[2], f[3]));
-    const double term = (tk > 0.0) ? __dmul_rn(tk, m.rate_weight) : 0.0;
-    double terma = term;
-#pragma unroll
-    for (int k = 1; k < C; ++k)
-      terma = __dadd_rn(terma, __shfl_down_sync(0xffffffffu, term, k, C));
-    if (cat == 0 && site < v.s.sites)
     {
-      double lk = log(terma);
-      if (sc[ps]) lk = __dadd_rn(lk, __dmul_rn((double)sc[ps], m.log_scale_thr));
-      acc = __dadd_rn(acc, lk);
+      double row[4];
+      lds256(pm + 4 * i, row);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) f[j][i] = __dmul_rn(__dmul_rn(m.freqs[i], dot4(row, c[j])), p[j][i]);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      const unsigned int site = site0 + (half + j) * kSitesPerPass;
+      const double tk = __dadd_rn(__dadd_rn(f[j][0], f[j][1]), __dadd_rn(f[j][2], f[j][3]));
+      const double term = (tk > 0.0) ? __dmul_rn(tk, m.rate_weight) : 0.0;
+      double terma = term;
+#pragma unroll
+      for (int k = 1; k < C; ++k)
+        terma = __dadd_rn(terma, __shfl_down_sync(0xffffffffu, term, k, C));
+      if (cat == 0 && site < v.s.sites)
+      {
+        double lk = log(terma);
+        if (sc[j]) lk = __dadd_rn(lk, __dmul_rn((double)sc[j], m.log_scale_thr));
+        acc = __dadd_rn(acc, lk);
+      }
     }
   }
   return acc;
@@ -334,6 +372,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)
   constexpr int T = kSitesPerPass * C;
   extern __shared__ __align__(16) double ring[];
   __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  __shared__ __align__(16) double smat[2 * C * kMatPad];
   __shared__ double sh_len;
   __shared__ int sh_done, sh_status;
   // fin[e] >= epoch <=> candidate e's solve of the current OPT step has finished.  The mark
@@ -374,7 +413,9 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)
     {
       const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
       if (!want(e)) continue;
-      const double part = block_sum<T>(blo_lnl_tile<C>(a.v, a.m, edges[e], tile), red);
+      const BloEdge edge = edges[e];
+      blo_stage_matrices<C>(a.v, edge.mat, edge.mat, 1, smat);
+      const double part = block_sum<T>(blo_lnl_tile<C>(a.v, a.m, edge, tile, smat), red);
       if (threadIdx.x == 0) a.tile_partials[(size_t)e * a.ntiles + tile] = part;
     }
     grid.sync();
@@ -407,7 +448,9 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)
       {
         const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
         const BloStep st = row[e];
-        if (st.type == BLO_OP && live(e)) blo_op_tile<C>(a.v, st, tile);
+        if (st.type != BLO_OP || !live(e)) continue;
+        blo_stage_matrices<C>(a.v, st.b_mat, st.c_mat, 2, smat);
+        blo_op_tile<C>(a.v, st, tile, smat);
       }
       grid.sync();
       return;

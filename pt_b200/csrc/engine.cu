@@ -1283,11 +1283,17 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
   const size_t per_cand = (size_t)npriv * clv_bytes + stride * sizeof(double) +
                           (size_t)(e->nchunks * 3 + e->ntiles) * sizeof(double) +
                           (size_t)nlen * (e->cats * 16 + 1) * sizeof(double);
-  size_t free_b = 0, total_b = 0;
-  CU(cudaMemGetInfo(&free_b, &total_b));
-  const size_t have = e->lcap_cand * ((size_t)e->lcap_clvs * clv_bytes + stride * sizeof(double));
-  const size_t chunk = std::min<size_t>(count, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
-  if (chunk > e->lcap_cand || npriv > e->lcap_clvs || nlen > e->lcap_lens)
+  size_t chunk = count;
+  const bool fits = count <= e->lcap_cand && npriv <= e->lcap_clvs && nlen <= e->lcap_lens;
+  if (!fits)
+  {
+    // grow the scratch: as many candidates per launch as 80 % of the free memory holds
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    const size_t have = e->lcap_cand * ((size_t)e->lcap_clvs * clv_bytes + stride * sizeof(double));
+    chunk = std::min<size_t>(count, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
+  }
+  if (!fits && (chunk > e->lcap_cand || npriv > e->lcap_clvs || nlen > e->lcap_lens))
   {
     const size_t nc = std::max<size_t>(chunk, e->lcap_cand), ncl = std::max<size_t>(npriv, e->lcap_clvs),
                  nl = std::max<size_t>(nlen, e->lcap_lens);

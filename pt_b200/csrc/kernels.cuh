@@ -770,12 +770,29 @@ __device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[
 
 // One tile of the site sweep.  out[0] += -L'/L terms, out[1] += second
 // derivative terms, out[2] += log-likelihood terms (only if WITH_LNL).
+// ck[q] of one sumtable entry: ((0 + s0 d0) + s1 d1) + s2 d2) + s3 d3 for q = 0, 1, 2
+// (LIBPLL/core_derivatives_avx.c:1019-1034), and the weighted likelihood term if asked for
 template <int C, bool WITH_LNL>
-__device__ __forceinline__ void sweep_tile_compute(const ModelConst &m, const double (&sv)[kPasses][4],
-                                                   const unsigned int (&scv)[kPasses], unsigned int sites,
-                                                   unsigned int tile, const double (&dg)[4][3],
-                                                   double out[3], LnlProd &lp,
-                                                   unsigned long long vec_end)
+__device__ __forceinline__ void sweep_entry_terms(const ModelConst &m, const double (&sv)[4],
+                                                  const double (&dg)[4][3], double (&ck)[WITH_LNL ? 4 : 3])
+{
+#pragma unroll
+  for (int q = 0; q < 3; ++q)
+  {
+    double a = __dadd_rn(0.0, __dmul_rn(sv[0], dg[0][q]));
+    a = __dadd_rn(a, __dmul_rn(sv[1], dg[1][q]));
+    a = __dadd_rn(a, __dmul_rn(sv[2], dg[2][q]));
+    ck[q] = __dadd_rn(a, __dmul_rn(sv[3], dg[3][q]));
+  }
+  if (WITH_LNL) ck[WITH_LNL ? 3 : 2] = (ck[0] > 0.0) ? __dmul_rn(ck[0], m.rate_weight) : 0.0;
+}
+
+// category sums of a tile's entry terms and the per-site contributions to d1, d2 (and lnL)
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void sweep_tile_finish(const ModelConst &m, const double (&ck)[kPasses][WITH_LNL ? 4 : 3],
+                                                  const unsigned int (&scv)[kPasses], unsigned int sites,
+                                                  unsigned int tile, double out[3], LnlProd &lp,
+                                                  unsigned long long vec_end)
 {
   const int cat = threadIdx.x % C;
   const unsigned int site0 = tile * kTileSites + threadIdx.x / C;
@@ -784,23 +801,6 @@ __device__ __forceinline__ void sweep_tile_compute(const ModelConst &m, const do
   const unsigned int full =
       vec_end == ~0ull ? sites / 4 * 4 : (unsigned int)min((unsigned long long)sites, vec_end);
   constexpr int NQ = WITH_LNL ? 4 : 3;
-  double ck[kPasses][NQ];
-  {
-#pragma unroll
-    for (int ps = 0; ps < kPasses; ++ps)
-    {
-#pragma unroll
-      for (int q = 0; q < 3; ++q)
-      {
-        // ((0 + s0 d0) + s1 d1) + s2 d2) + s3 d3  (LIBPLL/core_derivatives_avx.c:1019-1034)
-        double a = __dadd_rn(0.0, __dmul_rn(sv[ps][0], dg[0][q]));
-        a = __dadd_rn(a, __dmul_rn(sv[ps][1], dg[1][q]));
-        a = __dadd_rn(a, __dmul_rn(sv[ps][2], dg[2][q]));
-        ck[ps][q] = __dadd_rn(a, __dmul_rn(sv[ps][3], dg[3][q]));
-      }
-      if (WITH_LNL) ck[ps][NQ - 1] = (ck[ps][0] > 0.0) ? __dmul_rn(ck[ps][0], m.rate_weight) : 0.0;
-    }
-  }
   if (C == 4)
   {
     double r[NQ];
@@ -825,6 +825,20 @@ __device__ __forceinline__ void sweep_tile_compute(const ModelConst &m, const do
       if (cat == 0 && site < sites) site_terms<WITH_LNL>(m, lk, lk[NQ - 1], site, full, scv[ps], out, lp);
     }
   }
+}
+
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void sweep_tile_compute(const ModelConst &m, const double (&sv)[kPasses][4],
+                                                   const unsigned int (&scv)[kPasses], unsigned int sites,
+                                                   unsigned int tile, const double (&dg)[4][3],
+                                                   double out[3], LnlProd &lp,
+                                                   unsigned long long vec_end)
+{
+  constexpr int NQ = WITH_LNL ? 4 : 3;
+  double ck[kPasses][NQ];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps) sweep_entry_terms<C, WITH_LNL>(m, sv[ps], dg, ck[ps]);
+  sweep_tile_finish<C, WITH_LNL>(m, ck, scv, sites, tile, out, lp, vec_end);
 }
 
 // The summed scaler words a thread will need in the epilogue of this tile, fetched
