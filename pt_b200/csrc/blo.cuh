@@ -439,85 +439,128 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)
     grid.sync();
   };
 
-  auto run_step = [&](unsigned int k) {
-    const BloStep *row = a.steps + (size_t)k * a.B;
-    const int type = a.step_type[k];
-    if (type == BLO_OP)
+  // CLV updates [k, k2) of candidate e on one tile, back to back.  No grid barrier is needed
+  // between them: an entry written by one update is re-read by the next only by the thread
+  // that wrote it (same tile, same thread <-> (site, category) mapping), the scaler word of a
+  // site by the lanes next to its writer (ordered by the CTA barrier of the matrix staging).
+  auto update_run_tile = [&](unsigned int e, unsigned int tile, unsigned int k, unsigned int k2) {
+    for (unsigned int kk = k; kk < k2; ++kk)
     {
-      for (unsigned int w = blockIdx.x; w < a.B * a.ntiles; w += gridDim.x)
-      {
-        const unsigned int e = w / a.ntiles, tile = w % a.ntiles;
-        const BloStep st = row[e];
-        if (st.type != BLO_OP || !live(e)) continue;
-        blo_stage_matrices<C>(a.v, st.b_mat, st.c_mat, 2, smat);
-        blo_op_tile<C>(a.v, st, tile, smat);
-      }
-      grid.sync();
-      return;
+      const BloStep st = a.steps[(size_t)kk * a.B + e];
+      if (st.type != BLO_OP) continue;
+      blo_stage_matrices<C>(a.v, st.b_mat, st.c_mat, 2, smat);
+      blo_op_tile<C>(a.v, st, tile, smat);
     }
+  };
+
+  auto wants = [&](unsigned int e, const BloStep &st) { return st.type == BLO_OPT && live(e); };
+  auto start_length = [&](unsigned int e, const BloStep &st) {
+    double guess = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
+    if (a.procedure == 0 && (guess < a.xmin || guess > a.xmax))
+      guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
+    return guess;
+  };
+  const size_t pstride = (size_t)a.B * a.nchunks * 3;
+  // a run of CLV updates can share a phase with the edge optimisation that follows it only
+  // if both use the same work items ((candidate, chunk): what a thread wrote is what it reads),
+  // i.e. when a chunk is a tile (alignments up to 64k sites -- where barriers are what costs)
+  const bool chunk_items_ok = a.chunk_tiles == 1;
+
+  // Executes the steps from k on that form one group and returns the first step after it:
+  //   MAT ... MAT          one phase
+  //   OP ... OP [OPT]      the updates of a tile back to back; the optimisation's sumtable and
+  //                        first derivative evaluation in the same phase where possible; then
+  //                        one phase per further evaluation
+  auto run_group = [&](unsigned int k, unsigned int kend) -> unsigned int {
+    const int type = a.step_type[k];
     if (type == BLO_MAT)
     {
-      // P matrix of an edge at its current length (a traversal's pll_update_prob_matrices)
-      for (unsigned int w = blockIdx.x * T + threadIdx.x; w < a.B * C; w += gridDim.x * T)
+      // P matrices of edges at their current lengths (a traversal's pll_update_prob_matrices)
+      unsigned int k2 = k;
+      while (k2 < kend && a.step_type[k2] == BLO_MAT) ++k2;
+      const unsigned int n = (k2 - k) * a.B * C;
+      for (unsigned int w = blockIdx.x * T + threadIdx.x; w < n; w += gridDim.x * T)
       {
-        const unsigned int e = w / C, c = w % C;
-        const BloStep st = row[e];
+        const unsigned int c = w % C, e = (w / C) % a.B, kk = k + w / (C * a.B);
+        const BloStep st = a.steps[(size_t)kk * a.B + e];
         if (st.type == BLO_MAT && live(e))
           pmatrix_block(a.m, __ldcg(a.lens + (size_t)e * a.NL + st.slot), c,
                         blo_mat_ptr<C>(a.v, st.b_mat) + c * 16);
       }
       grid.sync();
-      return;
+      return k2;
     }
-    if (type != BLO_OPT) return;
-    // Edge optimisation, one grid barrier per derivative evaluation.
-    // Phase 0 arms the solve, builds the sumtable and evaluates the derivatives at the
-    // start length from the entries while they are still in registers.  Phase p >= 1:
+    if (type != BLO_OP && type != BLO_OPT) return k + 1;
+
+    unsigned int k2 = k;
+    while (k2 < kend && a.step_type[k2] == BLO_OP) ++k2;
+    const bool has_opt = k2 < kend && a.step_type[k2] == BLO_OPT;
+    const bool has_ops = k2 > k;
+    const bool fused = has_opt && has_ops && chunk_items_ok;
+    const BloStep *row = a.steps + (size_t)(has_opt ? k2 : k) * a.B;   // the OPT's row
+
+    // Phase A (tile items): the updates alone, when they cannot share the optimisation's work
+    // items.  Phase B (chunk items): the optimisation's phase 0 -- arm the solve, build the
+    // sumtable and evaluate the derivatives at the start length from the entries while they
+    // are in registers -- preceded, tile by tile, by the updates if they are fused in.
+    // (One loop body for both so that the tile code exists once.)
+    for (int phase = 0; phase < 2; ++phase)
+    {
+      const bool by_chunk = phase == 1;
+      const bool ops_here = by_chunk ? fused : (has_ops && !fused);
+      const bool opt_here = by_chunk && has_opt;
+      if (!ops_here && !opt_here) continue;
+      if (opt_here)
+      {
+        epoch += 1;
+        for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+        {
+          if (threadIdx.x != 0) continue;
+          NewtonState ns{};
+          const BloStep st = row[e];
+          const bool on = wants(e, st);
+          if (on) ns.len = start_length(e, st); else ns.done = 1;
+          a.nst[e] = ns;
+          if (!on) a.fin[e] = epoch;
+        }
+      }
+      const unsigned int per = by_chunk ? a.nchunks : a.ntiles;
+      for (unsigned int w = blockIdx.x; w < a.B * per; w += gridDim.x)
+      {
+        const unsigned int e = w / per, item = w % per;
+        if (!live(e)) continue;
+        const BloStep st = row[e];
+        const bool on = opt_here && st.type == BLO_OPT;
+        if (!on && !ops_here) continue;
+        const unsigned int t0 = by_chunk ? item * a.chunk_tiles : item;
+        const unsigned int t1 = by_chunk ? min(t0 + a.chunk_tiles, a.ntiles) : item + 1;
+        if (ops_here)
+          for (unsigned int tile = t0; tile < t1; ++tile) update_run_tile(e, tile, k, k2);
+        if (!on) continue;
+        double dg[4][3];
+        diag_regs<C>(a.m, start_length(e, st), cat, dg);
+        double out[3] = {0.0, 0.0, 0.0};
+        for (unsigned int tile = t0; tile < t1; ++tile)
+          blo_sumtable_sweep_tile<C>(a.v, a.m, st.a_clv, st.b_clv, a.sumtables + (size_t)e * a.entry_stride,
+                                     tile, dg, out, a.vec_end);
+        const double s1 = block_sum<T>(out[0], red);
+        const double s2 = block_sum<T>(out[1], red);
+        if (threadIdx.x == 0)
+        {
+          a.partials[(size_t)w * 3 + 0] = s1;
+          a.partials[(size_t)w * 3 + 1] = s2;
+        }
+      }
+      grid.sync();
+    }
+    if (!has_opt) return k2;
+
+    // Edge optimisation, one grid barrier per further derivative evaluation.  Phase p >= 1:
     // EVERY CTA that holds a chunk of candidate e first redoes e's reduction and scalar
     // Newton step from evaluation p-1 (same inputs, same code => same result in all of
     // them; only the CTA of chunk 0 publishes it), then sweeps its chunk at the new
     // length.  Partials and Newton state alternate between two buffers so that a fast CTA
     // never overwrites what a slow one still reads.
-    auto wants = [&](unsigned int e, const BloStep &st) { return st.type == BLO_OPT && live(e); };
-    auto start_length = [&](unsigned int e, const BloStep &st) {
-      double guess = __ldcg(a.lens + (size_t)e * a.NL + st.slot);
-      if (a.procedure == 0 && (guess < a.xmin || guess > a.xmax))
-        guess = 0.1;  // PLLMOD_OPT_DEFAULT_BRANCH_LEN
-      return guess;
-    };
-    const size_t pstride = (size_t)a.B * a.nchunks * 3;
-    epoch += 1;
-    for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
-    {
-      if (threadIdx.x != 0) continue;
-      NewtonState ns{};
-      const BloStep st = row[e];
-      const bool on = wants(e, st);
-      if (on) ns.len = start_length(e, st); else ns.done = 1;
-      a.nst[e] = ns;
-      if (!on) a.fin[e] = epoch;
-    }
-    for (unsigned int w = blockIdx.x; w < a.B * a.nchunks; w += gridDim.x)
-    {
-      const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
-      const BloStep st = row[e];
-      if (!wants(e, st)) continue;
-      double dg[4][3];
-      diag_regs<C>(a.m, start_length(e, st), cat, dg);
-      double out[3] = {0.0, 0.0, 0.0};
-      const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-      for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
-        blo_sumtable_sweep_tile<C>(a.v, a.m, st.a_clv, st.b_clv, a.sumtables + (size_t)e * a.entry_stride,
-                                   tile, dg, out, a.vec_end);
-      const double s1 = block_sum<T>(out[0], red);
-      const double s2 = block_sum<T>(out[1], red);
-      if (threadIdx.x == 0)
-      {
-        a.partials[(size_t)w * 3 + 0] = s1;
-        a.partials[(size_t)w * 3 + 1] = s2;
-      }
-    }
-    grid.sync();
     for (unsigned int p = 1; p <= a.max_newton; ++p)
     {
       const double *prd = a.partials + ((p - 1) & 1) * pstride;
@@ -597,6 +640,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)
       for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= __ldcg(a.fin + e) < epoch;
       if (!__syncthreads_or(running)) break;
     }
+    return k2 + 1;
   };
 
   for (unsigned int e = blockIdx.x * T + threadIdx.x; e < a.B; e += gridDim.x * T) a.fin[e] = 0;
@@ -625,7 +669,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)
       const unsigned int variant = round < 0 ? 0u : min((unsigned int)round, a.n_bodies - 1);
       const unsigned int k0 = round < 0 ? 0u : a.n_pro + variant * a.n_body;
       const unsigned int k1 = k0 + (round < 0 ? a.n_pro : a.n_body);
-      for (unsigned int k = k0; k < k1; ++k) run_step(k);
+      for (unsigned int k = k0; k < k1;) k = run_group(k, k1);
     }
     lnl_phase(finishing ? a.final_edge : a.smooth_edge,
               [&](unsigned int e) { return round < 0 || finishing || live(e); },

@@ -1482,6 +1482,14 @@ extern "C" int ptgpu_optimize_all_branches(ptgpu_engine *e, unsigned int n_prolo
   r.smoothings_out = passes_out;
   int rc = run_blo(e, r);
   if (rc) return rc;
+  if (getenv("PTGPU_DEBUG"))
+  {
+    unsigned int cnt[4] = {0, 0, 0, 0};
+    for (unsigned int k = n_prologue; k < n_prologue + n_body; ++k) cnt[steps[k].type & 3] += 1;
+    fprintf(stderr, "[ptgpu] all-branches program: prologue %u, body %u x %u (first body: %u OP, %u OPT, %u MAT, %u NOP), "
+                    "%d passes, lnL %.6f\n", n_prologue, n_body, n_bodies, cnt[1], cnt[2], cnt[3], cnt[0],
+            passes_out ? *passes_out : -1, *lnl_out);
+  }
   if (status_out && *status_out)
     return fail(PTGPU_ERR_NOT_FINITE, *status_out == 1 ? "d1 is not finite" : "d2 is not finite");
   return PTGPU_OK;
