@@ -213,6 +213,24 @@ class Engine:
             st.ctypes.data_as(ip), sm.ctypes.data_as(ip)))
         return lens, lnl, st, sm
 
+    def optimize_all_branches(self, steps, n_prologue, n_body, n_bodies, edge, lengths0,
+                              prior_edges=(), max_iter=32, eps=1e-6, map_lambda=0.0, max_passes=33):
+        """Partition::OptimizeAllBranches as one persistent kernel; `steps` is a STEP_DTYPE
+        array on the engine's own index spaces (see include/ptgpu.h).  Returns
+        (lengths [prob_matrices], lnl, passes)."""
+        st = np.ascontiguousarray(steps)
+        ed = np.ascontiguousarray(edge)
+        l0 = np.ascontiguousarray(lengths0, dtype=np.float64)
+        pr = np.ascontiguousarray(prior_edges, dtype=np.uint32)
+        out = np.empty_like(l0); lnl = C.c_double(); status = C.c_int(); passes = C.c_int()
+        self._chk(self.lib.ptgpu_optimize_all_branches(
+            self.h, C.c_uint(n_prologue), C.c_uint(n_body), C.c_uint(n_bodies),
+            st.ctypes.data_as(C.c_void_p), ed.ctypes.data_as(C.c_void_p), _d(l0),
+            pr.ctypes.data_as(_up), C.c_uint(len(pr)), C.c_uint(max_iter), C.c_double(eps),
+            C.c_double(map_lambda), C.c_uint(max_passes), _d(out), C.byref(lnl), C.byref(status),
+            C.byref(passes)))
+        return out, lnl.value, passes.value
+
     # --- test hooks -----------------------------------------------------------
     def get_clv(self, idx):
         out = np.empty(self.sites * self.cats * 4)

@@ -16,7 +16,7 @@ the C++ twin is pt::pll::Partition::ScoreNniNeighborhood(tree, radius).
 """
 import numpy as np
 
-BLO_NOP, BLO_OP, BLO_OPT = 0, 1, 2
+BLO_NOP, BLO_OP, BLO_OPT, BLO_MAT = 0, 1, 2, 3
 NNI_LEFT, NNI_RIGHT = 1, 2
 
 STEP_DTYPE = np.dtype([
