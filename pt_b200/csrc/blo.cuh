@@ -366,8 +366,11 @@ __device__ __forceinline__ double blo_lnl_tile(const BloView &v, const ModelCons
 // instead of a ~2 us round of global atomics): for programs whose (candidate, tile) work
 // fits a handful of CTAs -- OptimizeAllBranches on an alignment of a few thousand sites is
 // several thousand barriers per call, and nothing else.
+#ifndef PT_BLO_MINB
+#define PT_BLO_MINB 2
+#endif
 template <int C, bool CLUSTER>
-__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? 2 : 1)) blo_kernel(BloArgs a)
+__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO_MINB : 1)) blo_kernel(BloArgs a)
 {
   constexpr int T = kSitesPerPass * C;
   extern __shared__ __align__(16) double ring[];
