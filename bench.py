@@ -5,7 +5,8 @@ Workload (BASELINE.json configs[2]/[3] shape, the one the north_star target is
 quoted on): synthetic 64 taxa x 1,000,000 sites, GTR+Gamma4 (DS1's model).
 One STEP = one pass of the hot path over one parent tree:
     P matrices of all 2n-3 branches            (kernel 2)
-    all 3(n-2) directional CLVs                (kernel 1, one launch)
+    the directional CLVs the candidates read   (kernel 1, one launch; 105 of the
+                                                3(n-2) = 186: none that faces a tip)
     every NNI candidate of Wanderer::QueueMoves (2(n-2) = 124) scored with
     SingleBranchOptimizer semantics            (prepare + cooperative Newton)
 `value`  = candidates/s with the alignment resident in HBM, CUDA events on the
@@ -302,8 +303,6 @@ def run_ours(args):
     br = tree.branches()
     midx = np.array(list(br.keys()), dtype=np.uint32)
     mlen = np.array(list(br.values()), dtype=np.float64)
-    plan_rows = tree.directional_plan()
-    plan = ops_array(plan_rows)
     cand_rows = tree.nni_candidates()
     cands = cand_array(cand_rows)
     ncand = len(cands)
@@ -313,6 +312,11 @@ def run_ours(args):
         from pt_b200.local_blo import Program
         prog = Program(tree, args.radius, n, nbuf, nbuf, 2 * n - 3)
     last = {}
+    # only the directional CLVs the batch reads (and what they are computed from): none that
+    # faces a tip, nor the one facing a cherry from its only inner neighbour
+    plan_rows = tree.directional_plan(prog.referenced_clvs if prog is not None
+                                      else tree.referenced_clvs(cand_rows))
+    plan = ops_array(plan_rows)
 
     def step():
         e.update_prob_matrices(midx, mlen)
@@ -424,7 +428,8 @@ def run_ours(args):
         config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]/[3] shape): "
                              f"per step all {ncand} NNI candidates of one parent tree per GPU, "
                              + tester_name(args.radius) + " semantics, incl. P matrices and "
-                             "all directional CLVs", taxa=n, sites=S, rate_cats=4,
+                             f"the {len(plan_rows)} directional CLVs the candidates read "
+                             f"(of 3(n-2) = {3 * (n - 2)})", taxa=n, sites=S, rate_cats=4,
                     candidates_per_step_per_gpu=ncand, parallelism=f"candidate-parallel x{world}",
                     l2="inputs (>20 GB of CLVs per step) far exceed the 126 MB L2; no flush needed"),
         clv_site_updates_per_s=world * site_updates / (kt["partials"][0] * 1e-3) if kt["partials"][0] else None,

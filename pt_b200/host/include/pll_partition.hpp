@@ -129,7 +129,7 @@ class Partition
   void OptimizeAllBranchesFused(pll_unode_t* tree);
   unsigned int DirectionalClv(const pll_unode_t* record) const;
   int DirectionalScaler(const pll_unode_t* record) const;
-  void UpdateDirectionalClvs(pll_utree_t* tree);
+  void UpdateDirectionalClvs(pll_utree_t* tree, const std::vector<unsigned int>& needed);
   std::vector<NniScore> ScoreNniNeighborhoodLocal(pll_utree_t* tree, int radius);
   double LocalBranchOptimization(pll_unode_t* tree, double bl_min, double bl_max,
                                  double tolerance, int smoothings, int radius);

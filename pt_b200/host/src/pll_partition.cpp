@@ -676,9 +676,12 @@ int Partition::DirectionalScaler(const pll_unode_t* r) const
   return r->next ? static_cast<int>(directional_base_ + (r->node_index - tip_node_count_)) : -1;
 }
 
-// All P matrices at the tree's current lengths and all 3(n-2) directional CLVs
-// (one engine call each).
-void Partition::UpdateDirectionalClvs(pll_utree_t* tree)
+// All P matrices at the tree's current lengths and the directional CLVs listed in
+// `needed` (engine CLV indices; anything that is not a directional buffer is ignored) plus
+// the ones they are computed from -- one engine call each.  An NNI batch never reads a CLV
+// that faces a tip (a third of the 3(n-2)) nor the one facing a cherry from its only inner
+// neighbour, so those are not computed.
+void Partition::UpdateDirectionalClvs(pll_utree_t* tree, const std::vector<unsigned int>& needed)
 {
   if (!directional_base_)
     throw std::logic_error("directional CLV buffers were disabled (PTGPU_NO_DIRECTIONAL)");
@@ -736,20 +739,24 @@ void Partition::UpdateDirectionalClvs(pll_utree_t* tree)
       plan.push_back(op);
     }
   };
+  std::vector<char> wanted(3 * inner, 0);
+  const unsigned int first = tips + directional_base_;
+  for (unsigned int clv : needed)
+    if (clv >= first && clv - first < wanted.size()) wanted[clv - first] = 1;
   for (unsigned int i = tips; i < tips + inner; ++i) {
     pll_unode_t* n = tree->nodes[i];
-    schedule(n);
-    schedule(n->next);
-    schedule(n->next->next);
+    pll_unode_t* ring[3] = {n, n->next, n->next->next};
+    for (pll_unode_t* r : ring)
+      if (wanted[r->node_index - tips]) schedule(r);
   }
-  Check(ptgpu_update_partials(engine_, plan.data(), static_cast<unsigned int>(plan.size())));
+  if (!plan.empty())
+    Check(ptgpu_update_partials(engine_, plan.data(), static_cast<unsigned int>(plan.size())));
 }
 
 std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree, int radius)
 {
   if (radius < 0) throw std::invalid_argument("optimization radius must not be negative");
   StatScope stat(kStatNeighborhood);
-  UpdateDirectionalClvs(tree);
   if (radius > 0) return ScoreNniNeighborhoodLocal(tree, radius);
 
   const unsigned int tips = tip_node_count_;
@@ -795,6 +802,16 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tr
     }
   }
   if (cands.empty()) return out;
+
+  // bring the directional CLVs the candidates read up to date
+  std::vector<unsigned int> needed;
+  needed.reserve(4 * cands.size());
+  for (const ptgpu_nni_candidate_t& c : cands)
+    for (const ptgpu_operation_t* op : {&c.p, &c.q}) {
+      needed.push_back(op->child1_clv_index);
+      needed.push_back(op->child2_clv_index);
+    }
+  UpdateDirectionalClvs(tree, needed);
 
   std::vector<double> len(cands.size()), lnl(cands.size());
   std::vector<int> status(cands.size());
@@ -1005,6 +1022,25 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhoodLocal(pll_utree_
     }
   }
   if (progs.empty()) return out;
+
+  // bring the directional CLVs the programs read up to date
+  {
+    std::vector<unsigned int> needed;
+    auto note = [&needed](const ClvRef& r) {
+      if (!r.is_private) needed.push_back(r.index);
+    };
+    for (const CandidateProgram& c : progs) {
+      for (const SymStep& st : c.steps) {
+        if (st.type == PTGPU_BLO_NOP) continue;
+        note(st.a);
+        note(st.b);
+        if (st.type == PTGPU_BLO_OP) note(st.c);
+      }
+      note(c.smooth_parent);
+      note(c.smooth_child);
+    }
+    UpdateDirectionalClvs(tree, needed);
+  }
 
   const unsigned int count = static_cast<unsigned int>(progs.size());
   unsigned int n_private = 1, n_lengths = 1;

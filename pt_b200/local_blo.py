@@ -210,3 +210,14 @@ class Program:
                 arr[i]["child_clv"], arr[i]["child_scaler"] = rclv(i, chi)
                 arr[i]["matrix"] = rmat(i, mat)
         self.slot_edges = [dict((s, e) for e, s in c.slots.items()) for c in cands]
+        # the engine's (directional) CLVs the programs read: what must be up to date before
+        # ptgpu_optimize_local_batch -- never one that faces a tip
+        self.referenced_clvs = set()
+        for c in cands:
+            for st in c.steps:
+                for ref in st[1:6]:
+                    if isinstance(ref, tuple) and ref[0] == "g" and len(ref) == 3 and ref[1] >= tips:
+                        self.referenced_clvs.add(ref[1])
+            for ref in c.smooth + c.final:
+                if ref[0] == "g" and len(ref) == 3 and ref[1] >= tips:
+                    self.referenced_clvs.add(ref[1])

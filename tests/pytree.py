@@ -207,9 +207,17 @@ class Tree:
     def dir_scaler(self, r):
         return -1 if r.is_tip else r.node_index - self.tip_count
 
-    def directional_plan(self):
-        """ops computing all 3(n-2) directional CLVs in dependency order"""
+    def directional_plan(self, needed=None):
+        """ops computing the directional CLVs in dependency order: all 3(n-2) of them, or --
+        with `needed` = an iterable of directional CLV indices (dir_clv values) -- only those
+        and the ones they are computed from.  An NNI batch never reads a CLV that faces a tip
+        (a third of them) nor the one that faces a cherry from its only inner neighbour."""
         done, ops = set(), []
+        if needed is not None:
+            roots = [self.by_index[i] for i in sorted(set(int(x) for x in needed))
+                     if i >= self.tip_count]
+        else:
+            roots = [r for n in self.nodes[self.tip_count:] for r in (n, n.next, n.next.next)]
 
         def need(r):
             if r.is_tip or r.node_index in done:
@@ -230,10 +238,17 @@ class Tree:
                     stack.append((b, False))
                     stack.append((a, False))
 
-        for n in self.nodes[self.tip_count:]:
-            for r in (n, n.next, n.next.next):
-                need(r)
+        for r in roots:
+            need(r)
         return ops
+
+    @staticmethod
+    def referenced_clvs(cands):
+        """directional CLV indices the candidate rows of nni_candidates() read"""
+        out = set()
+        for (_, _, pop, qop, _) in cands:
+            out.update((pop[2], pop[5], qop[2], qop[5]))
+        return out
 
     def nni_candidates(self):
         """[(node_index of p, type, p-op row, q-op row, length0)] in QueueMoves order"""

@@ -148,6 +148,37 @@ def test_batch_is_bit_identical_to_single_edge_calls(name, radius):
         s.close()
 
 
+@pytest.mark.parametrize("radius", [0, 1, 2])
+def test_pruned_directional_plan_gives_identical_scores(radius):
+    """only the directional CLVs a batch reads need to be current: never one that faces a tip"""
+    from pt_b200.engine import ops_array
+    from pytree import cand_array
+    tree, seqs, g = load_set("ds1")
+    model = model_of(g)
+    results = []
+    for pruned in (False, True):
+        e = make_engine(tree, seqs, *model, directional=True)
+        try:
+            br = tree.branches()
+            e.update_prob_matrices(list(br.keys()), list(br.values()))
+            if radius == 0:
+                cands = tree.nni_candidates()
+                plan = tree.directional_plan(tree.referenced_clvs(cands) if pruned else None)
+                e.update_partials(ops_array(plan))
+                lens, lnl, status = e.score_nni_batch(cand_array(cands))
+            else:
+                prog = program(tree, radius)
+                plan = tree.directional_plan(prog.referenced_clvs if pruned else None)
+                e.update_partials(ops_array(plan))
+                lens, lnl, status, _ = e.optimize_local_batch(prog)
+            results.append((len(plan), lens.copy(), lnl.copy(), status.copy()))
+        finally:
+            e.close()
+    full, pruned = results
+    assert pruned[0] < full[0] == 3 * (tree.tip_count - 2)
+    assert all(np.array_equal(a, b) for a, b in zip(full[1:], pruned[1:]))
+
+
 def test_batch_on_a_larger_alignment_matches_sampled_sequential_runs():
     import synth
     taxa, sites = 24, 20000
