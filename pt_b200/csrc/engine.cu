@@ -97,6 +97,7 @@ struct ptgpu_engine
   double *d_lsum = nullptr, *d_llens = nullptr, *d_lpart = nullptr, *d_ltile = nullptr;
   BloStep *d_lsteps = nullptr; BloEdge *d_ledges = nullptr; BloCand *d_lcand = nullptr;
   NewtonState *d_lnst = nullptr; int *d_ltypes = nullptr, *d_lfin = nullptr; unsigned int *d_lprior = nullptr;
+  unsigned int blo_max_chunk = 0;          // env PTGPU_BLO_MAX_CHUNK (0 = as many as memory holds)
   unsigned int blo_cluster_work = 2 * 8;   // largest (candidates x tiles) run as one cluster; env PTGPU_BLO_CLUSTER_WORK
   size_t lcap_cand = 0, lcap_clvs = 0, lcap_lens = 0, lcap_steps = 0, lcap_types = 0, lcap_prior = 0;
   int blo_blocks_per_sm = 0;
@@ -260,6 +261,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   if (const char *pv = getenv("PTGPU_PREPARE")) e->prepare_version = atoi(pv);
   if (const char *pv = getenv("PTGPU_LNL_MARGIN")) e->lnl_margin = atof(pv);
   if (const char *pv = getenv("PTGPU_BLO_CLUSTER_WORK")) e->blo_cluster_work = (unsigned int)atoi(pv);
+  if (const char *pv = getenv("PTGPU_BLO_MAX_CHUNK")) e->blo_max_chunk = (unsigned int)atoi(pv);
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
@@ -1284,14 +1286,17 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
                           (size_t)(e->nchunks * 3 + e->ntiles) * sizeof(double) +
                           (size_t)nlen * (e->cats * 16 + 1) * sizeof(double);
   size_t chunk = count;
-  const bool fits = count <= e->lcap_cand && npriv <= e->lcap_clvs && nlen <= e->lcap_lens;
+  // PTGPU_BLO_MAX_CHUNK: candidates per launch (tests use it to exercise the chunked path that
+  // otherwise needs a batch larger than the free memory)
+  if (e->blo_max_chunk && chunk > e->blo_max_chunk) chunk = e->blo_max_chunk;
+  const bool fits = chunk <= e->lcap_cand && npriv <= e->lcap_clvs && nlen <= e->lcap_lens;
   if (!fits)
   {
     // grow the scratch: as many candidates per launch as 80 % of the free memory holds
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
     const size_t have = e->lcap_cand * ((size_t)e->lcap_clvs * clv_bytes + stride * sizeof(double));
-    chunk = std::min<size_t>(count, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
+    chunk = std::min<size_t>(chunk, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
   }
   if (!fits && (chunk > e->lcap_cand || npriv > e->lcap_clvs || nlen > e->lcap_lens))
   {

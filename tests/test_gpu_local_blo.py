@@ -179,6 +179,31 @@ def test_pruned_directional_plan_gives_identical_scores(radius):
     assert all(np.array_equal(a, b) for a, b in zip(full[1:], pruned[1:]))
 
 
+@pytest.mark.parametrize("knob", ["PTGPU_BLO_MAX_CHUNK=7", "PTGPU_BLO_CLUSTER_WORK=0",
+                                  "PTGPU_BLO_CLUSTER_WORK=100000"])
+def test_launch_geometry_does_not_change_results(knob, monkeypatch):
+    """the same batch in chunks of 7 candidates (private indices rebased per chunk), forced onto
+    the cooperative grid-barrier variant, and forced onto the single-cluster variant: a
+    candidate's numbers depend on neither its batch nor the barrier mechanism"""
+    tree, seqs, g = load_set("ds1")
+    model = model_of(g)
+    prog = program(tree, 2)
+    e = batch_engine(tree, seqs, model)
+    try:
+        base = e.optimize_local_batch(prog)
+    finally:
+        e.close()
+    name, value = knob.split("=")
+    monkeypatch.setenv(name, value)
+    e = batch_engine(tree, seqs, model)
+    try:
+        got = e.optimize_local_batch(prog)
+    finally:
+        e.close()
+    for a, b in zip(base, got):
+        assert np.array_equal(a, b)
+
+
 def test_batch_on_a_larger_alignment_matches_sampled_sequential_runs():
     import synth
     taxa, sites = 24, 20000
