@@ -47,7 +47,12 @@ from synth import (FREQS, RATES, SEED_ALN, SEED_TREE, SUBST, parent_tree,  # noq
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region"""
+    """SM clock and throttle reasons during the timed region.
+
+    Sampled in-process through NVML (nvidia_ml_py): two light queries every 25 ms.  A polling
+    `nvidia-smi -lms` child (the recipe's clocks line) is only the fallback: its NVML attach
+    and its polls take driver locks that were seen to stall the benchmark's own launches for
+    tens of ms inside the timed region."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -56,8 +61,39 @@ class ClockSampler(threading.Thread):
     def __init__(self, device):
         super().__init__(daemon=True)
         self.device, self.rows, self._stop_evt = device, [], threading.Event()
+        self.source = None
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x.strip() for x in vis.split(",") if x.strip()]
+            if self.device < len(ids) and ids[self.device].isdigit():
+                return int(ids[self.device])
+        return self.device
+
+    def _run_nvml(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self._physical_index())
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        bits = (("hw_slowdown", nv.nvmlClocksThrottleReasonHwSlowdown),
+                ("hw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap))
+        self.source = "nvml"
+        while not self._stop_evt.is_set():
+            sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            why = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            active = ["Active" if why & b else "Not Active" for _, b in bits]
+            self.rows.append([time.time(), str(self.device), str(sm), str(mx), "", ""] + active)
+            self._stop_evt.wait(0.025)
 
     def run(self):
+        try:
+            self._run_nvml()
+            return
+        except Exception:
+            self.source = "nvidia-smi"
         try:
             p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                   "-lms", "200", "-i", str(self.device)], stdout=subprocess.PIPE,
@@ -73,8 +109,7 @@ class ClockSampler(threading.Thread):
 
     def stop(self, t0=None, t1=None):
         """summary of the samples taken inside [t0, t1] (the timed region); the sampler itself
-        is started before the warm-up so that nvidia-smi's start-up (NVML attach can stall the
-        driver for tens of ms) never falls inside the timed region"""
+        is started before the warm-up so that its start-up never falls inside the timed region"""
         self._stop_evt.set()
         rows = [r[1:] for r in self.rows if t0 is None or t0 <= r[0] <= t1]
         if not rows:
@@ -90,7 +125,7 @@ class ClockSampler(threading.Thread):
                         reasons.add(name)
         return dict(sm_mhz=float(np.median(sm)) if sm else None,
                     sm_max_mhz=max(mx) if mx else None, reasons=sorted(reasons),
-                    samples=len(sm))
+                    samples=len(sm), source=self.source)
 
 
 def ncu_traffic(kernel, taxa, sites):
