@@ -98,3 +98,41 @@ def test_fused_from_a_stale_orientation():
     finally:
         e1.close()
         e2.close()
+
+
+def test_invalid_all_branches_programs_are_rejected():
+    from pt_b200.engine import PtGpuError, ops_array
+    tree, seqs, g, model = fresh("five")
+    e = make_engine(tree, seqs, *model)
+    try:
+        ops, midx, mlen = tree.full_traversal()
+        e.update_prob_matrices(midx, mlen)
+        e.update_partials(ops_array(ops))
+        flags = ab.Flags()
+        ab.traverse(tree.root, flags, partial=False)
+        n_edges = 2 * tree.tip_count - 3
+        steps, n_pro, n_body, n_bodies, edge, _ = ab.program(tree.root, flags, n_edges)
+        l0 = np.zeros(n_edges)
+        for r in tree.by_index.values():
+            l0[r.pmatrix_index] = r.length
+
+        def refuse(**kw):
+            args = dict(steps=steps.copy(), edge=edge.copy(), l0=l0.copy())
+            for k, f in kw.items():
+                f(args[k])
+            with pytest.raises(PtGpuError):
+                e.optimize_all_branches(args["steps"], n_pro, n_body, n_bodies, args["edge"], args["l0"])
+
+        k_op = int(np.nonzero(steps["type"] == 1)[0][0])
+        k_opt = int(np.nonzero(steps["type"] == 2)[0][0])
+        refuse(steps=lambda s: s["a_clv"].__setitem__(k_op, 0))              # CLV update into a tip
+        refuse(steps=lambda s: s["a_clv"].__setitem__(k_op, 10 ** 6))
+        refuse(steps=lambda s: s["b_matrix"].__setitem__(k_opt, n_edges))     # matrix out of range
+        refuse(steps=lambda s: s["length_slot"].__setitem__(k_opt, 0 if s["b_matrix"][k_opt] else 1))
+        refuse(steps=lambda s: s["type"].__setitem__(k_opt, 7))
+        refuse(edge=lambda ed: ed["matrix"].__setitem__(0, n_edges))
+        refuse(l0=lambda x: x.__setitem__(0, float("nan")))
+        out, lnl, passes = e.optimize_all_branches(steps, n_pro, n_body, n_bodies, edge, l0)
+        assert np.isfinite(lnl) and passes >= 1
+    finally:
+        e.close()

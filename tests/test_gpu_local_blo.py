@@ -227,3 +227,45 @@ def test_batch_on_a_larger_alignment_matches_sampled_sequential_runs():
     finally:
         e.close()
         s.close()
+
+
+def test_invalid_programs_are_rejected():
+    """a local batch may write only its own private slots; every index is checked on the host"""
+    from pt_b200.engine import PtGpuError
+    tree, seqs, g = load_set("five")
+    e = batch_engine(tree, seqs, model_of(g))
+    n = tree.tip_count
+    try:
+        good = program(tree, 1)
+        e.optimize_local_batch(good)
+
+        def broken(edit):
+            prog = program(tree, 1)
+            edit(prog)
+            with pytest.raises(PtGpuError):
+                e.optimize_local_batch(prog)
+
+        def write_engine_clv(p):       # CLV update into one of the engine's directional buffers
+            p.steps["a_clv"][0, 0] = n
+        def write_other_candidate(p):  # ... into another candidate's private buffer
+            p.steps["a_clv"][0, 0] = p.steps["a_clv"][0, 1]
+        def foreign_matrix(p):         # optimise an edge whose matrix is not the slot's own
+            k = int(np.nonzero(p.step_types == 2)[0][0])
+            p.steps["b_matrix"][k, 0] = 0
+        def slot_out_of_range(p):
+            k = int(np.nonzero(p.step_types == 2)[0][0])
+            p.steps["length_slot"][k, 0] = p.n_lengths
+        def wrong_type(p):
+            p.steps["type"][0, 0] = 2
+        def negative_length(p):
+            p.lengths0[0, 0] = -1.0
+        def bad_edge(p):
+            p.final_edges["child_clv"][0] = 10 ** 6
+        for edit in (write_engine_clv, write_other_candidate, foreign_matrix, slot_out_of_range,
+                     wrong_type, negative_length, bad_edge):
+            broken(edit)
+        # the engine still works after the refusals
+        again = e.optimize_local_batch(good)
+        assert np.isfinite(again[1]).all()
+    finally:
+        e.close()
