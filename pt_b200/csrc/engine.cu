@@ -108,6 +108,12 @@ struct ptgpu_engine
   double *d_mlen = nullptr;
   size_t mcap = 0;
   Staging stg;
+  // pinned host arena for the descriptor uploads / result downloads of the batch entry points
+  // (grown on demand): a copy to or from PAGEABLE memory goes through the driver's shared
+  // staging buffers and waits there for the stream, which serialises the engines of a
+  // many-wanderer process to two kernels in flight
+  unsigned char *h_pin = nullptr;
+  size_t h_pin_cap = 0;
   int coop_blocks_per_sm = 0;
   int sm_count = 0;
   // site-shard mode (ptgpu_set_allreduce / ptgpu_set_shard)
@@ -348,6 +354,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   for (auto &p : e->pending) { cudaEventDestroy(p.second.first); cudaEventDestroy(p.second.second); }
   for (auto ev : e->event_pool) cudaEventDestroy(ev);
   if (e->stg.host) cudaFreeHost(e->stg.host);
+  if (e->h_pin) cudaFreeHost(e->h_pin);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
 }
@@ -506,6 +513,36 @@ int ensure(T **ptr, size_t *cap, size_t need)
   *cap = n;
   return PTGPU_OK;
 }
+
+// pinned host arena of at least `bytes` (contents are NOT kept when it grows; the stream is
+// drained first, so nothing in flight still reads or writes the old one)
+int pin_reserve(ptgpu_engine *e, size_t bytes)
+{
+  if (bytes <= e->h_pin_cap) return PTGPU_OK;
+  CU(cudaStreamSynchronize(e->stream));
+  if (e->h_pin) CU(cudaFreeHost(e->h_pin));
+  e->h_pin = nullptr;
+  e->h_pin_cap = 0;
+  const size_t n = std::max<size_t>(bytes + bytes / 2, 1 << 16);
+  CU(cudaHostAlloc(&e->h_pin, n, cudaHostAllocDefault));
+  e->h_pin_cap = n;
+  return PTGPU_OK;
+}
+
+// carves 256-byte aligned sections out of the pinned arena
+struct PinCursor
+{
+  unsigned char *base;
+  size_t off = 0;
+  template <typename T>
+  T *take(size_t n)
+  {
+    T *p = reinterpret_cast<T *>(base + off);
+    off += (n * sizeof(T) + 255) & ~size_t(255);
+    return p;
+  }
+  static size_t padded(size_t bytes) { return (bytes + 255) & ~size_t(255); }
+};
 
 // host -> device copy of a small descriptor array on the engine's stream.
 // Arrays that fit go through the pinned staging area (truly asynchronous);
@@ -869,7 +906,9 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     CU(cudaMalloc(&e->d_bcands, chunk * sizeof(DevGroup)));
     e->bcap = chunk;
   }
-  std::vector<NewtonState> hst(chunk);
+  // per-candidate Newton states go up and come back through the pinned arena
+  if ((rc = pin_reserve(e, chunk * sizeof(NewtonState)))) return rc;
+  NewtonState *hst = reinterpret_cast<NewtonState *>(e->h_pin);
   for (unsigned int base = 0; base < count; base += (unsigned int)chunk)
   {
     const unsigned int nb = (unsigned int)std::min<size_t>(chunk, count - base);
@@ -928,7 +967,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     }
     const unsigned int ng = (unsigned int)groups.size();
     if ((rc = upload(e, e->d_bcands, groups.data(), ng * sizeof(DevGroup)))) return rc;
-    if ((rc = upload(e, e->d_bstate, hst.data(), nb * sizeof(NewtonState)))) return rc;
+    CU(cudaMemcpyAsync(e->d_bstate, hst, nb * sizeof(NewtonState), cudaMemcpyHostToDevice, e->stream));
     {
       LaunchScope ls(e, PTGPU_KERNEL_NNI_PREPARE);
       if (e->prepare_version == 1)
@@ -949,7 +988,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     a.sites = e->sites; a.B = nb; a.ntiles = e->ntiles; a.chunk_tiles = e->chunk_tiles; a.nchunks = e->nchunks; a.max_iter = max_iter;
     a.eps = epsilon; a.lambda = map_lambda; a.want_lnl = 1;
     if ((rc = run_newton(e, a))) return rc;
-    CU(cudaMemcpyAsync(hst.data(), e->d_bstate, nb * sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(hst, e->d_bstate, nb * sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     for (unsigned int i = 0; i < nb; ++i)
     {
@@ -1324,15 +1363,30 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
   if ((rc = ensure(&e->d_lsteps, &e->lcap_steps, (size_t)nsteps * chunk))) return rc;
   if ((rc = ensure(&e->d_ltypes, &e->lcap_types, (size_t)nsteps))) return rc;
   if ((rc = ensure(&e->d_lprior, &e->lcap_prior, (size_t)std::max(1u, r.n_prior)))) return rc;
+  // descriptors and results travel through the engine's pinned arena (see ptgpu_engine::h_pin)
+  if ((rc = pin_reserve(e, PinCursor::padded(nsteps * sizeof(int)) +
+                               PinCursor::padded(std::max(1u, r.n_prior) * sizeof(unsigned int)) +
+                               PinCursor::padded((size_t)nsteps * chunk * sizeof(BloStep)) +
+                               PinCursor::padded(2 * chunk * sizeof(BloEdge)) +
+                               PinCursor::padded(chunk * sizeof(BloCand)) +
+                               PinCursor::padded(chunk * nlen * sizeof(double)))))
+    return rc;
   CU(cudaStreamSynchronize(e->stream));  // nothing in flight still reads the descriptor buffers
-  CU(cudaMemcpyAsync(e->d_ltypes, r.step_types, nsteps * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+  PinCursor pin{e->h_pin};
+  int *htypes = pin.take<int>(nsteps);
+  unsigned int *hprior = pin.take<unsigned int>(std::max(1u, r.n_prior));
+  BloStep *hsteps = pin.take<BloStep>((size_t)nsteps * chunk);
+  BloEdge *hedges = pin.take<BloEdge>(2 * chunk);
+  BloCand *hcand = pin.take<BloCand>(chunk);
+  double *hlens = pin.take<double>(chunk * nlen);
+  memcpy(htypes, r.step_types, nsteps * sizeof(int));
+  CU(cudaMemcpyAsync(e->d_ltypes, htypes, nsteps * sizeof(int), cudaMemcpyHostToDevice, e->stream));
   if (r.n_prior)
-    CU(cudaMemcpyAsync(e->d_lprior, r.prior_slots, r.n_prior * sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+  {
+    memcpy(hprior, r.prior_slots, r.n_prior * sizeof(unsigned int));
+    CU(cudaMemcpyAsync(e->d_lprior, hprior, r.n_prior * sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+  }
 
-  std::vector<BloStep> hsteps;
-  std::vector<BloEdge> hedges;
-  std::vector<BloCand> hcand;
-  std::vector<double> hlens;
   for (unsigned int base = 0; base < count; base += (unsigned int)chunk)
   {
     const unsigned int nb = (unsigned int)std::min<size_t>(chunk, count - base);
@@ -1341,7 +1395,6 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     auto rb_clv = [&](unsigned int idx) { return idx >= clv_total ? idx - dclv : idx; };
     auto rb_scal = [&](int idx) { return (idx >= 0 && (unsigned int)idx >= e->scale_buffers) ? (int)(idx - dclv) : idx; };
     auto rb_mat = [&](unsigned int idx) { return idx >= e->prob_matrices ? idx - dmat : idx; };
-    hsteps.assign((size_t)nsteps * nb, BloStep{});
     for (unsigned int k = 0; k < nsteps; ++k)
       for (unsigned int i = 0; i < nb; ++i)
       {
@@ -1354,7 +1407,6 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
         d.slot = st.length_slot;
         hsteps[(size_t)k * nb + i] = d;
       }
-    hedges.assign((size_t)2 * nb, BloEdge{});
     for (unsigned int i = 0; i < nb; ++i)
       for (int w = 0; w < 2; ++w)
       {
@@ -1365,13 +1417,17 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
         d.mat = rb_mat(ed.matrix);
         hedges[(size_t)w * nb + i] = d;
       }
-    hcand.assign(nb, BloCand{});
-    for (auto &c : hcand) c.active = 1;
-    hlens.assign(r.lengths0 + (size_t)base * nlen, r.lengths0 + (size_t)(base + nb) * nlen);
-    CU(cudaMemcpyAsync(e->d_lsteps, hsteps.data(), hsteps.size() * sizeof(BloStep), cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(e->d_ledges, hedges.data(), hedges.size() * sizeof(BloEdge), cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(e->d_lcand, hcand.data(), hcand.size() * sizeof(BloCand), cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(e->d_llens, hlens.data(), hlens.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    for (unsigned int i = 0; i < nb; ++i)
+    {
+      hcand[i] = BloCand{};
+      hcand[i].active = 1;
+    }
+    const size_t nlens = (size_t)nb * nlen;
+    memcpy(hlens, r.lengths0 + (size_t)base * nlen, nlens * sizeof(double));
+    CU(cudaMemcpyAsync(e->d_lsteps, hsteps, (size_t)nsteps * nb * sizeof(BloStep), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->d_ledges, hedges, (size_t)2 * nb * sizeof(BloEdge), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->d_lcand, hcand, nb * sizeof(BloCand), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->d_llens, hlens, nlens * sizeof(double), cudaMemcpyHostToDevice, e->stream));
 
     BloArgs a{};
     a.v.s = e->dev;
@@ -1403,8 +1459,8 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
       DISPATCH_CATS(e, rc = launch_blo<C>(e, a, grid));
     }
     if (rc) return rc;
-    CU(cudaMemcpyAsync(hcand.data(), e->d_lcand, nb * sizeof(BloCand), cudaMemcpyDeviceToHost, e->stream));
-    CU(cudaMemcpyAsync(hlens.data(), e->d_llens, hlens.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(hcand, e->d_lcand, nb * sizeof(BloCand), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(hlens, e->d_llens, nlens * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     for (unsigned int i = 0; i < nb; ++i)
     {
@@ -1414,7 +1470,7 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
       e->counters[2] += (unsigned long long)hcand[i].newton_evals;
     }
     if (r.lengths_out)
-      memcpy(r.lengths_out + (size_t)base * nlen, hlens.data(), hlens.size() * sizeof(double));
+      memcpy(r.lengths_out + (size_t)base * nlen, hlens, nlens * sizeof(double));
     if (!in_place) e->counters[3] += nb;
   }
   return PTGPU_OK;
