@@ -498,7 +498,7 @@ def run_ptw_ds1(args):
             out = os.path.join(d, "good.tsv")
             tested = os.path.join(d, "tested.tsv")
             cmd = [binary, "--raxml-info", os.path.join(ds1, "RAxML_info.DS1"), "--threads", str(threads),
-                   "--lnl-offset", "-5", "--optimization-radius", "1", "--tested-trees", tested,
+                   "--polling-time", "1" if threads > 1 else "100", "--lnl-offset", "-5", "--optimization-radius", "1", "--tested-trees", tested,
                    os.path.join(ds1, "RAxML_bestTree.DS1"), os.path.join(ds1, "DS1.fasta"), out]
             t0 = time.perf_counter()
             r = subprocess.run(cmd, capture_output=True, text=True, check=True)
@@ -517,10 +517,11 @@ def run_ptw_ds1(args):
         raise SystemExit("oracle/_ref/gpu/ptw_batched is not built (needs /root/reference at build time)")
     sampler = ClockSampler(0)
     sampler.start()
+    W = max(1, args.wanderers)
     for _ in range(args.warmup):
-        walk(ours, 1)
+        walk(ours, W)
     wall0 = time.time()
-    runs = [walk(ours, 1) for _ in range(args.steps)]
+    runs = [walk(ours, W) for _ in range(args.steps)]
     clocks = sampler.stop(wall0, time.time())
     dt = sum(r[0] for r in runs) / len(runs)
     _, good, ntested, moves = runs[-1]
@@ -528,8 +529,10 @@ def run_ptw_ds1(args):
                 steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * dt, higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype="f64", data="DS1 (27 taxa x 1949 sites)",
                 config=dict(workload="BASELINE configs[1] on DS1: ptw topography walk, --lnl-offset -5 "
-                                     "--optimization-radius 1, one wanderer, batched move testing "
-                                     "(whole process, incl. ~1.1 s CUDA context creation)",
+                                     "--optimization-radius 1, %d wanderer(s) with one engine each on the same GPU, "
+                                     "batched move testing (whole process, incl. ~1.1 s CUDA context "
+                                     "creation)" % W,
+                            wanderers=W,
                             taxa=27, sites=1949, rate_cats=4),
                 good_trees=good, tested_trees=ntested, evaluate_move_calls=moves, clocks=clocks,
                 e2e=dict(value=moves / dt, unit="candidates/s", h2d_bytes_per_step=27 * 1949,
@@ -559,6 +562,8 @@ def main():
     ap.add_argument("--cpu-sample-sites", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1"])
+    ap.add_argument("--wanderers", type=int, default=1,
+                    help="ptw-ds1: wanderer threads of ptw_batched (each owns an engine on the GPU)")
     args = ap.parse_args()
     if args.workload == "ptw-ds1":
         if int(os.environ.get("RANK", "0")) == 0:

@@ -11,6 +11,7 @@
 #include "blo.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -114,6 +115,7 @@ struct ptgpu_engine
   // many-wanderer process to two kernels in flight
   unsigned char *h_pin = nullptr;
   size_t h_pin_cap = 0;
+  bool counted = false;             // included in g_live_engines
   int coop_blocks_per_sm = 0;
   int sm_count = 0;
   // site-shard mode (ptgpu_set_allreduce / ptgpu_set_shard)
@@ -135,6 +137,26 @@ struct ptgpu_engine
   double kernel_ms[PTGPU_KERNEL_KINDS] = {};
   unsigned long long kernel_launches[PTGPU_KERNEL_KINDS] = {};
 };
+
+namespace {
+
+// Engines alive on each device of this process.  A cooperative launch needs its whole grid
+// resident at once, so a full-device grid has to wait until every other engine's kernel has
+// drained (and holds up the ones behind it): with several engines on a device (one per
+// wanderer) each takes its share of the SMs instead (at most PTGPU_COOP_SHARE_MAX ways, default
+// 2: measured on the DS1 walk with 8 and 16 wanderers, halves beat both the full grid and
+// smaller shares).  Results do not depend on the grid size (fixed reduction trees).
+std::atomic<int> g_live_engines[64];
+
+unsigned int coop_grid_share(const ptgpu_engine *e, unsigned int full)
+{
+  const int live = g_live_engines[e->device & 63].load(std::memory_order_relaxed);
+  static const int max_div = [] { const char *v = getenv("PTGPU_COOP_SHARE_MAX"); return v ? std::max(1, atoi(v)) : 2; }();
+  const unsigned int div = (unsigned int)std::min(std::max(live, 1), max_div);
+  return std::max(std::min(full, 16u), full / div);
+}
+
+} // namespace
 
 namespace {
 // RAII bracket around one kernel launch: counts it and, when profiling is on,
@@ -333,6 +355,8 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   }
   CU_NEW(cudaStreamSynchronize(e->stream));
 #undef CU_NEW
+  e->counted = true;
+  g_live_engines[e->device & 63].fetch_add(1);
   *out = e;
   return PTGPU_OK;
 }
@@ -340,6 +364,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
 void ptgpu_destroy(ptgpu_engine *e)
 {
   if (!e) return;
+  if (e->counted) g_live_engines[e->device & 63].fetch_sub(1);
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   cudaFree(e->d_raw_all); cudaFree(e->d_tip_of); cudaFree(e->d_bad);
@@ -579,7 +604,7 @@ template <int C>
 int launch_newton(ptgpu_engine *e, NewtonArgs &a)
 {
   const unsigned int work = std::max(1u, a.B * a.nchunks);
-  const unsigned int maxg = (unsigned int)(e->coop_blocks_per_sm * e->sm_count);
+  const unsigned int maxg = coop_grid_share(e, (unsigned int)(e->coop_blocks_per_sm * e->sm_count));
   const unsigned int grid = std::min(work, maxg);
   void *params[] = {&a};
   {
@@ -1448,7 +1473,7 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     a.procedure = r.procedure; a.lambda = r.lambda;
     a.prior_slots = e->d_lprior; a.n_prior = r.n_prior;
     const unsigned int work = std::max(1u, nb * e->ntiles);
-    const unsigned int grid = std::min(work, (unsigned int)(e->blo_blocks_per_sm * e->sm_count));
+    const unsigned int grid = std::min(work, coop_grid_share(e, (unsigned int)(e->blo_blocks_per_sm * e->sm_count)));
     // a program whose phases are a couple of tiles per CTA is all barriers: one cluster
     if (work <= e->blo_cluster_work && !PT_SWEEP_RING)
     {

@@ -14,7 +14,5 @@ run() { # threads extra-env
   echo "threads=$T env=$* rc=$rc wall_ms=$(( (e - s) / 1000000 )) good=$(wc -l < gpurun_out/good_$T.tsv) tested=$(wc -l < gpurun_out/tested_$T.tsv) $(grep batched gpurun_out/ptw_T$T.err)"
 }
 run 1 A=1
-for T in 1 2 4 8 16 32; do run $T A=1; done
 export POLL=1
-for T in 1 2 4 8 16 32; do run $T POLL=1; done
-nproc
+for M in 1 2 4 8; do for T in 8 16; do for rep in 1 2 3; do run $T PTGPU_COOP_SHARE_MAX=$M; done; done; done
