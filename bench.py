@@ -313,7 +313,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     sampler = ClockSampler(local)   # started long before the timed region (see stop())
-    if rank == 0:
+    if rank == 0 and not os.environ.get("PTGPU_BENCH_NO_SAMPLER"):   # diagnostic switch only
         sampler.start()
     n, S = args.taxa, args.sites
     base = parent_tree(n, 0)
@@ -376,8 +376,11 @@ def run_ours(args):
     torch.cuda.synchronize()
     wall0 = time.time()
     ev0.record(stream)
+    step_host_ms = []   # host clock per step (every step ends in a stream sync): shows WHICH step a stall hit
     for _ in range(args.steps):
+        t_s = time.perf_counter()
         step()
+        step_host_ms.append(round(1e3 * (time.perf_counter() - t_s), 3))
     ev1.record(stream)
     torch.cuda.synchronize()
     if dist:
@@ -467,6 +470,7 @@ def run_ours(args):
                              f"(of 3(n-2) = {3 * (n - 2)})", taxa=n, sites=S, rate_cats=4,
                     candidates_per_step_per_gpu=ncand, parallelism=f"candidate-parallel x{world}",
                     l2="inputs (>20 GB of CLVs per step) far exceed the 126 MB L2; no flush needed"),
+        step_host_ms=step_host_ms, e2e_step_host_ms=[round(1e3 * x, 3) for x in t_e2e],
         clv_site_updates_per_s=world * site_updates / (kt["partials"][0] * 1e-3) if kt["partials"][0] else None,
         newton_iterations_per_candidate=passes / steps / ncand,
         lnl_carrying_sweeps_per_candidate=lnl_sweeps / steps / ncand,

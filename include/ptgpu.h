@@ -115,6 +115,26 @@ int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count,
                                const unsigned int *tip_indices,
                                const char *const *sequences);
 
+/* pll_set_pattern_weights (LIBPLL/pll.c:1047-1059): `weights` is a host array of
+   `sites` multiplicities (every one >= 1: the reference's vector paths assume "no
+   zero weights", LIBPLL/core_derivatives_avx.c:1123); NULL restores all-ones, the
+   state after ptgpu_create and the only one pt itself uses.  From then on every sum
+   over sites -- edge log-likelihoods, per-site log-likelihoods, both derivative sums,
+   the scores of the batch entry points -- weights pattern i by weights[i], as
+   libpll's kernels do.  CLVs, scalers and sumtables do not depend on the weights. */
+int ptgpu_set_pattern_weights(ptgpu_engine *e, const unsigned int *weights);
+
+/* pll_compress_site_patterns (LIBPLL/compress.c:138-282) for nucleotide data (pll_map_nt):
+   the unique columns of `count` sequences of *length characters, in the reference's
+   order (ascending by the columns' state codes, first taxon most significant), written
+   over the front of each sequence (NUL-terminated there), *length set to their number
+   and their multiplicities stored in weights_out[0 .. *length).  Characters come back
+   as the canonical symbol of their state code, as in the reference.  Host-only: the
+   alignment is compressed before it is uploaded.  An unknown character is
+   PTGPU_ERR_STATE and leaves the sequences untouched. */
+int ptgpu_compress_site_patterns(char **sequences, unsigned int count, unsigned int *length,
+                                 unsigned int *weights_out);
+
 /* pll_update_prob_matrices (LIBPLL/models.c:333-364) */
 int ptgpu_update_prob_matrices(ptgpu_engine *e, const unsigned int *matrix_indices,
                                const double *branch_lengths, unsigned int count);

@@ -494,6 +494,15 @@ double pto_edge_lnl(unsigned int sites, unsigned int cats,
                     const double *clvc, const unsigned int *sc,
                     const double *pmat, const double freqs[4], double *persite)
 {
+  return pto_edge_lnl_w(sites, cats, clvp, sp, clvc, sc, pmat, freqs, NULL, persite);
+}
+
+double pto_edge_lnl_w(unsigned int sites, unsigned int cats,
+                      const double *clvp, const unsigned int *sp,
+                      const double *clvc, const unsigned int *sc,
+                      const double *pmat, const double freqs[4],
+                      const unsigned int *weights, double *persite)
+{
   /* LIBPLL/core_likelihood_avx.c:1080-1266.
      t_k = (f0 + f1) + (f2 + f3), f_i = (pi_i * (P_k c)_i) * p_i  (:1194-1217)
      terma += t_k * w_k only when t_k > 0                          (:1225-1241)
@@ -518,7 +527,7 @@ double pto_edge_lnl(unsigned int sites, unsigned int cats,
     double site = log(terma);
     const unsigned int sclr = (sp ? sp[n] : 0u) + (sc ? sc[n] : 0u);
     if (sclr) site += sclr * log_thr;
-    site *= 1u; /* pattern weight */
+    site *= weights ? weights[n] : 1u; /* pattern weight (:1254) */
     if (persite) persite[n] = site;
     logl += site;
   }
@@ -558,6 +567,14 @@ void pto_derivatives(unsigned int sites, unsigned int cats,
                      const double *sumtable, const double evals[4],
                      const double *rates, double t, double *d1, double *d2)
 {
+  pto_derivatives_w(sites, cats, sumtable, evals, rates, NULL, t, d1, d2);
+}
+
+void pto_derivatives_w(unsigned int sites, unsigned int cats,
+                       const double *sumtable, const double evals[4],
+                       const double *rates, const unsigned int *weights, double t,
+                       double *d1, double *d2)
+{
   /* diag table: LIBPLL/core_derivatives.c:560-575 (prop_invar = 0, so
      ki = rates[c] / (1.0 - 0.0)); site loop: LIBPLL/core_derivatives_avx.c
      :1003-1166 -- equal rate weights are dropped (:921-928,1093-1097), four
@@ -593,14 +610,21 @@ void pto_derivatives(unsigned int sites, unsigned int cats,
     }
     for (int q = 0; q < 3; ++q) blk[n & 3][q] = lk[q];
     if (n < full && (n & 3) == 3)
+    {
+      /* four weights all 1: no products (:1123-1130), else every lane is multiplied by its
+         weight (:1131-1139) */
+      const int unit = !weights ||
+                       (weights[n - 3] | weights[n - 2] | weights[n - 1] | weights[n]) == 1;
       for (int v = 0; v < 4; ++v)
       {
         const double recip = 1.0 / blk[v][0];
         const double a = blk[v][1] * recip;
         const double b = a * a - blk[v][2] * recip;
-        lane1[v] = lane1[v] - a;
-        lane2[v] = lane2[v] + b;
+        const double w = unit ? 1.0 : (double)weights[n - 3 + v];
+        lane1[v] = lane1[v] - (unit ? a : a * w);
+        lane2[v] = lane2[v] + (unit ? b : b * w);
       }
+    }
   }
   double df = 0., ddf = 0.;
   for (unsigned int n = sites; n > full; --n)
@@ -608,8 +632,8 @@ void pto_derivatives(unsigned int sites, unsigned int cats,
     const double *lk = blk[(n - 1) & 3];
     const double a = (-lk[1] / lk[0]);
     const double b = (a * a - (lk[2] / lk[0]));
-    df += 1u * a;
-    ddf += 1u * b;
+    df += (weights ? weights[n - 1] : 1u) * a;
+    ddf += (weights ? weights[n - 1] : 1u) * b;
   }
   df += lane1[0] + lane1[1] + lane1[2] + lane1[3];
   ddf += lane2[0] + lane2[1] + lane2[2] + lane2[3];
@@ -628,6 +652,16 @@ double pto_optimize_branch(unsigned int sites, unsigned int cats,
                            unsigned int max_iter, double eps, double map_lambda,
                            int *iters, int *status)
 {
+  return pto_optimize_branch_w(sites, cats, sumtable, evals, rates, NULL, len0, max_iter, eps,
+                               map_lambda, iters, status);
+}
+
+double pto_optimize_branch_w(unsigned int sites, unsigned int cats,
+                             const double *sumtable, const double evals[4],
+                             const double *rates, const unsigned int *weights, double len0,
+                             unsigned int max_iter, double eps, double map_lambda,
+                             int *iters, int *status)
+{
   /* PTPLL/pll_partition.cpp:419-481 */
   double len = len0;
   int maybe_decreasing = 0, it = 0;
@@ -635,7 +669,7 @@ double pto_optimize_branch(unsigned int sites, unsigned int cats,
   for (unsigned int i = 0; i < max_iter; ++i)
   {
     double d1, d2;
-    pto_derivatives(sites, cats, sumtable, evals, rates, len, &d1, &d2);
+    pto_derivatives_w(sites, cats, sumtable, evals, rates, weights, len, &d1, &d2);
     ++it;
     if (map_lambda != 0.0) d1 += map_lambda;
     if (!isfinite(d1)) { *status = 1; break; }
@@ -652,4 +686,66 @@ double pto_optimize_branch(unsigned int sites, unsigned int cats,
   }
   if (iters) *iters = it;
   return len;
+}
+
+/* ------------------------------------------------------------------ */
+/* site pattern compression                                            */
+/* ------------------------------------------------------------------ */
+
+static unsigned int g_cmp_count;
+static int cmp_columns(const void *a, const void *b)
+{
+  return memcmp(*(const unsigned char *const *)a, *(const unsigned char *const *)b, g_cmp_count);
+}
+
+int pto_compress_site_patterns(char **sequence, unsigned int count, unsigned int *length,
+                               unsigned int *weight)
+{
+  /* LIBPLL/compress.c:138-282 with map = pll_map_nt (all codes < 256, so charmap = map, :160-164).
+     characters -> state codes (:173), alignment split into columns (:214-219), columns sorted
+     (:222; a three-way radix quicksort on the code strings = ascending strcmp order, so any
+     sort gives the same sequence of DISTINCT columns), first of every run kept and the run
+     length is its weight (:225-241), codes decoded through the inverse map, which holds the
+     LAST character of each code (:166-170, :244-246), terminator added (:248-249).
+     returns 0, or -1 on a character outside pll_map_nt (the reference would encode it as 0
+     and truncate the column string there; pt rejects such input before, PTPLL/pll_partition.cpp:184-187) */
+  const unsigned int n = *length;
+  unsigned char inv[256];
+  memset(inv, 0, sizeof inv);
+  for (int c = 1; c < 256; ++c)
+    if (pto_nt_mask(c)) inv[pto_nt_mask(c)] = (unsigned char)c;
+  if (!n) return 0;
+  unsigned char *mem = (unsigned char *)malloc((size_t)n * count);
+  unsigned char **column = (unsigned char **)malloc(sizeof(unsigned char *) * n);
+  for (unsigned int i = 0; i < n; ++i) column[i] = mem + (size_t)i * count;
+  for (unsigned int j = 0; j < count; ++j)
+    for (unsigned int i = 0; i < n; ++i)
+    {
+      const unsigned int k = pto_nt_mask((unsigned char)sequence[j][i]);
+      if (!k) { free(mem); free(column); return -1; }
+      column[i][j] = (unsigned char)k;
+    }
+  g_cmp_count = count;
+  qsort(column, n, sizeof column[0], cmp_columns);
+  unsigned int ref = 0;
+  weight[0] = 1;
+  for (unsigned int i = 1; i < n; ++i)
+  {
+    if (memcmp(column[i], column[i - 1], count))
+    {
+      column[ref + 1] = column[i];
+      ++ref;
+      weight[ref] = 1;
+    }
+    else
+      weight[ref]++;
+  }
+  const unsigned int m = ref + 1;
+  for (unsigned int i = 0; i < m; ++i)
+    for (unsigned int j = 0; j < count; ++j) sequence[j][i] = (char)inv[column[i][j]];
+  for (unsigned int j = 0; j < count; ++j) sequence[j][m] = 0;
+  *length = m;
+  free(mem);
+  free(column);
+  return 0;
 }

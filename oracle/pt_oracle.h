@@ -83,6 +83,29 @@ double pto_optimize_branch(unsigned int sites, unsigned int cats,
                            unsigned int max_iter, double eps, double map_lambda,
                            int *iters, int *status);
 
+/* -- the same three with pattern weights (LIBPLL/core_likelihood_avx.c:1254,
+      LIBPLL/core_derivatives_avx.c:1123-1139,1153-1154); weights == NULL is all ones -- */
+double pto_edge_lnl_w(unsigned int sites, unsigned int cats,
+                      const double *clvp, const unsigned int *sp,
+                      const double *clvc, const unsigned int *sc,
+                      const double *pmat, const double freqs[4],
+                      const unsigned int *weights, double *persite);
+void pto_derivatives_w(unsigned int sites, unsigned int cats,
+                       const double *sumtable, const double evals[4],
+                       const double *rates, const unsigned int *weights, double t,
+                       double *d1, double *d2);
+double pto_optimize_branch_w(unsigned int sites, unsigned int cats,
+                             const double *sumtable, const double evals[4],
+                             const double *rates, const unsigned int *weights, double len0,
+                             unsigned int max_iter, double eps, double map_lambda,
+                             int *iters, int *status);
+
+/* -- pll_compress_site_patterns for nucleotide data (LIBPLL/compress.c:138-282) --
+   sequences are overwritten by the unique columns (NUL-terminated), *length by their
+   number, weight[0 .. *length) by their multiplicities; -1 on an illegal character */
+int pto_compress_site_patterns(char **sequence, unsigned int count, unsigned int *length,
+                               unsigned int *weight);
+
 #ifdef __cplusplus
 }
 #endif

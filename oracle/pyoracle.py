@@ -130,6 +130,59 @@ class Oracle:
         return v, it.value, st.value
 
 
+    # --- pattern weights / compression ------------------------------------
+    def edge_lnl_w(self, sites, cats, clvp, sp, clvc, sc, pmat, freqs, weights, persite=False):
+        ps = np.empty(sites) if persite else None
+        freqs = np.ascontiguousarray(freqs, dtype=np.float64)
+        self.lib.pto_edge_lnl_w.restype = C.c_double
+        v = self.lib.pto_edge_lnl_w(C.c_uint(sites), C.c_uint(cats), _d(clvp), _u(sp),
+                                    _d(clvc), _u(sc), _d(pmat), _d(freqs), _u(weights),
+                                    None if ps is None else _d(ps))
+        return (v, ps) if persite else v
+
+    def derivatives_w(self, sites, cats, sumtable, evals, rates, weights, t):
+        d1 = C.c_double(); d2 = C.c_double()
+        rates = np.ascontiguousarray(rates, dtype=np.float64)
+        self.lib.pto_derivatives_w(C.c_uint(sites), C.c_uint(cats), _d(sumtable),
+                                   _d(evals), _d(rates), _u(weights), C.c_double(t),
+                                   C.byref(d1), C.byref(d2))
+        return d1.value, d2.value
+
+    def optimize_branch_w(self, sites, cats, sumtable, evals, rates, weights, len0,
+                          max_iter=32, eps=1e-6, map_lambda=0.0):
+        it = C.c_int(); st = C.c_int()
+        rates = np.ascontiguousarray(rates, dtype=np.float64)
+        self.lib.pto_optimize_branch_w.restype = C.c_double
+        v = self.lib.pto_optimize_branch_w(C.c_uint(sites), C.c_uint(cats),
+                                           _d(sumtable), _d(evals), _d(rates), _u(weights),
+                                           C.c_double(len0), C.c_uint(max_iter),
+                                           C.c_double(eps), C.c_double(map_lambda),
+                                           C.byref(it), C.byref(st))
+        return v, it.value, st.value
+
+    def compress_site_patterns(self, seqs):
+        """(compressed sequences, weights) of a list of equally long strings"""
+        return _compress(self.lib.pto_compress_site_patterns, seqs)
+
+
+def _compress(fn, seqs, ret_is_length=False):
+    n = len(seqs[0])
+    bufs = [C.create_string_buffer(s.encode() if isinstance(s, str) else bytes(s), n + 1) for s in seqs]
+    arr = (C.c_char_p * len(seqs))(*[C.cast(b, C.c_char_p) for b in bufs])
+    w = np.zeros(n, dtype=np.uint32)
+    if ret_is_length:      # the reference glue: (seqs, count, length, weights) -> new length
+        m = fn(arr, C.c_int(len(seqs)), C.c_int(n), w.ctypes.data_as(C.POINTER(C.c_uint)))
+        if m < 0:
+            raise RuntimeError("pattern compression failed")
+    else:                  # (seqs, count, &length, weights) -> status
+        ln = C.c_uint(n)
+        rc = fn(arr, C.c_uint(len(seqs)), C.byref(ln), w.ctypes.data_as(C.POINTER(C.c_uint)))
+        if rc:
+            raise ValueError("pattern compression: illegal character (status %d)" % rc)
+        m = ln.value
+    return [b.raw[:m].decode() for b in bufs], w[:m].copy()
+
+
 def have_ref():
     return os.path.exists(REF_SO)
 
@@ -150,6 +203,10 @@ class RefLib:
         r = np.empty(cats)
         self.lib.pll_compute_gamma_cats(alpha, cats, _d(r), 0)  # PLL_GAMMA_RATES_MEAN
         return r
+
+    def compress_site_patterns(self, seqs):
+        """pll_compress_site_patterns itself: (compressed sequences, weights)"""
+        return _compress(self.lib.ref_compress, seqs, ret_is_length=True)
 
     def open(self, newick, fasta, info, cats=4, tree_index=0, map_mode=False):
         h = self.lib.ref_open(newick.encode(), fasta.encode(), info.encode(),
@@ -184,6 +241,11 @@ class RefPartition:
         if self.h:
             self.lib.ref_close(self.h)
             self.h = None
+
+    def set_pattern_weights(self, weights):
+        w = np.ascontiguousarray(weights, dtype=np.uint32)
+        assert w.size == self.sites
+        self.lib.ref_set_pattern_weights(self.h, w.ctypes.data_as(C.POINTER(C.c_uint)))
 
     def select_tree(self, i):
         assert self.lib.ref_select_tree(self.h, C.c_int(i))

@@ -109,6 +109,23 @@ void* ref_open_mem(const char* newick, int tips, const char** labels,
   }
 }
 
+/* the reference's own pattern compression and weights (never called by pt; used to pin the
+   engine's pattern-weight path): sequences are rewritten in place, returns the new length */
+int ref_compress(char** seqs, int count, int length, unsigned* weights_out)
+{
+  int len = length;
+  unsigned int* w = pll_compress_site_patterns(seqs, pll_map_nt, count, &len);
+  if (!w) return -1;
+  memcpy(weights_out, w, sizeof(unsigned) * len);
+  free(w);
+  return len;
+}
+
+void ref_set_pattern_weights(void* hv, const unsigned* weights)
+{
+  pll_set_pattern_weights(static_cast<RefHandle*>(hv)->part->partition_.get(), weights);
+}
+
 void ref_close(void* hv)
 {
   RefHandle* h = static_cast<RefHandle*>(hv);

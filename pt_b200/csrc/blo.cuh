@@ -352,6 +352,7 @@ __device__ __forceinline__ double blo_lnl_tile(const BloView &v, const ModelCons
       {
         double lk = log(terma);
         if (sc[j]) lk = __dadd_rn(lk, __dmul_rn((double)sc[j], m.log_scale_thr));
+        if (m.weights) lk = __dmul_rn(lk, (double)__ldg(m.weights + site));
         acc = __dadd_rn(acc, lk);
       }
     }

@@ -115,6 +115,7 @@ struct ptgpu_engine
   // many-wanderer process to two kernels in flight
   unsigned char *h_pin = nullptr;
   size_t h_pin_cap = 0;
+  unsigned int *d_weights = nullptr; // pattern weights (ptgpu_set_pattern_weights), model.weights points here
   bool counted = false;             // included in g_live_engines
   int coop_blocks_per_sm = 0;
   int sm_count = 0;
@@ -367,7 +368,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   if (e->counted) g_live_engines[e->device & 63].fetch_sub(1);
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
-  cudaFree(e->d_raw_all); cudaFree(e->d_tip_of); cudaFree(e->d_bad);
+  cudaFree(e->d_raw_all); cudaFree(e->d_tip_of); cudaFree(e->d_bad); cudaFree(e->d_weights);
   cudaFree(e->d_tips); cudaFree(e->d_raw); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
   cudaFree(e->d_sumtable); cudaFree(e->d_persite); cudaFree(e->d_partials); cudaFree(e->d_counter);
   cudaFree(e->d_state); cudaFree(e->d_idx1); cudaFree(e->d_red); cudaFree(e->d_active);
@@ -450,6 +451,88 @@ int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *se
     const unsigned char ch = (unsigned char)sequence[bad];
     return fail(PTGPU_ERR_STATE, "Illegal state code in tip \"%c\" (site %u)", ch ? ch : '?', bad);
   }
+  return PTGPU_OK;
+}
+
+namespace { int pin_reserve(ptgpu_engine *e, size_t bytes); }
+
+int ptgpu_set_pattern_weights(ptgpu_engine *e, const unsigned int *weights)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_set_pattern_weights: null engine");
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamSynchronize(e->stream));
+  if (!weights)
+  {
+    e->model.weights = nullptr;
+    return PTGPU_OK;
+  }
+  for (unsigned int i = 0; i < e->sites; ++i)
+    if (!weights[i]) return fail(PTGPU_ERR_ARG, "ptgpu_set_pattern_weights: weight of pattern %u is zero", i);
+  if (!e->d_weights) CU(cudaMalloc(&e->d_weights, (size_t)e->sites * sizeof(unsigned int)));
+  int rc;
+  if ((rc = pin_reserve(e, (size_t)e->sites * sizeof(unsigned int)))) return rc;
+  memcpy(e->h_pin, weights, (size_t)e->sites * sizeof(unsigned int));
+  CU(cudaMemcpyAsync(e->d_weights, e->h_pin, (size_t)e->sites * sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  e->model.weights = e->d_weights;
+  return PTGPU_OK;
+}
+
+int ptgpu_compress_site_patterns(char **sequences, unsigned int count, unsigned int *length,
+                                 unsigned int *weights_out)
+{
+  if (!sequences || !length || !weights_out || !count)
+    return fail(PTGPU_ERR_ARG, "ptgpu_compress_site_patterns: null argument");
+  const size_t n = *length;
+  if (!n) return PTGPU_OK;
+  // state codes of the characters and, for the way back, the LAST character of every code
+  // (LIBPLL/compress.c:166-170: inv_charmap is filled in ascending character order)
+  unsigned char code[256], back[256] = {0};
+  for (int c = 0; c < 256; ++c) code[c] = (unsigned char)nucleotide_mask((unsigned char)c);
+  code[0] = 0;
+  for (int c = 0; c < 256; ++c)
+    if (code[c]) back[code[c]] = (unsigned char)c;
+  // columns as rows (:214-219)
+  std::vector<unsigned char> col(n * count);
+  for (unsigned int j = 0; j < count; ++j)
+  {
+    if (!sequences[j]) return fail(PTGPU_ERR_ARG, "ptgpu_compress_site_patterns: sequence %u is null", j);
+    for (size_t i = 0; i < n; ++i)
+    {
+      const unsigned char k = code[(unsigned char)sequences[j][i]];
+      if (!k)
+        return fail(PTGPU_ERR_STATE, "Illegal state code in sequence %u \"%c\" (site %zu)", j,
+                    sequences[j][i] ? sequences[j][i] : '?', i);
+      col[i * count + j] = k;
+    }
+  }
+  // the reference sorts the columns (multikey quicksort, :222) and keeps the first of every run
+  // of equal ones (:229-241): the outcome is the set of distinct columns in ascending order
+  std::vector<size_t> order(n);
+  for (size_t i = 0; i < n; ++i) order[i] = i;
+  const unsigned char *base = col.data();
+  std::sort(order.begin(), order.end(), [base, count](size_t a, size_t b) {
+    return memcmp(base + a * count, base + b * count, count) < 0;
+  });
+  size_t m = 0;
+  for (size_t i = 0; i < n; ++i)
+  {
+    const unsigned char *c = base + order[i] * count;
+    if (i && memcmp(c, base + order[i - 1] * count, count) == 0)
+    {
+      ++weights_out[m - 1];
+      continue;
+    }
+    weights_out[m] = 1;
+    order[m] = order[i];   // m <= i: entries before i are no longer needed
+    ++m;
+  }
+  for (unsigned int j = 0; j < count; ++j)
+  {
+    for (size_t i = 0; i < m; ++i) sequences[j][i] = (char)back[base[order[i] * count + j]];
+    sequences[j][m] = 0;   // :248-249 (the input carries its terminator, so index m <= n exists)
+  }
+  *length = (unsigned int)m;
   return PTGPU_OK;
 }
 
@@ -912,13 +995,19 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
   CU(cudaSetDevice(e->device));
   const size_t stride = e->dev.clv_stride;
   // candidates are processed in chunks whose sumtables fit the scratch budget
-  size_t free_b = 0, total_b = 0;
-  CU(cudaMemGetInfo(&free_b, &total_b));
   const size_t per_cand = stride * sizeof(double) + (size_t)e->sites * sizeof(unsigned int) +
                           (size_t)e->ntiles * 3 * sizeof(double) + sizeof(NewtonState) + sizeof(DevGroup);
-  size_t have = e->bcap * per_cand;
-  size_t budget = std::max(have, (size_t)((free_b + have) * 0.8));
-  size_t chunk = std::min<size_t>(count, std::max<size_t>(1, budget / per_cand));
+  size_t chunk = count;
+  if (chunk > e->bcap)
+  {
+    // the scratch has to grow: as many candidates per launch as 80 % of the free memory holds
+    // (asked only now -- cudaMemGetInfo is a heavyweight driver call, not one for every batch)
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    const size_t have = e->bcap * per_cand;
+    const size_t budget = std::max(have, (size_t)((free_b + have) * 0.8));
+    chunk = std::min<size_t>(count, std::max<size_t>(1, budget / per_cand));
+  }
   if (chunk > e->bcap)
   {
     cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials); cudaFree(e->d_bcands);

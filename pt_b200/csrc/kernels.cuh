@@ -57,6 +57,9 @@ struct ModelConst
   double rates[kMaxCats];
   double rate_weight;   // 1/C                               (LIBPLL/pll.c:742-748)
   double log_scale_thr; // host log(2^-256)                  (LIBPLL/core_likelihood_avx.c:1250)
+  // pattern weights [sites] (LIBPLL/pll.c: pll_set_pattern_weights), or null = all 1 as under
+  // pt, which never compresses; read only where a per-site value enters a sum over sites
+  const unsigned int *weights;
 };
 
 struct DevOp // == ptgpu_operation_t
@@ -623,6 +626,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C)
     {
       double lk = log(terma);
       if (sc[ps]) lk = __dadd_rn(lk, __dmul_rn((double)sc[ps], m.log_scale_thr));
+      if (m.weights) lk = __dmul_rn(lk, (double)__ldg(m.weights + site));  // :1254
       if (persite) persite[site] = lk;
       acc = __dadd_rn(acc, lk);
     }
@@ -735,6 +739,35 @@ struct LnlProd
     prod = __dmul_rn(prod, __hiloint2double((hi & 0x800fffff) | 0x3fe00000, lo));  // mantissa in [0.5, 1)
     if (prod < 3.0549363634996047e-151) { prod = __dmul_rn(prod, 3.2733906078961419e150); esum -= 500; }  // x 2^500
   }
+  // pattern of weight w: its likelihood enters the product w times, i.e. mantissa^w (by
+  // squaring, renormalised to [0.5, 1) after every product so nothing underflows) and
+  // w x exponent; no extra state is carried by the unweighted path
+  __device__ __forceinline__ void add_weighted(double terma, unsigned int sc, unsigned int w)
+  {
+    if (!(terma > 0.0)) { zero = zero || terma == 0.0; if (terma != 0.0) prod = terma; return; }
+    int ex = 0;
+    if (terma < 2.2250738585072014e-308) { terma = __dmul_rn(terma, 1.2676506002282294e30); ex = -100; }
+    const int hi = __double2hiint(terma), lo = __double2loint(terma);
+    ex += ((hi >> 20) & 0x7ff) - 1022 - 256 * (int)sc;
+    esum += ex * (int)w;
+    double b = __hiloint2double((hi & 0x800fffff) | 0x3fe00000, lo), r = 1.0;
+    int be = 0, re = 0;
+    while (true)
+    {
+      if (w & 1u)
+      {
+        r = __dmul_rn(r, b); re += be;
+        if (r < 0.5) { r = __dmul_rn(r, 2.0); re -= 1; }
+      }
+      w >>= 1;
+      if (!w) break;
+      b = __dmul_rn(b, b); be *= 2;
+      if (b < 0.5) { b = __dmul_rn(b, 2.0); be -= 1; }
+    }
+    esum += re;
+    prod = __dmul_rn(prod, r);
+    if (prod < 3.0549363634996047e-151) { prod = __dmul_rn(prod, 3.2733906078961419e150); esum -= 500; }
+  }
   __device__ __forceinline__ double value() const
   {
     if (zero) return -INFINITY;
@@ -750,6 +783,29 @@ __device__ __forceinline__ void site_terms(const ModelConst &m, const double lk[
 {
   // LIBPLL/core_derivatives_avx.c:1111-1156: sites below `full` (= sites/4*4) use
   // the reciprocal form of the 4-site vector step, the tail true divisions
+  if (m.weights)
+  {
+    // pattern weights multiply the site's two terms (:1131-1139, :1153-1154).  All-ones, pt's
+    // own case, is m.weights == null and takes the code below untouched.
+    const unsigned int w = __ldg(m.weights + site);
+    double a, b;
+    if (site < full)
+    {
+      const double recip = __ddiv_rn(1.0, lk[0]);
+      a = __dmul_rn(lk[1], recip);
+      b = __dadd_rn(__dmul_rn(a, a), -__dmul_rn(lk[2], recip));
+      a = -a;
+    }
+    else
+    {
+      a = -__ddiv_rn(lk[1], lk[0]);
+      b = __dadd_rn(__dmul_rn(a, a), -__ddiv_rn(lk[2], lk[0]));
+    }
+    out[0] = __dadd_rn(out[0], __dmul_rn(a, (double)w));
+    out[1] = __dadd_rn(out[1], __dmul_rn(b, (double)w));
+    if (WITH_LNL) lp.add_weighted(terma, sc, w);
+    return;
+  }
   if (site < full)
   {
     const double recip = __ddiv_rn(1.0, lk[0]);

@@ -74,6 +74,22 @@ def ops_array(rows):
     return out
 
 
+def compress_site_patterns(seqs):
+    """ptgpu_compress_site_patterns (= pll_compress_site_patterns for nucleotide data): the
+    unique columns of equally long sequences and their multiplicities.  Host-only."""
+    L = load_library()
+    n = len(seqs[0])
+    bufs = [C.create_string_buffer(s.encode() if isinstance(s, str) else bytes(s), n + 1) for s in seqs]
+    arr = (C.c_char_p * len(seqs))(*[C.cast(b, C.c_char_p) for b in bufs])
+    w = np.zeros(max(n, 1), dtype=np.uint32)
+    ln = C.c_uint(n)
+    rc = L.ptgpu_compress_site_patterns(arr, C.c_uint(len(seqs)), C.byref(ln), w.ctypes.data_as(_up))
+    if rc != PTGPU_OK:
+        raise PtGpuError(rc, L.ptgpu_last_error().decode())
+    m = ln.value
+    return [b.raw[:m].decode() for b in bufs], w[:m].copy()
+
+
 class Engine:
     """One alignment resident on one B200 (a ptgpu_engine handle)."""
 
@@ -102,6 +118,16 @@ class Engine:
             self.close()
         except Exception:
             pass
+
+    def set_pattern_weights(self, weights):
+        """pll_set_pattern_weights; None restores all-ones"""
+        if weights is None:
+            self._chk(self.lib.ptgpu_set_pattern_weights(self.h, None))
+            return
+        w = np.ascontiguousarray(weights, dtype=np.uint32)
+        if w.size != self.sites:
+            raise ValueError("one weight per site pattern")
+        self._chk(self.lib.ptgpu_set_pattern_weights(self.h, w.ctypes.data_as(_up)))
 
     # --- model / data -----------------------------------------------------
     def set_model(self, freqs, subst, rates):

@@ -136,13 +136,39 @@ Partition::Partition(pll_utree_t* tree,
     if (const char* env = std::getenv("PTGPU_FUSED_ALL_BRANCHES_MAX_SITES")) limit = std::strtoul(env, nullptr, 10);
     stepwise_all_branches_ = std::getenv("PTGPU_STEPWISE_ALL_BRANCHES") != nullptr || site_count_ > limit;
   }
+  // PTGPU_COMPRESS_PATTERNS=1 (off by default, as pt never compresses): the engine
+  // holds the alignment's unique columns and weights every sum over sites by their
+  // multiplicities (pll_compress_site_patterns + pll_set_pattern_weights, LIBPLL/compress.c:138,
+  // LIBPLL/pll.c:1047).  Scores then differ from the uncompressed ones in the last bits only
+  // (another summation order; well inside the 1e-9 the tables are compared at).
+  std::vector<std::string> unique_columns;
+  std::vector<unsigned int> weights;
+  const std::vector<std::string>* tip_sequences = &sequences;
+  if (std::getenv("PTGPU_COMPRESS_PATTERNS") && site_count_ > 0) {
+    bool ragged = false;   // left to SetTipStates, which names the offending sequence
+    for (const std::string& s : sequences) ragged = ragged || s.size() != site_count_;
+    if (!ragged) {
+      unique_columns = sequences;
+      std::vector<char*> rows;
+      for (std::string& s : unique_columns) rows.push_back(&s[0]);
+      unsigned int length = site_count_;
+      weights.resize(length);
+      Check(ptgpu_compress_site_patterns(rows.data(), static_cast<unsigned int>(rows.size()), &length,
+                                         weights.data()));
+      for (std::string& s : unique_columns) s.resize(length);
+      weights.resize(length);
+      site_count_ = length;
+      tip_sequences = &unique_columns;
+    }
+  }
   device_ = pick_device();
   Check(ptgpu_create(tip_node_count_, inner_node_count() + extra, site_count_,
                      static_cast<unsigned int>(model.category_rates.size()), branch_count(),
                      inner_node_count() + extra, device_, &engine_));
   try {
     SetModel(model);
-    SetTipStates(tree, labels, sequences);
+    SetTipStates(tree, labels, *tip_sequences);
+    if (!weights.empty()) Check(ptgpu_set_pattern_weights(engine_, weights.data()));
   } catch (...) {
     ptgpu_destroy(engine_);
     engine_ = nullptr;
