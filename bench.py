@@ -320,6 +320,16 @@ def run_ours(args):
     aln = simulate(base, S, np.random.default_rng(SEED_ALN))
     tree = parent_tree(n, rank)
     labels = tree.labels()
+    S_sites, weights = S, None
+    if args.compress_patterns:
+        # NOT the headline configuration (pt never compresses; BASELINE's shapes are in sites):
+        # the same alignment as its unique columns + multiplicities, prepared once
+        # outside the timed region like the alignment itself
+        from pt_b200.engine import compress_site_patterns
+        keys = list(aln.keys())
+        cols, weights = compress_site_patterns([bytes(aln[k]) for k in keys])
+        aln = {k: np.frombuffer(c.encode(), dtype=np.uint8).copy() for k, c in zip(keys, cols)}
+        S = len(weights)
     # raw alignment in pinned host memory (what a caller hands to the C ABI)
     host_aln = torch.empty((n, S), dtype=torch.uint8).pin_memory()
     for i, tip in enumerate(tree.nodes[:n]):
@@ -327,6 +337,8 @@ def run_ours(args):
     nbuf = 3 * (n - 2)
     e = Engine(n, nbuf, S, 4, 2 * n - 3, nbuf, device=local)
     e.set_model(FREQS, SUBST, RATES)
+    if weights is not None:
+        e.set_pattern_weights(weights)
 
     tip_ids = np.arange(n, dtype=np.uint32)
     tip_ptrs = [host_aln[t].data_ptr() for t in range(n)]
@@ -463,11 +475,13 @@ def run_ours(args):
         metric="nni_candidates_scored_per_s", value=value, unit="candidates/s",
         n_gpus=world, steps=steps, warmup=args.warmup, ms_per_step=ms / steps,
         higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
-        config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]/[3] shape): "
+        config=dict(workload=f"synthetic {n} taxa x {S_sites} sites GTR+G4 (BASELINE configs[2]/[3] shape)"
+                             + (f", PATTERN-COMPRESSED to {S} unique columns + weights (not the headline "
+                                f"configuration)" if weights is not None else "") + ": "
                              f"per step all {ncand} NNI candidates of one parent tree per GPU, "
                              + tester_name(args.radius) + " semantics, incl. P matrices and "
                              f"the {len(plan_rows)} directional CLVs the candidates read "
-                             f"(of 3(n-2) = {3 * (n - 2)})", taxa=n, sites=S, rate_cats=4,
+                             f"(of 3(n-2) = {3 * (n - 2)})", taxa=n, sites=S_sites, patterns=S, rate_cats=4,
                     candidates_per_step_per_gpu=ncand, parallelism=f"candidate-parallel x{world}",
                     l2="inputs (>20 GB of CLVs per step) far exceed the 126 MB L2; no flush needed"),
         step_host_ms=step_host_ms, e2e_step_host_ms=[round(1e3 * x, 3) for x in t_e2e],
@@ -566,6 +580,8 @@ def main():
     ap.add_argument("--cpu-sample-sites", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1"])
+    ap.add_argument("--compress-patterns", action="store_true",
+                    help="score the alignment's unique columns with weights (SURVEY 8f-4; not the headline)")
     ap.add_argument("--wanderers", type=int, default=1,
                     help="ptw-ds1: wanderer threads of ptw_batched (each owns an engine on the GPU)")
     args = ap.parse_args()
