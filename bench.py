@@ -25,6 +25,8 @@ partition per thread, on a bounded site sample, scaled to the full site count.
 (`--lnl-offset -5 --optimization-radius 1`, one wanderer) through ptw_batched (pt's own
 driver objects + this engine + the batched move tester) next to the reference's
 ptw_threads on the host cores; candidates/s = EvaluateMove questions / wall time.
+`--workload sharded`: BASELINE configs[2] -- one tree's full-tree lnL + OptimizeAllBranches with the
+SITES sharded over the GPUs (strong scaling; allreduce of per-tree scalars only), see run_sharded.
 """
 import argparse
 import json
@@ -566,6 +568,219 @@ def run_ptw_ds1(args):
     print(json.dumps(line))
 
 
+# --------------------------------------------------------------------------
+# BASELINE configs[2]: one tree, sites sharded over the GPUs (strong scaling)
+# --------------------------------------------------------------------------
+def sharded_reference_leg(taxa, sites, sample, steps=1):
+    """the unmodified reference on one host thread (a single tree gives libpll nothing to run
+    in parallel): FULL traversal + lnL + OptimizeAllBranches on `sample` sites, scaled"""
+    from oracle.pyoracle import RefLib, have_ref
+    if not have_ref():
+        return None
+    tree = parent_tree(taxa, 0)
+    aln = simulate(tree, sample, np.random.default_rng(SEED_ALN))
+    labels = tree.labels()
+    best = None
+    for _ in range(1 + steps):
+        p = RefLib().open_mem(tree.newick(), labels, [bytes(aln[l]) for l in labels], FREQS, SUBST, RATES)
+        t0 = time.perf_counter()
+        p.traversal_update(p.root, True)
+        p.loglikelihood(p.root)
+        p.optimize_all_branches(p.root)
+        p.traversal_update(p.root, False)
+        lnl = p.loglikelihood(p.root)
+        dt = time.perf_counter() - t0
+        p.close()
+        best = dt if best is None else min(best, dt)
+    return dict(value=1.0 / (best * sites / sample), unit="trees/s", cores=1, kind="reference",
+                sample=f"FULL traversal + lnL + OptimizeAllBranches of one {taxa}-taxon tree on {sample} of "
+                       f"{sites} sites, 1 thread (one tree is sequential in the reference), best of "
+                       f"{1 + steps} ({best:.2f} s), scaled by sites ratio", seconds_at_sample=best)
+
+
+def run_sharded(args):
+    """`--workload sharded`: BASELINE configs[2] -- synthetic 64 taxa x 1M sites, full-tree lnL +
+    OptimizeAllBranches, the SITES split over the ranks (contiguous tile-aligned ranges).  The
+    only collective is the allreduce of per-tree scalars the engine issues on its own stream
+    (1 double per edge lnL, 3 per Newton step); strong scaling: the tree and the alignment are
+    the same at every N.  One STEP = what Wanderer::MoveForward does for a tree it visits
+    (src/wanderer.cpp:150-210): FULL TraversalUpdate, LogLikelihood, OptimizeAllBranches
+    (call by call: the step-program kernel is a single-device procedure), LogLikelihood."""
+    import torch
+    import torch.distributed as dist
+    import all_branches as ab
+    from pt_b200.engine import ops_array
+    from pt_b200.sharded import SiteShardedEngine, shard_range
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if rank == 0:
+            T = host_cores()
+            cb = sharded_reference_leg(args.taxa, args.sites, min(args.sites, 20000), args.steps)
+            if cb is None:
+                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpllref.so missing"}))
+                return
+            print(json.dumps(dict(metric="trees_visited_per_s", value=cb["value"], unit="trees/s", impl="reference",
+                                  n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                                  ms_per_step=1e3 / cb["value"], higher_is_better=True, scaling="strong",
+                                  vs_baseline=None, dtype="f64", data="synthetic",
+                                  config=dict(workload=f"synthetic {args.taxa} taxa x {args.sites} sites GTR+G4: "
+                                              "full-tree lnL + OptimizeAllBranches of one tree",
+                                              taxa=args.taxa, sites=args.sites, rate_cats=4, host_cores=T),
+                                  cpu_baseline=cb,
+                                  e2e=dict(value=cb["value"], unit="trees/s", h2d_bytes_per_step=0,
+                                           d2h_bytes_per_step=0))))
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29577")
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n, S = args.taxa, args.sites
+    tree = parent_tree(n, 0)
+    aln = simulate(tree, S, np.random.default_rng(SEED_ALN))
+    e = SiteShardedEngine(n, n - 2, S, 4, 2 * n - 3, n - 2, device=local)
+    e.set_model(FREQS, SUBST, RATES)
+    b0, b1 = shard_range(S, world, rank)
+    # this rank's slice of the raw alignment in pinned host memory
+    host_aln = torch.empty((n, b1 - b0), dtype=torch.uint8).pin_memory()
+    for tip in tree.nodes[:n]:
+        host_aln[tip.clv_index].copy_(torch.from_numpy(np.ascontiguousarray(aln[tip.label][b0:b1])))
+    tip_ids = np.arange(n, dtype=np.uint32)
+    tip_ptrs = [host_aln[t].data_ptr() for t in range(n)]
+    e.engine.set_tip_states_batch(tip_ids, tip_ptrs)
+    lengths0 = {r.node_index: r.length for r in tree.by_index.values()}
+    root = tree.root
+    info = {}
+    count = dict(partials_bytes=0)      # per site, over ALL steps run (warm-up, timed, e2e)
+    raw_update_partials = e.engine.update_partials
+
+    def counted_update_partials(ops):
+        for c in ("child1_clv_index", "child2_clv_index"):
+            count["partials_bytes"] += int(np.where(ops[c] < n, 1, 132).sum())
+        count["partials_bytes"] += 132 * len(ops)
+        raw_update_partials(ops)
+
+    e.engine.update_partials = counted_update_partials
+
+    def step():
+        for r in tree.by_index.values():          # every step starts from the input lengths
+            r.length = lengths0[r.node_index]
+        flags = ab.Flags()
+        mats, ops = ab.traverse(root, flags, partial=False)
+        e.update_prob_matrices([m.pmatrix_index for m in mats], [m.length for m in mats])
+        e.update_partials(ops_array(ops))
+        rb = root.back
+        info["lnl0"] = e.edge_loglikelihood(root.clv_index, root.scaler_index, rb.clv_index,
+                                            rb.scaler_index, root.pmatrix_index)
+        info["lnl"], info["passes"] = ab.stepwise(e, root, flags)
+
+    for _ in range(args.warmup):
+        step()
+    stream = torch.cuda.ExternalStream(e.stream(), device=torch.device("cuda", local))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0, calls0, dbl0 = e.counters(), e.allreduce_calls, e.allreduce_doubles
+    dist.barrier()
+    torch.cuda.synchronize()
+    wall0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    c1, calls1, dbl1 = e.counters(), e.allreduce_calls, e.allreduce_doubles
+    # per-kernel CUDA events in a SEPARATE pass: two event records around each of the ~20 k
+    # launches of a step would weigh on the timed region
+    e.set_profiling(True)
+    e.kernel_times(reset=True)
+    torch.cuda.synchronize()
+    tp0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize()
+    ms_profiled = 1e3 * (time.perf_counter() - tp0)
+    kt = e.kernel_times(reset=True)
+    e.set_profiling(False)
+    t_e2e = []
+    for i in range(1 + args.steps):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e.engine.set_tip_states_batch(tip_ids, tip_ptrs)
+        step()
+        torch.cuda.synchronize()
+        if i:
+            t_e2e.append(time.perf_counter() - t0)
+    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
+    t = torch.tensor([ms, sum(t_e2e)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_s = float(t[0]), float(t[1])
+    upd = torch.tensor([float(c1["site_updates"] - c0["site_updates"]),
+                        float(c1["newton_passes"] - c0["newton_passes"])], dtype=torch.float64, device="cuda")
+    dist.all_reduce(upd, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        dist.destroy_process_group()
+        return
+    steps = args.steps
+    site_updates = float(upd[0])                      # all ranks, all timed steps
+    peak, peak_kind = measured_peak()
+    Sl = b1 - b0
+    # rank 0's kernels on its shard (CUDA events on the engine's stream); algorithmic bytes:
+    # CLV updates exactly from the op lists, sumtable 384 B/site (256 in, 128 out), a derivative
+    # sweep 128 B/site (one sweep + one reduce + one update kernel per Newton step), edge lnL 268 B/site
+    kernels = {}
+    sweeps = kt["newton"][1] / 3.0 / steps
+    algo = dict(partials=count["partials_bytes"] / (1 + args.warmup + 3 * steps) * steps * Sl,
+                sumtable=kt["sumtable"][1] * 384.0 * Sl, newton=sweeps * steps * 128.0 * Sl,
+                edge_lnl=kt["edge_lnl"][1] * 268.0 * Sl)
+    for k in ("partials", "sumtable", "newton", "edge_lnl", "pmatrix"):
+        k_ms, k_n = kt[k]
+        if k_n:
+            kernels[k] = dict(ms_total_per_step=k_ms / steps, launches_per_step=k_n / steps,
+                              share_of_step=k_ms / ms_profiled)
+            if k in algo:
+                kernels[k]["achieved_gbs"] = algo[k] / (k_ms * 1e-3) / 1e9
+    gap = 1.0 - sum(v["share_of_step"] for v in kernels.values())
+    dom = max(kernels, key=lambda k: kernels[k]["share_of_step"]) if kernels else None
+    value = steps / (ms * 1e-3)
+    line = dict(
+        metric="trees_visited_per_s", value=value, unit="trees/s", n_gpus=world, steps=steps,
+        warmup=args.warmup, ms_per_step=ms / steps, higher_is_better=True, scaling="strong",
+        vs_baseline=None, dtype="f64", data="synthetic",
+        config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]): per step FULL "
+                             "traversal + lnL + OptimizeAllBranches + lnL of ONE tree, sites sharded over the "
+                             "GPUs (contiguous tile-aligned ranges), allreduce of per-tree scalars only",
+                    taxa=n, sites=S, sites_per_gpu=Sl, rate_cats=4, parallelism=f"site-sharded x{world}",
+                    l2="every pass streams this rank's CLVs (>= 128 MB each at N <= 8): larger than L2; no flush"),
+        clv_site_updates_per_s=site_updates / (ms * 1e-3),
+        optimize_all_branches_passes=info["passes"], newton_sweeps_per_step=sweeps,
+        allreduce_calls_per_step=(calls1 - calls0) / steps,
+        allreduce_doubles_per_step=(dbl1 - dbl0) / steps,
+        lnl_start=info["lnl0"], lnl_optimised=info["lnl"],
+        gpu_launches=int(c1["launches"] - c0["launches"]), kernels=kernels,
+        outside_kernels_share=gap,   # launch gaps, the allreduce and the Python driver between ~20 k launches
+        ms_per_step_with_kernel_events=ms_profiled / steps,
+        roofline=(dict(bound="hbm", kernel=dom, achieved=kernels[dom]["achieved_gbs"], peak=peak, unit="GB/s",
+                       frac=kernels[dom]["achieved_gbs"] / peak, peak_source=peak_kind, traffic=None)
+                  if dom else None),
+        clocks=clocks,
+        e2e=dict(value=steps / e2e_s, unit="trees/s", h2d_bytes_per_step=n * Sl, d2h_bytes_per_step=16,
+                 note="every rank uploads + encodes its slice of the raw alignment (pinned host memory) "
+                      "every step; bytes are per rank"))
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = sharded_reference_leg(n, S, min(S, 20000))
+    print(json.dumps(line))
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -579,7 +794,7 @@ def main():
                          "BranchNeighborhoodOptimizer semantics (BASELINE configs[1]'s tester)")
     ap.add_argument("--cpu-sample-sites", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1"])
+    ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1", "sharded"])
     ap.add_argument("--compress-patterns", action="store_true",
                     help="score the alignment's unique columns with weights (SURVEY 8f-4; not the headline)")
     ap.add_argument("--wanderers", type=int, default=1,
@@ -588,6 +803,8 @@ def main():
     if args.workload == "ptw-ds1":
         if int(os.environ.get("RANK", "0")) == 0:
             run_ptw_ds1(args)
+    elif args.workload == "sharded":
+        run_sharded(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

@@ -66,6 +66,7 @@ class SiteShardedEngine:
         self.engine.set_allreduce(self._hook)
         self.allreduce_calls = 0
         self.allreduce_doubles = 0
+        self._views = {}
 
     # the hook the engine calls between its local reduction and the scalar update
     def _allreduce(self, ctx, ptr, count, stream):
@@ -74,10 +75,19 @@ class SiteShardedEngine:
             self.allreduce_calls += 1
             self.allreduce_doubles += int(count)
             if self.on_cuda:
-                dev = torch.device("cuda", self.device if self.device is not None else
-                                   torch.cuda.current_device())
-                t = torch.as_tensor(_DevBuf(ptr, int(count)), device=dev)
-                with torch.cuda.stream(torch.cuda.ExternalStream(stream, device=dev)):
+                # the engine hands over the same few buffers on the same stream call after call
+                # (several thousand times per OptimizeAllBranches): the zero-copy tensor view and
+                # the stream wrapper are made once per (pointer, count, stream)
+                key = (ptr, int(count), stream)
+                hit = self._views.get(key)
+                if hit is None:
+                    dev = torch.device("cuda", self.device if self.device is not None else
+                                       torch.cuda.current_device())
+                    hit = (torch.as_tensor(_DevBuf(ptr, int(count)), device=dev),
+                           torch.cuda.ExternalStream(stream, device=dev))
+                    self._views[key] = hit
+                t, ext = hit
+                with torch.cuda.stream(ext):
                     dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
             else:
                 a = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(int(count),))

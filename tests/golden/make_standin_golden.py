@@ -34,7 +34,7 @@ DATA = os.path.join(HERE, "data", "standins")
 # published shapes: name -> (taxa, sites, walk arguments)
 SETS = {
     "DS3": (36, 1812, ["--lnl-offset", "-2", "--optimization-radius", "1"]),
-    "DS5": (50, 378, ["--lnl-offset", "-1", "--optimization-radius", "0"]),
+    "DS6": (50, 1133, ["--lnl-offset", "-2", "--optimization-radius", "0"]),
     "DS8": (64, 1008, ["--lnl-offset", "-2", "--optimization-radius", "1"]),
 }
 
