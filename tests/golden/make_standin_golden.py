@@ -35,7 +35,7 @@ DATA = os.path.join(HERE, "data", "standins")
 SETS = {
     "DS3": (36, 1812, ["--lnl-offset", "-2", "--optimization-radius", "1"]),
     "DS6": (50, 1133, ["--lnl-offset", "-2", "--optimization-radius", "0"]),
-    "DS8": (64, 1008, ["--lnl-offset", "-2", "--optimization-radius", "1"]),
+    "DS8": (64, 1008, ["--lnl-offset", "-1.5", "--optimization-radius", "0"]),
 }
 
 
