@@ -249,6 +249,14 @@ int coop_occupancy(int *out)
   CU(cudaFuncSetAttribute(newton_sweep_kernel<C, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
   CU(cudaFuncSetAttribute(newton_sweep_kernel<C, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
   CU(cudaFuncSetAttribute(newton_sweep_kernel<C, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ring));
+  // the few-work-items variants (deep ring; one CTA per SM is all they need)
+  constexpr int FS = few_work_stages<C>();
+  const int deep = (int)ring_bytes<C>(FS);
+  CU(cudaFuncSetAttribute(newton_kernel<C, false, FS>, cudaFuncAttributeMaxDynamicSharedMemorySize, deep));
+  CU(cudaFuncSetAttribute(newton_kernel<C, true, FS>, cudaFuncAttributeMaxDynamicSharedMemorySize, deep));
+  CU(cudaFuncSetAttribute(newton_sweep_kernel<C, false, false, FS>, cudaFuncAttributeMaxDynamicSharedMemorySize, deep));
+  CU(cudaFuncSetAttribute(newton_sweep_kernel<C, true, false, FS>, cudaFuncAttributeMaxDynamicSharedMemorySize, deep));
+  CU(cudaFuncSetAttribute(newton_sweep_kernel<C, true, true, FS>, cudaFuncAttributeMaxDynamicSharedMemorySize, deep));
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, newton_kernel<C, false>, kSitesPerPass * C, ring));
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, newton_kernel<C, true>, kSitesPerPass * C, ring));
   *out = std::min(a, b);
@@ -683,6 +691,14 @@ int launch_pmatrix(ptgpu_engine *e, const unsigned int *d_idx, const double *d_l
   return PTGPU_OK;
 }
 
+// few work items, each a long chunk: the launches that take the deep-ring sweep (kernels.cuh,
+// few_work_stages); PTGPU_FEW_WORK_RING=0 turns it off
+bool few_long_items(const ptgpu_engine *e, unsigned int work, unsigned int chunk_tiles)
+{
+  static const bool on = [] { const char *v = getenv("PTGPU_FEW_WORK_RING"); return !v || atoi(v) != 0; }();
+  return on && work <= (unsigned int)e->sm_count && chunk_tiles >= 8;
+}
+
 template <int C>
 int launch_newton(ptgpu_engine *e, NewtonArgs &a)
 {
@@ -692,8 +708,17 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   void *params[] = {&a};
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-    void *fn = a.want_lnl ? (void *)newton_kernel<C, true> : (void *)newton_kernel<C, false>;
-    CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kSitesPerPass * C), params, sweep_ring_bytes<C>(), e->stream));
+    if (few_long_items(e, work, a.chunk_tiles))
+    {
+      constexpr int FS = few_work_stages<C>();
+      void *fn = a.want_lnl ? (void *)newton_kernel<C, true, FS> : (void *)newton_kernel<C, false, FS>;
+      CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kSitesPerPass * C), params, ring_bytes<C>(FS), e->stream));
+    }
+    else
+    {
+      void *fn = a.want_lnl ? (void *)newton_kernel<C, true> : (void *)newton_kernel<C, false>;
+      CU(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kSitesPerPass * C), params, sweep_ring_bytes<C>(), e->stream));
+    }
   }
   return PTGPU_OK;
 }
@@ -717,14 +742,24 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
   if (!e->d_active) CU(cudaMalloc(&e->d_active, 2 * sizeof(unsigned int)));
   const unsigned int work = std::max(1u, a.B * a.nchunks);
   const unsigned int grid = std::min(work, (unsigned int)e->sm_count * 8u);
+  constexpr int FS = few_work_stages<C>();
+  const bool deep = few_long_items(e, work, a.chunk_tiles);
   volatile unsigned int *active_h = (volatile unsigned int *)(e->stg.host + 256);
   unsigned int pending_lnl = 0;
   for (unsigned int it = 0; it < a.max_iter; ++it)
   {
     {
       LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-      if (a.want_lnl) newton_sweep_kernel<C, true, false><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
-      else newton_sweep_kernel<C, false, false><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
+      if (deep)
+      {
+        if (a.want_lnl) newton_sweep_kernel<C, true, false, FS><<<grid, kSitesPerPass * C, ring_bytes<C>(FS), e->stream>>>(a);
+        else newton_sweep_kernel<C, false, false, FS><<<grid, kSitesPerPass * C, ring_bytes<C>(FS), e->stream>>>(a);
+      }
+      else
+      {
+        if (a.want_lnl) newton_sweep_kernel<C, true, false><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
+        else newton_sweep_kernel<C, false, false><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
+      }
     }
     { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<false><<<a.B, 256, 0, e->stream>>>(a, e->d_red); }
     CU(cudaGetLastError());
@@ -743,7 +778,8 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
   if (!pending_lnl) return PTGPU_OK;
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-    newton_sweep_kernel<C, true, true><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
+    if (deep) newton_sweep_kernel<C, true, true, FS><<<grid, kSitesPerPass * C, ring_bytes<C>(FS), e->stream>>>(a);
+    else newton_sweep_kernel<C, true, true><<<grid, kSitesPerPass * C, sweep_ring_bytes<C>(), e->stream>>>(a);
   }
   { LaunchScope ls(e, PTGPU_KERNEL_NEWTON); newton_reduce_kernel<true><<<a.B, 256, 0, e->stream>>>(a, e->d_red); }
   CU(cudaGetLastError());

@@ -951,17 +951,30 @@ constexpr int kRingStages = 3;
 #define PT_SWEEP_RING 0   // measured on B200: plain LDG.256 streaming (3 CTAs/SM) beats the ring (2 CTAs/SM)
 #endif
 
-template <int C>
-constexpr size_t sweep_ring_bytes() { return PT_SWEEP_RING ? (size_t)kRingStages * kPasses * kSitesPerPass * C * 32 : 0; }
+constexpr int kDefaultStages = PT_SWEEP_RING ? kRingStages : 0;   // 0 = direct loads
 
-template <int C, bool WITH_LNL>
+template <int C>
+constexpr size_t ring_bytes(int stages) { return (size_t)stages * kPasses * kSitesPerPass * C * 32; }
+
+template <int C>
+constexpr size_t sweep_ring_bytes() { return ring_bytes<C>(kDefaultStages); }
+
+// A launch with FEW work items, each a long chunk (one branch on a long alignment: B x nchunks
+// of the order of the SM count, 30 tiles per chunk) cannot hide memory latency behind other
+// CTAs -- there are none.  Such launches take the ring with as many stages as shared memory
+// holds: 5 tiles (160 KB at C = 4) in flight per SM instead of one.  Same arithmetic in the
+// same order as the direct form, so results are bit-identical.
+template <int C>
+constexpr int few_work_stages() { return C <= 4 ? 6 : 3; }
+
+template <int C, bool WITH_LNL, int STAGES = kDefaultStages>
 __device__ __forceinline__ void sweep_chunk(const ModelConst &m, const double *sumtable,
                                             const unsigned int *sclr, unsigned int sites,
                                             unsigned int t0, unsigned int t1, const double (&dg)[4][3],
                                             double *ring, double out[3], LnlProd &lp,
                                             unsigned long long vec_end)
 {
-  if (!PT_SWEEP_RING)
+  if (STAGES == 0)
   {
     for (unsigned int tile = t0; tile < t1; ++tile)
       sweep_tile<C, WITH_LNL>(m, sumtable, sclr, sites, tile, dg, out, lp, vec_end);
@@ -982,26 +995,26 @@ __device__ __forceinline__ void sweep_chunk(const ModelConst &m, const double *s
     }
   };
 #pragma unroll
-  for (int k = 0; k < kRingStages - 1; ++k)
+  for (int k = 0; k < STAGES - 1; ++k)
   {
     if (t0 + k < t1) issue(t0 + k, k);
     cp_async_commit();
   }
-  int stage = 0, fill = kRingStages - 1;
+  int stage = 0, fill = STAGES - 1;
   for (unsigned int tile = t0; tile < t1; ++tile)
   {
-    if (tile + (kRingStages - 1) < t1) issue(tile + (kRingStages - 1), fill);
+    if (tile + (STAGES - 1) < t1) issue(tile + (STAGES - 1), fill);
     cp_async_commit();                       // (possibly empty) group: keeps the count uniform
     unsigned int scv[kPasses];
     load_scaler_words<C, WITH_LNL>(sclr, sites, tile, scv);
-    cp_async_wait<kRingStages - 1>();        // the group of `tile` has landed
+    cp_async_wait<STAGES - 1>();        // the group of `tile` has landed
     double sv[kPasses][4];
 #pragma unroll
     for (int ps = 0; ps < kPasses; ++ps)
       lds256(ring + ((size_t)(stage * kPasses + ps) * T + threadIdx.x) * 4, sv[ps]);
     sweep_tile_compute<C, WITH_LNL>(m, sv, scv, sites, tile, dg, out, lp, vec_end);
-    stage = stage + 1 == kRingStages ? 0 : stage + 1;
-    fill = fill + 1 == kRingStages ? 0 : fill + 1;
+    stage = stage + 1 == STAGES ? 0 : stage + 1;
+    fill = fill + 1 == STAGES ? 0 : fill + 1;
   }
   cp_async_wait<0>();
 }
@@ -1152,8 +1165,8 @@ __device__ __forceinline__ void newton_scalar_update(const NewtonArgs &a, unsign
 // fixed-order reduction + the scalar update done by one CTA per branch, a grid
 // barrier.  Reduction units (chunks) depend only on the site count, so results
 // are independent of the grid size.
-template <int C, bool LNL>
-__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? (PT_SWEEP_RING ? 2 : 3) : 1)) newton_kernel(NewtonArgs a)
+template <int C, bool LNL, int STAGES = kDefaultStages>
+__global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (STAGES ? 2 : 3) : 1)) newton_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
   cg::grid_group grid = cg::this_grid();
@@ -1175,11 +1188,11 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? (PT_SWEEP_RING ? 2
       const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
       const bool with_lnl = LNL && __ldcg(&a.st[e].try_lnl);
       if (with_lnl)
-        sweep_chunk<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+        sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                               a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
       else
-        sweep_chunk<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+        sweep_chunk<C, false, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
                                chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
       const double s1 = block_sum<T>(out[0], red);
       const double s2 = block_sum<T>(out[1], red);
@@ -1228,7 +1241,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? (PT_SWEEP_RING ? 2
     double out[3] = {0.0, 0.0, 0.0};
     LnlProd lp;
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-    sweep_chunk<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+    sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                               a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
     const double sm = block_sum<T>(lp.value(), red);
@@ -1251,7 +1264,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 ? (PT_SWEEP_RING ? 2
 // the caller's sum over shards (the allreduce hook, one [2B] or [B] buffer per
 // iteration) can run between the local reduction and the scalar update -- the
 // scheme of pll-modules' parallel_reduce_cb (PLLMOD/optimize/pll_optimize.c:1211-1255).
-template <int C, bool LNL, bool FINAL>
+template <int C, bool LNL, bool FINAL, int STAGES = kDefaultStages>
 __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonArgs a)
 {
   constexpr int T = kSitesPerPass * C;
@@ -1270,11 +1283,11 @@ __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonAr
     const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
     const bool with_lnl = LNL && (FINAL || a.st[e].try_lnl);
     if (with_lnl)
-      sweep_chunk<C, true>(a.m, a.sumtables + (size_t)e * a.entry_stride,
+      sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                               a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
     else
-      sweep_chunk<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
+      sweep_chunk<C, false, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
                                chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
     const double s1 = block_sum<T>(out[0], red);
     const double s2 = block_sum<T>(out[1], red);
