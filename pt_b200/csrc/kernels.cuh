@@ -974,12 +974,13 @@ __device__ __forceinline__ void sweep_chunk(const ModelConst &m, const double *s
                                             double *ring, double out[3], LnlProd &lp,
                                             unsigned long long vec_end)
 {
-  if (STAGES == 0)
+  if constexpr (STAGES == 0)
   {
     for (unsigned int tile = t0; tile < t1; ++tile)
       sweep_tile<C, WITH_LNL>(m, sumtable, sclr, sites, tile, dg, out, lp, vec_end);
-    return;
   }
+  else
+  {
   constexpr int T = kSitesPerPass * C;
   const int cat = threadIdx.x % C;
   const unsigned int lsite = threadIdx.x / C;
@@ -1017,6 +1018,7 @@ __device__ __forceinline__ void sweep_chunk(const ModelConst &m, const double *s
     fill = fill + 1 == STAGES ? 0 : fill + 1;
   }
   cp_async_wait<0>();
+  }
 }
 
 struct NewtonArgs
