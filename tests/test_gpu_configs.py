@@ -186,3 +186,42 @@ def test_config4_batch_vs_oracle_and_vs_single_edge_path(oracle):
             assert abs(lnls[k] - ll) <= 1e-9 * abs(ll), (k, lnls[k], ll)
     finally:
         e.close()
+
+
+def test_few_work_ring_is_bit_identical_to_direct_loads():
+    """One branch on a long alignment (64 taxa x 300k sites: 131 chunks of 9 tiles, fewer work
+    items than SMs) takes the 6-stage cp.async ring in the Newton sweeps; PTGPU_FEW_WORK_RING=0
+    restores direct loads.  Same arithmetic in the same order: OptimizeBranch's length,
+    iteration count, the edge lnL and (d1, d2) must agree to the last bit.  (The switch is read
+    once per process, hence two child processes.)"""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, "."); sys.path.insert(0, "tests")
+from synth import FREQS, SUBST, RATES, parent_tree, simulate
+from common import make_engine
+from pt_b200.engine import ops_array
+tree = parent_tree(64, 0)
+aln = simulate(tree, 300000, np.random.default_rng(3))
+e = make_engine(tree, {k: bytes(v) for k, v in aln.items()}, FREQS, SUBST, RATES)
+ops, midx, mlen = tree.full_traversal()
+e.update_prob_matrices(midx, mlen); e.update_partials(ops_array(ops))
+r, b = tree.root, tree.root.back
+args = (r.clv_index, r.scaler_index, b.clv_index, b.scaler_index, r.pmatrix_index)
+e.update_sumtable(r.clv_index, b.clv_index, r.scaler_index, b.scaler_index)
+out = [e.derivatives(t) for t in (0.01, 0.1, 1.0)]
+ln, it = e.optimize_branch(*args, 0.3)
+print(repr((out, ln, it, e.edge_loglikelihood(*args))))
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    got = []
+    for flag in ("1", "0"):
+        env = dict(os.environ, PTGPU_FEW_WORK_RING=flag)
+        r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True,
+                           text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        got.append(r.stdout.strip().splitlines()[-1])
+    assert got[0] == got[1], got
+    assert "nan" not in got[0]
