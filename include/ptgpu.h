@@ -115,6 +115,13 @@ int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count,
                                const unsigned int *tip_indices,
                                const char *const *sequences);
 
+/* A second engine on the same alignment without a second upload: what a caller of the
+   reference gets by constructing another pll_partition_t and repeating the per-tip
+   pll_set_tip_states loop (lib/libptpll/src/pll_partition.cpp:160-199).  `dst` and `src`
+   must have the same tip and site counts and live on the same device; the encoded tip
+   states (and the pattern weights, if set) are copied device to device. */
+int ptgpu_copy_tip_states(ptgpu_engine *dst, ptgpu_engine *src);
+
 /* pll_set_pattern_weights (LIBPLL/pll.c:1047-1059): `weights` is a host array of
    `sites` multiplicities (every one >= 1: the reference's vector paths assume "no
    zero weights", LIBPLL/core_derivatives_avx.c:1123); NULL restores all-ones, the

@@ -486,6 +486,28 @@ int ptgpu_set_pattern_weights(ptgpu_engine *e, const unsigned int *weights)
   return PTGPU_OK;
 }
 
+int ptgpu_copy_tip_states(ptgpu_engine *dst, ptgpu_engine *src)
+{
+  if (!dst || !src) return fail(PTGPU_ERR_ARG, "ptgpu_copy_tip_states: null engine");
+  if (dst->tips != src->tips || dst->sites != src->sites || dst->device != src->device)
+    return fail(PTGPU_ERR_ARG, "ptgpu_copy_tip_states: engines differ in tips, sites or device");
+  CU(cudaSetDevice(dst->device));
+  CU(cudaStreamSynchronize(src->stream));
+  CU(cudaMemcpyAsync(dst->d_tips, src->d_tips, (size_t)src->tips * src->dev.tip_stride, cudaMemcpyDeviceToDevice,
+                     dst->stream));
+  if (src->model.weights)
+  {
+    if (!dst->d_weights) CU(cudaMalloc(&dst->d_weights, (size_t)dst->sites * sizeof(unsigned int)));
+    CU(cudaMemcpyAsync(dst->d_weights, src->d_weights, (size_t)src->sites * sizeof(unsigned int),
+                       cudaMemcpyDeviceToDevice, dst->stream));
+    dst->model.weights = dst->d_weights;
+  }
+  else
+    dst->model.weights = nullptr;
+  CU(cudaStreamSynchronize(dst->stream));
+  return PTGPU_OK;
+}
+
 int ptgpu_compress_site_patterns(char **sequences, unsigned int count, unsigned int *length,
                                  unsigned int *weights_out)
 {

@@ -21,8 +21,11 @@
 #ifndef PT_B200_HOST_PLL_PARTITION_HPP_
 #define PT_B200_HOST_PLL_PARTITION_HPP_
 
+#include <cstdint>
+#include <future>
 #include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <libpll/pll.h>
@@ -116,10 +119,41 @@ class Partition
   int device() const { return device_; }
   ptgpu_engine* engine() { return engine_; }
 
+  // ---- visits computed ahead of time (pt_b200/host/ptw/visit_prefetcher) ----
+  //
+  // Wanderer::MoveForward visits every move it queued: clone the tree with the move applied,
+  // OptimizeAllBranches, LogLikelihood (src/wanderer.cpp:150-210).  The result is a pure
+  // function of that tree, so it can be computed as soon as the move is queued, on another
+  // engine, while the wanderer goes on.  A Replica() is such an engine (same alignment, model
+  // and mode, tips copied on the device, no batch buffers); PublishVisit() registers the
+  // pending result of OptimizeAllBranches for the tree with the given fingerprint, and
+  // OptimizeAllBranches() of a non-replica partition takes a registered result instead of
+  // computing it: it writes the optimised lengths into the tree and marks every CLV stale, so
+  // the PARTIAL traversal + LogLikelihood the caller does next recompute CLVs and score with
+  // the same kernels on the same lengths -- bit-identical to having optimised here.
+  struct VisitResult {
+    std::vector<double> lengths;   // by node_index of every record of the tree
+  };
+  std::unique_ptr<Partition> Replica() const;
+  bool is_replica() const { return is_replica_; }
+  // order-independent hash of (node_index, back->node_index, length) over all records
+  static uint64_t TreeFingerprint(const pll_utree_t* tree);
+  static void PublishVisit(uint64_t fingerprint, std::shared_future<VisitResult> result);
+  static bool VisitKnown(uint64_t fingerprint);
+  static void ClearVisits();
+  // (visits served from the registry, visits computed here) since process start
+  static std::pair<unsigned long long, unsigned long long> VisitStatistics();
+
  private:
   int device_;
   unsigned int directional_base_;  // first extra CLV / scaler buffer (0 = none allocated)
   bool stepwise_all_branches_ = false;  // PTGPU_STEPWISE_ALL_BRANCHES: one engine call per step (A/B testing)
+  bool is_replica_ = false;
+
+  struct ReplicaTag {};
+  Partition(const Partition& proto, ReplicaTag);
+  uint64_t FingerprintFrom(pll_unode_t* root);
+  bool TakePublishedVisit(pll_unode_t* root);
 
   void SetTipStates(pll_utree_t* tree, const std::vector<std::string>& labels,
                     const std::vector<std::string>& sequences);

@@ -5,6 +5,7 @@
 #include <stdexcept>
 
 #include "authority.hpp"
+#include "visit_prefetcher.hpp"
 
 namespace pt { namespace move_tester {
 
@@ -73,7 +74,16 @@ std::pair<bool, double> BatchedNeighborhood::EvaluateMove(pll::Partition& partit
   for (const pll::Partition::NniScore& m : scores->moves) {
     if (m.node == node && m.type == static_cast<int>(type)) {
       // testing only: the score is not reported to the authority here
-      return std::make_pair(m.lnl >= authority.GetThresholdScore(), m.lnl);
+      const bool accept = m.lnl >= authority.GetThresholdScore();
+      if (accept && VisitPrefetcher::Instance().enabled()) {
+        // the wanderer will visit this move if the authority grants it (src/wanderer.cpp:262-272):
+        // start that visit now, on the tree the move leads to (applied and undone as
+        // Guru::RequestMove does, src/guru.cpp:219-244)
+        pll_utree_nni(node, static_cast<int>(type), nullptr);
+        VisitPrefetcher::Instance().Submit(partition, tree);
+        pll_utree_nni(node, static_cast<int>(type), nullptr);
+      }
+      return std::make_pair(accept, m.lnl);
     }
   }
   throw std::logic_error("move is not an NNI across an inner edge of this tree");

@@ -21,6 +21,7 @@
 #include <pll_util.hpp>
 
 #include "batched_neighborhood.hpp"
+#include "visit_prefetcher.hpp"
 #include "compressed_tree.hpp"
 #include "guru.hpp"
 #include "options.hpp"
@@ -55,6 +56,11 @@ int Run(int argc, const char* argv[])
     options.move_tester = batched;
   }
 
+  // visits of queued moves ahead of time: opt-in (PTGPU_PREFETCH_VISITS=n workers), because the
+  // scores then agree with the reference's only to the optimiser's own tolerance, not to the
+  // last printed digit (pt_b200/host/ptw/visit_prefetcher.hpp)
+  if (batched) pt::move_tester::VisitPrefetcher::Instance().Start(0);
+
   TreeSet input;
   input.trees = pt::pll::ParseMultiNewick(options.newick_path);
   if (input.trees.empty())
@@ -74,6 +80,12 @@ int Run(int argc, const char* argv[])
   DumpTable(guru.GetVisitedTreeTable(), options.visited_trees_path);
   DumpTable(guru.GetTestedTreeTable(), options.tested_trees_path);
 
+  if (pt::move_tester::VisitPrefetcher::Instance().enabled()) {
+    const auto visits = pt::pll::Partition::VisitStatistics();
+    std::fprintf(stderr, "visits ahead of time: %llu submitted, %llu taken by OptimizeAllBranches, %llu computed in place\n",
+                 pt::move_tester::VisitPrefetcher::Instance().submitted(), visits.first, visits.second);
+  }
+  pt::move_tester::VisitPrefetcher::Instance().Shutdown();   // before the partitions and the CUDA runtime go
   if (batched) {
     const auto stats = batched->Statistics();
     std::fprintf(stderr, "batched move testing: %llu moves answered from %llu engine batches\n",

@@ -14,7 +14,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <future>
 #include <map>
+#include <mutex>
+#include <unordered_map>
 #include <stdexcept>
 #include <string>
 #include <strings.h>
@@ -177,6 +180,150 @@ Partition::Partition(pll_utree_t* tree,
   AllocateScratchBuffers();
 }
 
+// ---- visits computed ahead of time (see the header) -------------------------------------
+namespace {
+
+std::mutex g_visit_mutex;
+std::unordered_map<uint64_t, std::shared_future<Partition::VisitResult>> g_visits;
+std::atomic<bool> g_visits_used{false};
+std::atomic<unsigned long long> g_visits_served{0}, g_visits_computed{0};
+
+inline uint64_t record_hash(const pll_unode_t* r)
+{
+  uint64_t bits;
+  std::memcpy(&bits, &r->length, sizeof bits);
+  uint64_t h = 0x9e3779b97f4a7c15ull * (r->node_index + 1);
+  h ^= 0xc2b2ae3d27d4eb4full * (r->back->node_index + 1) + (h << 6) + (h >> 2);
+  h ^= bits + 0x165667b19e3779f9ull + (h << 6) + (h >> 2);
+  h ^= h >> 29; h *= 0xbf58476d1ce4e5b9ull; h ^= h >> 32;
+  return h;
+}
+
+inline uint64_t node_hash(const pll_unode_t* n)
+{
+  uint64_t h = 0;
+  const pll_unode_t* r = n;
+  do {
+    h += record_hash(r);   // commutative: the order in which records are met does not matter
+    r = r->next;
+  } while (r && r != n);
+  return h;
+}
+
+} // namespace
+
+uint64_t Partition::TreeFingerprint(const pll_utree_t* tree)
+{
+  uint64_t h = 0;
+  for (unsigned int i = 0; i < tree->tip_count + tree->inner_count; ++i) h += node_hash(tree->nodes[i]);
+  return h;
+}
+
+uint64_t Partition::FingerprintFrom(pll_unode_t* root)
+{
+  unsigned int found = 0;
+  if (!pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, visit_all, travbuffer_.data(), &found))
+    return 0;
+  if (found != node_count()) return 0;
+  uint64_t h = 0;
+  for (unsigned int i = 0; i < found; ++i) h += node_hash(travbuffer_[i]);
+  return h;
+}
+
+void Partition::PublishVisit(uint64_t fingerprint, std::shared_future<VisitResult> result)
+{
+  std::lock_guard<std::mutex> lock(g_visit_mutex);
+  g_visits.emplace(fingerprint, std::move(result));
+  g_visits_used = true;
+}
+
+bool Partition::VisitKnown(uint64_t fingerprint)
+{
+  std::lock_guard<std::mutex> lock(g_visit_mutex);
+  return g_visits.count(fingerprint) != 0;
+}
+
+void Partition::ClearVisits()
+{
+  std::lock_guard<std::mutex> lock(g_visit_mutex);
+  g_visits.clear();
+}
+
+std::pair<unsigned long long, unsigned long long> Partition::VisitStatistics()
+{
+  return std::make_pair(g_visits_served.load(), g_visits_computed.load());
+}
+
+// the registered result of OptimizeAllBranches for this very tree, if there is one: lengths into
+// the tree, every CLV marked stale (the caller's next traversal recomputes them all)
+bool Partition::TakePublishedVisit(pll_unode_t* root)
+{
+  if (is_replica_ || !g_visits_used.load(std::memory_order_relaxed)) return false;
+  const uint64_t fp = FingerprintFrom(root);   // fills travbuffer_ with one record per node
+  if (!fp) return false;
+  std::shared_future<VisitResult> pending;
+  {
+    std::lock_guard<std::mutex> lock(g_visit_mutex);
+    auto it = g_visits.find(fp);
+    if (it == g_visits.end()) return false;
+    pending = it->second;
+    g_visits.erase(it);
+  }
+  VisitResult res;
+  try {
+    res = pending.get();
+  } catch (...) {
+    return false;   // the background visit failed: compute here, where the caller sees the error
+  }
+  for (unsigned int i = 0; i < node_count(); ++i) {
+    pll_unode_t* n = travbuffer_[i];
+    pll_unode_t* r = n;
+    do {
+      if (r->node_index >= res.lengths.size()) return false;
+      r = r->next;
+    } while (r && r != n);
+  }
+  for (unsigned int i = 0; i < node_count(); ++i) {
+    pll_unode_t* n = travbuffer_[i];
+    pll_unode_t* r = n;
+    do {
+      r->length = res.lengths[r->node_index];
+      if (r->next && r->data) static_cast<node_info_t*>(r->data)->clv_valid = 0;
+      r = r->next;
+    } while (r && r != n);
+  }
+  return true;
+}
+
+Partition::Partition(const Partition& proto, ReplicaTag) :
+    tip_node_count_(proto.tip_node_count_),
+    map_mode_(proto.map_mode_),
+    engine_(nullptr),
+    site_count_(proto.site_count_),
+    device_(proto.device_),
+    directional_base_(0),
+    stepwise_all_branches_(proto.stepwise_all_branches_),
+    is_replica_(true)
+{
+  Check(ptgpu_create(tip_node_count_, inner_node_count(), site_count_,
+                     static_cast<unsigned int>(proto.model_.category_rates.size()), branch_count(),
+                     inner_node_count(), device_, &engine_));
+  try {
+    SetModel(proto.model_);
+    Check(ptgpu_copy_tip_states(engine_, proto.engine_));
+  } catch (...) {
+    ptgpu_destroy(engine_);
+    engine_ = nullptr;
+    throw;
+  }
+  AllocateScratchBuffers();
+}
+
+std::unique_ptr<Partition> Partition::Replica() const
+{
+  return std::unique_ptr<Partition>(new Partition(*this, ReplicaTag{}));
+}
+
 // PTPLL/pll_partition.cpp:67-80: the engine moves, scratch is re-allocated
 Partition::Partition(Partition&& rhs) :
     tip_node_count_(rhs.tip_node_count_),
@@ -186,7 +333,8 @@ Partition::Partition(Partition&& rhs) :
     site_count_(rhs.site_count_),
     device_(rhs.device_),
     directional_base_(rhs.directional_base_),
-    stepwise_all_branches_(rhs.stepwise_all_branches_)
+    stepwise_all_branches_(rhs.stepwise_all_branches_),
+    is_replica_(rhs.is_replica_)
 {
   rhs.engine_ = nullptr;
   AllocateScratchBuffers();
@@ -388,6 +536,11 @@ void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
 void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 {
   StatScope stat(kStatAllBranches);
+  if (!use_pllmod && TakePublishedVisit(tree)) {
+    g_visits_served += 1;
+    return;
+  }
+  if (!is_replica_) g_visits_computed += 1;
   if (!use_pllmod && !stepwise_all_branches_) {
     OptimizeAllBranchesFused(tree);
     return;

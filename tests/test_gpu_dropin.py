@@ -96,3 +96,33 @@ def test_ptw_batched_tables_identical_and_faster(config):
     print(f"{config}: batched {t_batched:.2f}s, move-at-a-time {t_sequential:.2f}s")
     if config == "config2":   # config 1 is nine trees: mostly process start-up
         assert t_batched < t_sequential
+
+
+@pytest.mark.parametrize("workers", ["2", "8"])
+def test_ptw_batched_with_visits_ahead_of_time(workers, monkeypatch):
+    """BASELINE configs[1] on DS1 with the queued moves' visits computed ahead of time on 2 / 8
+    background engines (opt-in, pt_b200/host/ptw/visit_prefetcher.hpp explains why the scores
+    then match the reference's only to the optimiser's tolerance): same counts, same good /
+    visited / tested topologies, identical good_trees lines, every visited and tested score
+    within 2e-6 relative (the last of the 6 printed digits) of the reference's."""
+    from make_ptw_golden import run, summarise
+    bat = need("ptw_batched")
+    with open(os.path.join(ROOT, "tests", "golden", "ptw_golden.json")) as f:
+        gold = json.load(f)["config2"]
+    monkeypatch.setenv("PTGPU_PREFETCH_VISITS", workers)
+    tables = run(bat, gold["args"])
+    got = summarise(tables)
+    for key in ("counts", "good_topologies_sha", "visited_topologies_sha", "tested_topologies_sha", "good"):
+        assert got[key] == gold[key], key
+    monkeypatch.setenv("PTGPU_PREFETCH_VISITS", "0")
+    plain = run(bat, gold["args"])
+    assert summarise(plain)["tested_sha"] == gold["tested_sha"]
+    differing = 0
+    for name in ("visited", "tested"):
+        a = {l.split("\t", 1)[1]: float(l.split("\t", 1)[0]) for l in tables[name]}
+        b = {l.split("\t", 1)[1]: float(l.split("\t", 1)[0]) for l in plain[name]}
+        assert a.keys() == b.keys()
+        for topo, v in b.items():
+            assert abs(a[topo] - v) <= 2e-6 * abs(v), (name, topo)
+            differing += a[topo] != v
+    print(f"prefetch workers={workers}: {differing} printed scores differ in the last digit")
