@@ -329,6 +329,40 @@ int ptgpu_set_allreduce(ptgpu_engine *e, ptgpu_allreduce_fn fn, void *ctx);
 int ptgpu_set_shard(ptgpu_engine *e, unsigned long long site_offset,
                     unsigned long long global_sites);
 
+/* ---- site shards, the engines' own exchange (SURVEY.md 8b "sharded: ptgpu_comm_init",
+   8e): instead of a caller-supplied hook the kernels sum the per-tree scalars themselves,
+   over NVLink peer memory -- every shard owns a small mailbox that all shards have mapped;
+   a value is published with plain stores into every shard's mailbox and collected by
+   polling the local one; sums are formed in rank order, so every shard sees the same bits
+   and results are reproducible per shard count.  With this exchange in place the
+   step-program entry points (ptgpu_optimize_all_branches, ptgpu_optimize_local_batch) run
+   on shards as ONE persistent kernel per GPU: no launch, no host round trip and no
+   collective call between the Newton steps of a whole-tree optimisation.  It replaces what
+   a multi-partition caller of pll-modules would supply as parallel_reduce_cb
+   (PLLMOD/optimize/pll_optimize.c:1211-1212 lnL, :1249-1255 df/ddf).
+   All shards must make the same sequence of engine calls (they compute the same sums, so
+   they take the same decisions); a shard whose peer does not answer within
+   PTGPU_SHARD_TIMEOUT_MS (default 20000) fails the call with PTGPU_ERR_STATE instead of
+   hanging.  At most 8 shards.
+
+   One process drives all shards (what pt::pll::Partition does with PTGPU_SITE_SHARDS=n):
+   shards[r] becomes rank r; the engines may live on different devices (peer access is
+   enabled) or, for tests, on the same one.  Call ptgpu_set_shard on each as well. */
+int ptgpu_comm_init(ptgpu_engine *const *shards, unsigned int nshards);
+/* One process per shard (torchrun): every rank exports a handle to its mailbox
+   (a cudaIpcMemHandle_t), the ranks exchange the handles by whatever means they have
+   (e.g. torch.distributed.all_gather_object), then every rank connects with the full
+   list (handles[r] = rank r's; its own entry is ignored). */
+typedef struct ptgpu_shard_handle { unsigned char bytes[64]; } ptgpu_shard_handle_t;
+int ptgpu_shard_export(ptgpu_engine *e, ptgpu_shard_handle_t *out);
+int ptgpu_shard_connect(ptgpu_engine *e, unsigned int rank, unsigned int nranks,
+                        const ptgpu_shard_handle_t *handles);
+int ptgpu_shard_disconnect(ptgpu_engine *e);
+/* shard count (0 = not connected), the sticky time-out flag and the number of exchanges
+   completed since connect (synchronises the engine's stream) */
+int ptgpu_shard_status(ptgpu_engine *e, int *nranks_out, int *error_out,
+                       unsigned long long *exchanges_out);
+
 /* test / debug hooks: host copies of device state */
 int ptgpu_get_clv(ptgpu_engine *e, unsigned int clv_index, double *out);
 int ptgpu_set_clv(ptgpu_engine *e, unsigned int clv_index, const double *in);

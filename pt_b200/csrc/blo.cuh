@@ -105,6 +105,12 @@ struct BloArgs
   double lambda;             // MAP prior rate (procedure 1), 0 = ML
   const unsigned int *prior_slots;  // length slots whose prior terms LogLikelihood adds, in its order
   unsigned int n_prior;
+  // site shards (kernels.cuh, ShardComm): this engine holds one contiguous range of the
+  // alignment's sites; every sum over sites (d1/d2 of a Newton evaluation, an edge lnL) is
+  // formed locally in the usual fixed order and then summed over the shards in rank order,
+  // inside the kernel, over peer memory.  All shards run the same program on the same sums,
+  // so they take the same decisions and stay in lock step.  nranks <= 1: not sharded.
+  ShardComm comm;
 };
 
 // ---- loaders over the combined index spaces ---------------------------------
@@ -395,6 +401,11 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
     }
   } grid;
 
+  // exchanges are numbered; the count is uniform over the grid (one per Newton phase and
+  // per lnL phase, whether or not a CTA takes part) and carried from launch to launch
+  const bool sharded = a.comm.nranks > 1;
+  unsigned long long xq = sharded ? *(volatile unsigned long long *)a.comm.seq : 0ull;
+
   NewtonArgs na{};
   na.m = a.m;
   na.sumtables = a.sumtables;
@@ -430,6 +441,17 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
       for (unsigned int t = threadIdx.x; t < a.ntiles; t += T)
         acc = __dadd_rn(acc, __ldcg(a.tile_partials + (size_t)e * a.ntiles + t));
       acc = block_sum<T>(acc, red);
+      if (sharded)
+      {
+        // this shard's sum -> the sum over all shards (pll_optimize.c:1211-1212)
+        if (threadIdx.x == 0) shard_put(a.comm, xq, e, acc);
+        if (threadIdx.x < 32)
+        {
+          double s[1];
+          shard_collect<1>(a.comm, xq, e, s);
+          acc = s[0];
+        }
+      }
       if (threadIdx.x == 0)
       {
         // MAP: log(lambda) - lambda t per branch, added one by one in LogLikelihood's order
@@ -440,6 +462,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
         store(e, acc);
       }
     }
+    if (sharded) xq += 1;
     grid.sync();
   };
 
@@ -571,6 +594,30 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
       double *pwr = a.partials + (p & 1) * pstride;
       const NewtonState *srd = a.nst + ((p - 1) & 1) * (size_t)a.B;
       NewtonState *swr = a.nst + (p & 1) * (size_t)a.B;
+      if (sharded)
+      {
+        // Site shards: the (d1, d2) sums of evaluation p-1 over THIS shard's chunks go out to
+        // all shards (pll_optimize.c:1249-1255), one publishing CTA per candidate, before any
+        // CTA of this grid starts to wait for a sum -- publishing never waits, so the order
+        // in which CTAs reach their work items cannot close a cycle.
+        for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
+        {
+          if (__syncthreads_or(threadIdx.x == 0 && __ldcg(a.fin + e) >= epoch)) continue;
+          double a1 = 0.0, a2 = 0.0;
+          for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+          {
+            a1 = __dadd_rn(a1, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 0));
+            a2 = __dadd_rn(a2, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 1));
+          }
+          a1 = block_sum<T>(a1, red);
+          a2 = block_sum<T>(a2, red);
+          if (threadIdx.x == 0)
+          {
+            shard_put(a.comm, xq, 2 * e, a1);
+            shard_put(a.comm, xq, 2 * e + 1, a2);
+          }
+        }
+      }
       for (unsigned int w = blockIdx.x; w < a.B * a.nchunks; w += gridDim.x)
       {
         const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
@@ -579,13 +626,27 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
         // (the mark may be written while we look: one thread reads, the CTA follows it)
         if (__syncthreads_or(threadIdx.x == 0 && __ldcg(a.fin + e) >= epoch)) continue;
         double a1 = 0.0, a2 = 0.0;
-        for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+        if (sharded)
         {
-          a1 = __dadd_rn(a1, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 0));
-          a2 = __dadd_rn(a2, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 1));
+          // the sums over all shards, in rank order (same bits on every shard and in every CTA)
+          if (threadIdx.x < 32)
+          {
+            double s[2];
+            shard_collect<2>(a.comm, xq, 2 * e, s);
+            a1 = s[0];
+            a2 = s[1];
+          }
         }
-        a1 = block_sum<T>(a1, red);
-        a2 = block_sum<T>(a2, red);
+        else
+        {
+          for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+          {
+            a1 = __dadd_rn(a1, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 0));
+            a2 = __dadd_rn(a2, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 1));
+          }
+          a1 = block_sum<T>(a1, red);
+          a2 = block_sum<T>(a2, red);
+        }
         NewtonState ns;
         if (threadIdx.x == 0)
         {
@@ -639,6 +700,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
           pwr[(size_t)w * 3 + 1] = s2;
         }
       }
+      if (sharded) xq += 1;
       grid.sync();
       int running = 0;
       for (unsigned int e = threadIdx.x; e < a.B; e += T) running |= __ldcg(a.fin + e) < epoch;
@@ -710,6 +772,9 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
     }
     if (round + 1 >= (int)a.smoothings) finishing = true;
   }
+  // every CTA has read the sequence number long ago (grid barriers since); the next launch on
+  // this stream continues the numbering
+  if (sharded && blockIdx.x == 0 && threadIdx.x == 0) *a.comm.seq = xq;
 }
 
 } // namespace ptgpu

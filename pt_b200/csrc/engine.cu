@@ -59,6 +59,14 @@ struct Staging
   unsigned char *host = nullptr;
   unsigned char *dev = nullptr;
 };
+// every staged scalar object has its own slot in the first 4 KiB
+constexpr size_t kStgResult = 0;      // one double (edge lnL)
+constexpr size_t kStgBad = 192;       // first illegal tip character
+constexpr size_t kStgNewton = 256;    // one NewtonState
+constexpr size_t kStgActive = 448;    // two counters of the split-phase Newton loop
+constexpr size_t kStgMatrixIdx = 480; // one matrix index going up
+constexpr size_t kStgShardErr = 512;  // sticky error flag of the shard exchange (written by kernels)
+static_assert(sizeof(ptgpu::NewtonState) <= kStgActive - kStgNewton, "staging slot too small");
 
 } // namespace
 
@@ -107,7 +115,7 @@ struct ptgpu_engine
   size_t ops_cap = 0;
   unsigned int *d_midx = nullptr;
   double *d_mlen = nullptr;
-  size_t mcap = 0;
+  size_t midx_cap = 0, mlen_cap = 0;
   Staging stg;
   // pinned host arena for the descriptor uploads / result downloads of the batch entry points
   // (grown on demand): a copy to or from PAGEABLE memory goes through the driver's shared
@@ -125,6 +133,12 @@ struct ptgpu_engine
   unsigned long long vec_end = ~0ull;
   double *d_red = nullptr;          // [2 * red_cap] per-branch sums handed to the hook
   size_t red_cap = 0;
+  // native exchange between site shards (ptgpu_comm_init / ptgpu_shard_connect): the kernels sum
+  // per-tree scalars over peer-mapped mailboxes themselves (kernels.cuh, ShardComm)
+  ShardComm comm{};
+  unsigned long long *d_mailbox = nullptr;   // this shard's mailbox (peers write into it)
+  unsigned long long *d_seq = nullptr;
+  void *ipc_open[kMaxShards] = {};           // peers' mailboxes opened from IPC handles
   unsigned int *d_active = nullptr;
   unsigned long long counters[4] = {0, 0, 0, 0};
   unsigned long long lnl_sweeps = 0, final_sweeps = 0;
@@ -376,6 +390,9 @@ void ptgpu_destroy(ptgpu_engine *e)
   if (e->counted) g_live_engines[e->device & 63].fetch_sub(1);
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  for (void *p : e->ipc_open)
+    if (p) cudaIpcCloseMemHandle(p);
+  cudaFree(e->d_mailbox); cudaFree(e->d_seq);
   cudaFree(e->d_raw_all); cudaFree(e->d_tip_of); cudaFree(e->d_bad); cudaFree(e->d_weights);
   cudaFree(e->d_tips); cudaFree(e->d_raw); cudaFree(e->dev.clv); cudaFree(e->dev.scalers); cudaFree(e->dev.pmat);
   cudaFree(e->d_sumtable); cudaFree(e->d_persite); cudaFree(e->d_partials); cudaFree(e->d_counter);
@@ -439,8 +456,8 @@ int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *se
   if (!e->d_raw) CU(cudaMalloc(&e->d_raw, e->sites));
   // the characters are encoded on the device: one H2D copy of the raw bytes
   // (asynchronous when the caller's buffer is pinned) and one byte-map kernel
-  unsigned int *bad_h = (unsigned int *)(e->stg.host + 192);
-  unsigned int *bad_d = (unsigned int *)(e->stg.dev + 192);
+  unsigned int *bad_h = (unsigned int *)(e->stg.host + kStgBad);
+  unsigned int *bad_d = (unsigned int *)(e->stg.dev + kStgBad);
   CU(cudaStreamSynchronize(e->stream));
   *bad_h = 0xffffffffu;
   CU(cudaMemcpyAsync(e->d_raw, sequence, e->sites, cudaMemcpyHostToDevice, e->stream));
@@ -595,7 +612,7 @@ int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count, const unsign
   }
   if (!e->d_tip_of) CU(cudaMalloc(&e->d_tip_of, e->tips * sizeof(unsigned int)));
   if (!e->d_bad) CU(cudaMalloc(&e->d_bad, sizeof(unsigned long long)));
-  unsigned long long *bad_h = (unsigned long long *)(e->stg.host + 192);
+  unsigned long long *bad_h = (unsigned long long *)(e->stg.host + kStgBad);
   unsigned long long *bad_d = e->d_bad;
   CU(cudaStreamSynchronize(e->stream));
   CU(cudaMemsetAsync(bad_d, 0xff, sizeof(unsigned long long), e->stream));
@@ -636,7 +653,7 @@ int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count, const unsign
 namespace {
 
 // staging layout: [0, 4096) scalar results written by kernels through the
-// mapped pointer; [4096, 1 MiB) small uploads (ops, matrix lists, candidates)
+// mapped pointer (slots: kStg* above); [4096, 1 MiB) small uploads (ops, matrix lists, candidates)
 constexpr size_t kUploadOff = 4096;
 
 template <typename T>
@@ -745,11 +762,35 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   return PTGPU_OK;
 }
 
-// sum `count` doubles at `buf` (device) over all shards through the caller's hook
+// this engine holds a site shard: its sums over sites are partial sums
+inline bool is_sharded(const ptgpu_engine *e) { return e->allreduce != nullptr || e->comm.nranks > 1; }
+
+// sum `count` doubles at `buf` (device) over all shards: through the caller's hook if one is
+// set, else through the engines' own peer-memory exchange (one single-CTA kernel on the stream)
 int shard_sum(ptgpu_engine *e, double *buf, size_t count)
 {
-  const int rc = e->allreduce(e->allreduce_ctx, buf, count, (void *)e->stream);
-  if (rc != 0) return fail(PTGPU_ERR_STATE, "allreduce hook failed with code %d", rc);
+  if (e->allreduce)
+  {
+    const int rc = e->allreduce(e->allreduce_ctx, buf, count, (void *)e->stream);
+    if (rc != 0) return fail(PTGPU_ERR_STATE, "allreduce hook failed with code %d", rc);
+    return PTGPU_OK;
+  }
+  for (size_t off = 0; off < count; off += kShardSlots)
+  {
+    const unsigned int n = (unsigned int)std::min<size_t>(kShardSlots, count - off);
+    e->counters[0]++;
+    shard_allreduce_kernel<<<1, 256, 0, e->stream>>>(e->comm, buf + off, n);
+  }
+  CU(cudaGetLastError());
+  return PTGPU_OK;
+}
+
+// after a stream synchronisation: did an exchange between the shards time out?
+int shard_check(ptgpu_engine *e)
+{
+  if (e->comm.nranks > 1 && *(volatile int *)(e->stg.host + kStgShardErr))
+    return fail(PTGPU_ERR_STATE, "site shards: a peer shard did not answer within %llu ms (rank %d of %d)",
+                e->comm.timeout_ns / 1000000ull, e->comm.rank, e->comm.nranks);
   return PTGPU_OK;
 }
 
@@ -766,7 +807,7 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
   const unsigned int grid = std::min(work, (unsigned int)e->sm_count * 8u);
   constexpr int FS = few_work_stages<C>();
   const bool deep = few_long_items(e, work, a.chunk_tiles);
-  volatile unsigned int *active_h = (volatile unsigned int *)(e->stg.host + 256);
+  volatile unsigned int *active_h = (volatile unsigned int *)(e->stg.host + kStgActive);
   unsigned int pending_lnl = 0;
   for (unsigned int it = 0; it < a.max_iter; ++it)
   {
@@ -815,7 +856,7 @@ int run_newton(ptgpu_engine *e, NewtonArgs &a)
 {
   a.vec_end = e->vec_end;
   a.lnl_margin = e->lnl_margin;
-  if (e->allreduce) { DISPATCH_CATS(e, return newton_split<C>(e, a)); }
+  if (is_sharded(e)) { DISPATCH_CATS(e, return newton_split<C>(e, a)); }
   DISPATCH_CATS(e, return launch_newton<C>(e, a));
   return PTGPU_OK;
 }
@@ -840,9 +881,8 @@ int ptgpu_update_prob_matrices(ptgpu_engine *e, const unsigned int *matrix_indic
   }
   CU(cudaSetDevice(e->device));
   int rc;
-  size_t cap2 = e->mcap;
-  if ((rc = ensure(&e->d_midx, &e->mcap, count))) return rc;
-  if ((rc = ensure(&e->d_mlen, &cap2, count))) return rc;
+  if ((rc = ensure(&e->d_midx, &e->midx_cap, count))) return rc;
+  if ((rc = ensure(&e->d_mlen, &e->mlen_cap, count))) return rc;
   if ((rc = upload(e, e->d_midx, matrix_indices, count * sizeof(unsigned int)))) return rc;
   if ((rc = upload(e, e->d_mlen, branch_lengths, count * sizeof(double)))) return rc;
   DISPATCH_CATS(e, rc = launch_pmatrix<C>(e, e->d_midx, e->d_mlen, count));
@@ -891,8 +931,8 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
     if (!e->d_persite) CU(cudaMalloc(&e->d_persite, (size_t)e->sites * sizeof(double)));
     d_persite = e->d_persite;
   }
-  double *result = (double *)e->stg.dev;
-  if (e->allreduce)
+  double *result = (double *)(e->stg.dev + kStgResult);
+  if (is_sharded(e))
   {
     if ((rc = ensure(&e->d_red, &e->red_cap, 2))) return rc;
     result = e->d_red;  // shard partial stays on the device for the hook
@@ -907,14 +947,14 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
   if (persite_lnl)
     CU(cudaMemcpyAsync(persite_lnl, d_persite, (size_t)e->sites * sizeof(double),
                        cudaMemcpyDeviceToHost, e->stream));
-  if (e->allreduce)
+  if (is_sharded(e))
   {
     if ((rc = shard_sum(e, e->d_red, 1))) return rc;
-    CU(cudaMemcpyAsync(e->stg.host, e->d_red, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(e->stg.host + kStgResult, e->d_red, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   }
   CU(cudaStreamSynchronize(e->stream));
-  *lnl_out = *(volatile double *)e->stg.host;
-  return PTGPU_OK;
+  *lnl_out = *(volatile double *)(e->stg.host + kStgResult);
+  return shard_check(e);
 }
 
 int ptgpu_update_sumtable(ptgpu_engine *e, unsigned int parent_clv_index,
@@ -969,7 +1009,7 @@ int ptgpu_compute_likelihood_derivatives(ptgpu_engine *e, double branch_length, 
   CU(cudaSetDevice(e->device));
   int rc;
   if ((rc = newton_single(e, branch_length, 1, 0.0, 0.0, nullptr))) return rc;
-  NewtonState *hs = (NewtonState *)(e->stg.host + 64);
+  NewtonState *hs = (NewtonState *)(e->stg.host + kStgNewton);
   CU(cudaMemcpyAsync(hs, e->d_state, sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   *d_f = hs->d1;
@@ -992,11 +1032,11 @@ int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
   if ((rc = newton_single(e, length0, max_iter, epsilon, map_lambda, nullptr))) return rc;
   // UpdateBranchLength (PTPLL/pll_partition.cpp:395-406): the edge's P matrix at
   // the new length, straight from the device-resident state
-  *(unsigned int *)(e->stg.host + 128) = matrix_index;
-  CU(cudaMemcpyAsync(e->d_idx1, e->stg.host + 128, sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
+  *(unsigned int *)(e->stg.host + kStgMatrixIdx) = matrix_index;
+  CU(cudaMemcpyAsync(e->d_idx1, e->stg.host + kStgMatrixIdx, sizeof(unsigned int), cudaMemcpyHostToDevice, e->stream));
   DISPATCH_CATS(e, rc = launch_pmatrix<C>(e, e->d_idx1, &e->d_state->len, 1));
   if (rc) return rc;
-  NewtonState *hs = (NewtonState *)(e->stg.host + 64);
+  NewtonState *hs = (NewtonState *)(e->stg.host + kStgNewton);
   CU(cudaMemcpyAsync(hs, e->d_state, sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   *length_out = hs->len;
@@ -1025,7 +1065,7 @@ int ptgpu_optimize_branch_bounded(ptgpu_engine *e, unsigned int parent_clv_index
   if (rts < xmin) rts = xmin;
   if (rts > xmax) rts = xmax;
   if ((rc = newton_single(e, rts, max_iter, tolerance, 0.0, nullptr, 1, xmin, xmax))) return rc;
-  NewtonState *hs = (NewtonState *)(e->stg.host + 64);
+  NewtonState *hs = (NewtonState *)(e->stg.host + kStgNewton);
   CU(cudaMemcpyAsync(hs, e->d_state, sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   *length_out = hs->len;
@@ -1065,6 +1105,9 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     const size_t have = e->bcap * per_cand;
     const size_t budget = std::max(have, (size_t)((free_b + have) * 0.8));
     chunk = std::min<size_t>(count, std::max<size_t>(1, budget / per_cand));
+    // all shards must cut a batch into the same launches; free memory may differ between them
+    if (is_sharded(e) && chunk < count)
+      return fail(PTGPU_ERR_STATE, "site shards: a batch of %u candidates does not fit this shard's memory", count);
   }
   if (chunk > e->bcap)
   {
@@ -1332,6 +1375,145 @@ int ptgpu_synchronize(ptgpu_engine *e)
 
 } // extern "C"
 
+
+// ---- the engines' own exchange between site shards (kernels.cuh, ShardComm) --------------
+namespace {
+
+int shard_alloc(ptgpu_engine *e)
+{
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamSynchronize(e->stream));
+  if (!e->d_mailbox) CU(cudaMalloc(&e->d_mailbox, shard_mailbox_bytes()));
+  if (!e->d_seq) CU(cudaMalloc(&e->d_seq, sizeof(unsigned long long)));
+  CU(cudaMemset(e->d_mailbox, 0, shard_mailbox_bytes()));
+  CU(cudaMemset(e->d_seq, 0, sizeof(unsigned long long)));
+  *(volatile int *)(e->stg.host + kStgShardErr) = 0;
+  CU(cudaDeviceSynchronize());
+  return PTGPU_OK;
+}
+
+void shard_fill(ptgpu_engine *e, unsigned int rank, unsigned int nranks)
+{
+  e->comm.rank = (int)rank;
+  e->comm.nranks = (int)nranks;
+  e->comm.seq = e->d_seq;
+  e->comm.error = (int *)(e->stg.dev + kStgShardErr);
+  unsigned long long ms = 20000;
+  if (const char *v = getenv("PTGPU_SHARD_TIMEOUT_MS")) ms = std::max(1ull, strtoull(v, nullptr, 10));
+  e->comm.timeout_ns = ms * 1000000ull;
+}
+
+void shard_close(ptgpu_engine *e)
+{
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (void *&p : e->ipc_open)
+    if (p) { cudaIpcCloseMemHandle(p); p = nullptr; }
+  e->comm = ShardComm{};
+}
+
+} // namespace
+
+extern "C" {
+
+int ptgpu_shard_export(ptgpu_engine *e, ptgpu_shard_handle_t *out)
+{
+  if (!e || !out) return fail(PTGPU_ERR_ARG, "ptgpu_shard_export: null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(ptgpu_shard_handle_t), "handle size");
+  shard_close(e);
+  int rc;
+  if ((rc = shard_alloc(e))) return rc;
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, e->d_mailbox));
+  memset(out, 0, sizeof *out);
+  memcpy(out->bytes, &h, sizeof h);
+  return PTGPU_OK;
+}
+
+int ptgpu_shard_connect(ptgpu_engine *e, unsigned int rank, unsigned int nranks,
+                        const ptgpu_shard_handle_t *handles)
+{
+  if (!e || !handles) return fail(PTGPU_ERR_ARG, "ptgpu_shard_connect: null argument");
+  if (nranks < 1 || nranks > (unsigned int)kMaxShards || rank >= nranks)
+    return fail(PTGPU_ERR_ARG, "ptgpu_shard_connect: rank %u of %u (at most %d shards)", rank, nranks, kMaxShards);
+  if (!e->d_mailbox) return fail(PTGPU_ERR_STATE, "ptgpu_shard_connect: call ptgpu_shard_export first");
+  if (e->allreduce) return fail(PTGPU_ERR_STATE, "ptgpu_shard_connect: an allreduce hook is set");
+  CU(cudaSetDevice(e->device));
+  for (unsigned int r = 0; r < nranks; ++r)
+  {
+    if (r == rank) { e->comm.box[r] = e->d_mailbox; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handles[r].bytes, sizeof h);
+    void *p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    e->ipc_open[r] = p;
+    e->comm.box[r] = (unsigned long long *)p;
+  }
+  shard_fill(e, rank, nranks);
+  return PTGPU_OK;
+}
+
+int ptgpu_comm_init(ptgpu_engine *const *shards, unsigned int nshards)
+{
+  if (!shards || nshards < 1 || nshards > (unsigned int)kMaxShards)
+    return fail(PTGPU_ERR_ARG, "ptgpu_comm_init: 1 to %d shards", kMaxShards);
+  int rc;
+  for (unsigned int r = 0; r < nshards; ++r)
+  {
+    if (!shards[r]) return fail(PTGPU_ERR_ARG, "ptgpu_comm_init: shard %u is null", r);
+    if (shards[r]->allreduce) return fail(PTGPU_ERR_STATE, "ptgpu_comm_init: shard %u has an allreduce hook", r);
+    for (unsigned int k = 0; k < r; ++k)
+      if (shards[k] == shards[r]) return fail(PTGPU_ERR_ARG, "ptgpu_comm_init: shard %u listed twice", r);
+    shard_close(shards[r]);
+    if ((rc = shard_alloc(shards[r]))) return rc;
+  }
+  // every device maps every other one (NVLink / NVSwitch peer access)
+  for (unsigned int a = 0; a < nshards; ++a)
+    for (unsigned int b = 0; b < nshards; ++b)
+    {
+      const int da = shards[a]->device, db = shards[b]->device;
+      if (da == db) continue;
+      int can = 0;
+      CU(cudaDeviceCanAccessPeer(&can, da, db));
+      if (!can) return fail(PTGPU_ERR_CUDA, "ptgpu_comm_init: device %d cannot access device %d", da, db);
+      CU(cudaSetDevice(da));
+      const cudaError_t err = cudaDeviceEnablePeerAccess(db, 0);
+      if (err == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+      else if (err != cudaSuccess)
+        return fail(PTGPU_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", da, db, cudaGetErrorString(err));
+    }
+  for (unsigned int a = 0; a < nshards; ++a)
+  {
+    for (unsigned int b = 0; b < nshards; ++b) shards[a]->comm.box[b] = shards[b]->d_mailbox;
+    shard_fill(shards[a], a, nshards);
+  }
+  return PTGPU_OK;
+}
+
+int ptgpu_shard_disconnect(ptgpu_engine *e)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_shard_disconnect: null engine");
+  shard_close(e);
+  return PTGPU_OK;
+}
+
+int ptgpu_shard_status(ptgpu_engine *e, int *nranks_out, int *error_out, unsigned long long *exchanges_out)
+{
+  if (!e) return fail(PTGPU_ERR_ARG, "ptgpu_shard_status: null engine");
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamSynchronize(e->stream));
+  if (nranks_out) *nranks_out = e->comm.nranks;
+  if (error_out) *error_out = *(volatile int *)(e->stg.host + kStgShardErr);
+  if (exchanges_out)
+  {
+    *exchanges_out = 0;
+    if (e->d_seq) CU(cudaMemcpy(exchanges_out, e->d_seq, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  }
+  return PTGPU_OK;
+}
+
+} // extern "C"
+
 namespace {
 
 constexpr unsigned int kBloCluster = 8;   // CTAs of the single-cluster variant (portable maximum)
@@ -1480,7 +1662,13 @@ int blo_validate(ptgpu_engine *e, const BloRequest &r)
 int run_blo(ptgpu_engine *e, const BloRequest &r)
 {
   int rc;
-  if (e->allreduce) return fail(PTGPU_ERR_STATE, "step programs are not available on a site shard");
+  // site shards: the kernel sums over the shards itself (peer memory); a caller-supplied hook
+  // cannot be called from inside a kernel
+  if (e->allreduce)
+    return fail(PTGPU_ERR_STATE, "step programs on a site shard need the engines' own exchange "
+                                 "(ptgpu_comm_init / ptgpu_shard_connect), not an allreduce hook");
+  if (e->comm.nranks > 1 && (size_t)r.count * 2 > kShardSlots)
+    return fail(PTGPU_ERR_ARG, "site shards: at most %u candidates per step program", kShardSlots / 2);
   if ((rc = blo_validate(e, r))) return rc;
   CU(cudaSetDevice(e->device));
   if ((rc = blo_prepare_kernel(e))) return rc;
@@ -1507,7 +1695,12 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
     const size_t have = e->lcap_cand * ((size_t)e->lcap_clvs * clv_bytes + stride * sizeof(double));
-    chunk = std::min<size_t>(chunk, std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand));
+    const size_t can = std::max<size_t>(1, (size_t)((free_b + have) * 0.8) / per_cand);
+    // all shards must cut a batch into the same launches; free memory may differ between them
+    if (e->comm.nranks > 1 && can < chunk)
+      return fail(PTGPU_ERR_STATE, "site shards: a batch of %zu candidates does not fit this shard's memory "
+                                   "(set PTGPU_BLO_MAX_CHUNK to the same value on every shard)", chunk);
+    chunk = std::min<size_t>(chunk, can);
   }
   if (!fits && (chunk > e->lcap_cand || npriv > e->lcap_clvs || nlen > e->lcap_lens))
   {
@@ -1619,6 +1812,7 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     a.vec_end = e->vec_end;
     a.procedure = r.procedure; a.lambda = r.lambda;
     a.prior_slots = e->d_lprior; a.n_prior = r.n_prior;
+    a.comm = e->comm;
     const unsigned int work = std::max(1u, nb * e->ntiles);
     const unsigned int grid = std::min(work, coop_grid_share(e, (unsigned int)(e->blo_blocks_per_sm * e->sm_count)));
     // a program whose phases are a couple of tiles per CTA is all barriers: one cluster
@@ -1634,6 +1828,7 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
     CU(cudaMemcpyAsync(hcand, e->d_lcand, nb * sizeof(BloCand), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaMemcpyAsync(hlens, e->d_llens, nlens * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    if ((rc = shard_check(e))) return rc;
     for (unsigned int i = 0; i < nb; ++i)
     {
       r.lnl_out[base + i] = hcand[i].final_lnl;

@@ -118,6 +118,107 @@ struct NewtonState
   int final_sweeps;
 };
 
+// ---------------------------------------------------------------- site shards
+// The only exchange between the GPUs that hold the site shards of one alignment is the sum
+// of per-tree scalars: 1 double per edge log-likelihood, 2 (d1, d2) per Newton step -- the
+// shape of pll-modules' parallel_reduce_cb hooks (PLLMOD/optimize/pll_optimize.c:1211-1212,
+// :1249-1255).  It is done INSIDE the kernels over NVLink peer memory: every rank owns a
+// mailbox that all ranks have mapped; a value is published by storing it into every rank's
+// mailbox and collected by polling the local one.  Each double travels as two 8-byte words
+// {32 data bits, 32-bit sequence flag} (8-byte stores are single-copy atomic, so a word is
+// valid exactly when it carries the flag of the exchange the reader waits for): no fence, no
+// ordering between words, no host, no NCCL call.  Sums are formed in RANK ORDER by every
+// reader, so all ranks get the same bits and results are reproducible per shard count.
+// Slots alternate between two halves by exchange parity; a rank publishes exchange q+1 only
+// after all its readers of exchange q have passed a grid barrier (or a kernel boundary), and
+// a peer can publish q+2 only after it has collected this rank's q+1 -- nobody overwrites a
+// word that is still being waited for.
+constexpr int kMaxShards = 8;
+constexpr unsigned int kShardSlots = 4096;   // doubles per (parity, source rank)
+
+struct ShardComm
+{
+  int rank, nranks;                      // nranks <= 1: not sharded
+  unsigned long long *box[kMaxShards];   // box[r]: rank r's mailbox as mapped here, [2][nranks][kShardSlots][2] words
+  unsigned long long *seq;               // this device: exchanges completed so far (same on all ranks)
+  int *error;                            // this device: sticky; a peer did not answer within timeout_ns
+  unsigned long long timeout_ns;
+};
+
+constexpr size_t shard_mailbox_bytes() { return (size_t)2 * kMaxShards * kShardSlots * 2 * sizeof(unsigned long long); }
+
+__device__ __forceinline__ unsigned long long shard_flag(unsigned long long q)
+{
+  return q % 0xffffffffull + 1ull;   // never 0: a zeroed mailbox matches no exchange
+}
+
+__device__ __forceinline__ unsigned long long global_timer_ns()
+{
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// publish value `slot` of exchange q to every rank (own mailbox included)
+__device__ __forceinline__ void shard_put(const ShardComm &c, unsigned long long q, unsigned int slot, double v)
+{
+  const unsigned long long bits = (unsigned long long)__double_as_longlong(v), f = shard_flag(q);
+  const unsigned long long w0 = (bits << 32) | f, w1 = (bits & 0xffffffff00000000ull) | f;
+  const size_t off = (((q & 1ull) * (size_t)c.nranks + (size_t)c.rank) * kShardSlots + slot) * 2;
+  for (int d = 0; d < c.nranks; ++d)
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(c.box[d] + off), "l"(w0), "l"(w1) : "memory");
+}
+
+// value `slot` of exchange q as published by rank `src` (spins until it has arrived; NaN and
+// the sticky error flag if it does not within the timeout, so that a dead peer ends the
+// kernel with "derivative not finite" instead of hanging the device)
+__device__ __forceinline__ double shard_get(const ShardComm &c, unsigned long long q, unsigned int slot, int src)
+{
+  const unsigned long long f = shard_flag(q);
+  const unsigned long long *p =
+      c.box[c.rank] + (((q & 1ull) * (size_t)c.nranks + (size_t)src) * kShardSlots + slot) * 2;
+  unsigned long long w0, w1, t0 = 0;
+  unsigned int spins = 0;
+  for (;;)
+  {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+    if ((w0 & 0xffffffffull) == f && (w1 & 0xffffffffull) == f) break;
+    if ((++spins & 0xffu) == 0)
+    {
+      if (*(volatile int *)c.error) return __longlong_as_double(0x7ff8000000000000ll);
+      const unsigned long long now = global_timer_ns();
+      if (!t0) t0 = now;
+      else if (now - t0 > c.timeout_ns)
+      {
+        *(volatile int *)c.error = 1;
+        return __longlong_as_double(0x7ff8000000000000ll);
+      }
+    }
+  }
+  return __longlong_as_double((long long)((w0 >> 32) | (w1 & 0xffffffff00000000ull)));
+}
+
+// Sums over ranks of values slot0 .. slot0+NV-1 of exchange q, in rank order.  Called by all
+// 32 lanes of one (converged) warp: lane r waits for rank r's words, so the polls overlap;
+// every lane returns the same sums.
+template <int NV>
+__device__ __forceinline__ void shard_collect(const ShardComm &c, unsigned long long q, unsigned int slot0,
+                                              double (&out)[NV])
+{
+  const int lane = threadIdx.x & 31;
+  double mine[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) mine[v] = lane < c.nranks ? shard_get(c, q, slot0 + v, lane) : 0.0;
+  __syncwarp();
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+  {
+    double acc = __shfl_sync(0xffffffffu, mine[v], 0);
+    for (int r = 1; r < c.nranks; ++r) acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, mine[v], r));
+    out[v] = acc;
+  }
+}
+
 // ---------------------------------------------------------------- helpers
 
 #define PT_SCALE_FACTOR 1.157920892373161954235709850086879078532699846656405640394575840079131296399360e77 /* 2^256 */
@@ -1343,6 +1444,23 @@ __global__ void newton_store_lnl_kernel(NewtonArgs a, const double *shard)
     a.st[e].lnl = shard[(size_t)e * 3 + 2];
     a.st[e].lnl_valid = 1;
   }
+}
+
+// Sum of `count` doubles at `buf` over all site shards, in place, on the engine's stream: the
+// exchange of the single-purpose entry points (one launch of one CTA; the persistent
+// step-program kernel does the same exchange inline).  count <= kShardSlots.
+__global__ void __launch_bounds__(256) shard_allreduce_kernel(ShardComm c, double *buf, unsigned int count)
+{
+  const unsigned long long q = *(volatile unsigned long long *)c.seq;
+  for (unsigned int i = threadIdx.x; i < count; i += blockDim.x) shard_put(c, q, i, buf[i]);
+  for (unsigned int i = threadIdx.x; i < count; i += blockDim.x)
+  {
+    double acc = shard_get(c, q, i, 0);
+    for (int r = 1; r < c.nranks; ++r) acc = __dadd_rn(acc, shard_get(c, q, i, r));
+    buf[i] = acc;
+  }
+  __syncthreads();   // everybody has read the sequence number and collected its values
+  if (threadIdx.x == 0) *c.seq = q + 1;
 }
 
 // edge log-likelihood of a shard: tile partials -> one double in device memory

@@ -65,6 +65,27 @@ def _d(a):
     return a.ctypes.data_as(_dp)
 
 
+def comm_init(engines):
+    """ptgpu_comm_init: the Engines of ONE process become the site shards 0..n-1 of one
+    alignment (same device or peer-accessible devices); call set_shard on each as well"""
+    L = load_library()
+    arr = (C.c_void_p * len(engines))(*[e.h for e in engines])
+    rc = L.ptgpu_comm_init(arr, C.c_uint(len(engines)))
+    if rc != PTGPU_OK:
+        raise PtGpuError(rc, L.ptgpu_last_error().decode())
+
+
+def gamma_rates_mean(alpha, cats):
+    """ptgpu_gamma_rates_mean = pll_compute_gamma_cats(alpha, cats, PLL_GAMMA_RATES_MEAN):
+    host-only, needs no device"""
+    L = load_library()
+    out = np.empty(cats)
+    rc = L.ptgpu_gamma_rates_mean(C.c_double(alpha), C.c_uint(cats), _d(out))
+    if rc != PTGPU_OK:
+        raise PtGpuError(rc, L.ptgpu_last_error().decode())
+    return out
+
+
 def ops_array(rows):
     """list of 8-int rows (pll_operation_t field order) -> structured array"""
     a = np.asarray(rows, dtype=np.int64).reshape(-1, 8)
@@ -307,6 +328,29 @@ class Engine:
         self._hook = fn
         self._chk(self.lib.ptgpu_set_allreduce(
             self.h, C.cast(fn, C.c_void_p) if fn is not None else None, None))
+
+    # the engines' own exchange over peer memory (no hook, no NCCL call): see include/ptgpu.h
+    def shard_export(self):
+        """64-byte handle of this shard's mailbox, to be sent to the other ranks"""
+        buf = (C.c_ubyte * 64)()
+        self._chk(self.lib.ptgpu_shard_export(self.h, buf))
+        return bytes(buf)
+
+    def shard_connect(self, rank, handles):
+        """handles[r] = rank r's shard_export() (own entry ignored)"""
+        blob = b"".join(bytes(h) for h in handles)
+        assert len(blob) == 64 * len(handles)
+        arr = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        self._chk(self.lib.ptgpu_shard_connect(self.h, C.c_uint(rank), C.c_uint(len(handles)), arr))
+
+    def shard_disconnect(self):
+        self._chk(self.lib.ptgpu_shard_disconnect(self.h))
+
+    def shard_status(self):
+        """(shard count, sticky time-out flag, exchanges completed)"""
+        n = C.c_int(); err = C.c_int(); ex = C.c_ulonglong()
+        self._chk(self.lib.ptgpu_shard_status(self.h, C.byref(n), C.byref(err), C.byref(ex)))
+        return n.value, err.value, ex.value
 
     def synchronize(self):
         self._chk(self.lib.ptgpu_synchronize(self.h))

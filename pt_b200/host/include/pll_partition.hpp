@@ -18,10 +18,19 @@
 // re-entrant per object.  Each Partition owns one engine = one CUDA stream on
 // one device; devices are assigned round-robin over the visible GPUs
 // (wanderer-parallel) unless PTGPU_DEVICE pins one.
+//
+// Site shards (BASELINE configs[2]): with PTGPU_SITE_SHARDS=n (n <= 8) a
+// Partition holds n engines, each with a contiguous, tile-aligned range of the alignment's
+// sites, on n consecutive devices (wrapping round when there are fewer).  The public surface is
+// unchanged: every method issues the same engine call on all shards at once (one host thread
+// per shard), the engines sum the per-tree scalars among themselves over NVLink peer memory
+// (ptgpu_comm_init), and all shards return the same numbers.  OptimizeAllBranches is then ONE
+// persistent kernel per GPU with no host round trip inside a pass.
 #ifndef PT_B200_HOST_PLL_PARTITION_HPP_
 #define PT_B200_HOST_PLL_PARTITION_HPP_
 
 #include <cstdint>
+#include <functional>
 #include <future>
 #include <memory>
 #include <string>
@@ -118,6 +127,8 @@ class Partition
 
   int device() const { return device_; }
   ptgpu_engine* engine() { return engine_; }
+  // site shards of this partition (1 unless PTGPU_SITE_SHARDS asked for more)
+  unsigned int shard_count() const { return static_cast<unsigned int>(shards_.size()); }
 
   // ---- visits computed ahead of time (pt_b200/host/ptw/visit_prefetcher) ----
   //
@@ -149,6 +160,19 @@ class Partition
   unsigned int directional_base_;  // first extra CLV / scaler buffer (0 = none allocated)
   bool stepwise_all_branches_ = false;  // PTGPU_STEPWISE_ALL_BRANCHES: one engine call per step (A/B testing)
   bool is_replica_ = false;
+
+  // all engines of this partition; shards_[0] == engine_, shard s holds the sites
+  // [shard_begin_[s], shard_begin_[s + 1]) of the alignment
+  std::vector<ptgpu_engine*> shards_;
+  std::vector<unsigned int> shard_begin_;
+  class ShardPool;
+  std::shared_ptr<ShardPool> pool_;
+  // runs call(engine, shard) for every shard (concurrently when there are several: a shard's
+  // kernel waits for its peers') and throws what Check would for the first failure
+  void OnShards(const std::function<int(ptgpu_engine*, unsigned int)>& call) const;
+  void CreateEngines(unsigned int clv_buffers, unsigned int scale_buffers, unsigned int rate_cats,
+                     unsigned int wanted_shards);
+  void DestroyEngines();
 
   struct ReplicaTag {};
   Partition(const Partition& proto, ReplicaTag);

@@ -10,6 +10,8 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <thread>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -106,6 +108,157 @@ void Partition::Check(int rc) const
   throw std::runtime_error("ptgpu: " + msg);
 }
 
+// ---- site shards ---------------------------------------------------------------------------
+// One worker thread per extra shard; Run(fn) executes fn(0) on the caller's thread and fn(s) on
+// worker s-1, and returns when all are done.  A shard's kernel waits for its peers' kernels, so
+// the calls must be in flight together; the engine library keeps its error text per thread,
+// hence every thread reports its own.
+class Partition::ShardPool {
+ public:
+  explicit ShardPool(unsigned int shards) : rc_(shards, 0), msg_(shards)
+  {
+    for (unsigned int s = 1; s < shards; ++s) workers_.emplace_back([this, s] { Loop(s); });
+  }
+  ~ShardPool()
+  {
+    {
+      std::lock_guard<std::mutex> lock(m_);
+      quit_ = true;
+    }
+    wake_.notify_all();
+    for (std::thread& t : workers_) t.join();
+  }
+  // returns the first failing shard's (code, message), or (0, "")
+  std::pair<int, std::string> Run(const std::function<int(unsigned int)>& fn)
+  {
+    {
+      std::lock_guard<std::mutex> lock(m_);
+      fn_ = &fn;
+      pending_ = static_cast<unsigned int>(workers_.size());
+      ++generation_;
+    }
+    wake_.notify_all();
+    Invoke(fn, 0);
+    {
+      std::unique_lock<std::mutex> lock(m_);
+      done_.wait(lock, [this] { return pending_ == 0; });
+      fn_ = nullptr;
+    }
+    for (size_t s = 0; s < rc_.size(); ++s)
+      if (rc_[s] != PTGPU_OK) return std::make_pair(rc_[s], msg_[s]);
+    return std::make_pair(PTGPU_OK, std::string());
+  }
+
+ private:
+  void Invoke(const std::function<int(unsigned int)>& fn, unsigned int s)
+  {
+    try {
+      rc_[s] = fn(s);
+      msg_[s] = rc_[s] == PTGPU_OK ? std::string() : std::string(ptgpu_last_error());
+    } catch (const std::exception& ex) {
+      rc_[s] = PTGPU_ERR_STATE;
+      msg_[s] = ex.what();
+    }
+  }
+  void Loop(unsigned int s)
+  {
+    unsigned long long seen = 0;
+    for (;;) {
+      const std::function<int(unsigned int)>* fn = nullptr;
+      {
+        std::unique_lock<std::mutex> lock(m_);
+        wake_.wait(lock, [&] { return quit_ || generation_ != seen; });
+        if (quit_) return;
+        seen = generation_;
+        fn = fn_;
+      }
+      Invoke(*fn, s);
+      {
+        std::lock_guard<std::mutex> lock(m_);
+        --pending_;
+      }
+      done_.notify_one();
+    }
+  }
+  std::mutex m_;
+  std::condition_variable wake_, done_;
+  const std::function<int(unsigned int)>* fn_ = nullptr;
+  unsigned long long generation_ = 0;
+  unsigned int pending_ = 0;
+  bool quit_ = false;
+  std::vector<int> rc_;
+  std::vector<std::string> msg_;
+  std::vector<std::thread> workers_;
+};
+
+namespace {
+// Sharded operations of different Partitions are not interleaved: each is a set of kernels
+// that spin on one another, and two such sets that each hold part of a device while waiting
+// for the rest of it would wait for ever.  (A sharded alignment is one that fills the GPUs.)
+std::mutex g_sharded_call;
+
+void ThrowFor(int rc, const std::string& msg)
+{
+  if (rc == PTGPU_ERR_NOT_FINITE) throw std::range_error(msg);
+  if (rc == PTGPU_ERR_ARG || rc == PTGPU_ERR_STATE) throw std::invalid_argument(msg);
+  throw std::runtime_error("ptgpu: " + msg);
+}
+} // namespace
+
+void Partition::OnShards(const std::function<int(ptgpu_engine*, unsigned int)>& call) const
+{
+  if (shards_.size() <= 1) {
+    Check(call(engine_, 0));
+    return;
+  }
+  std::lock_guard<std::mutex> lock(g_sharded_call);
+  const auto failed = pool_->Run([&](unsigned int s) { return call(shards_[s], s); });
+  if (failed.first != PTGPU_OK) ThrowFor(failed.first, failed.second);
+}
+
+// the engines: one, or `wanted_shards` with contiguous tile-aligned site ranges (fewer if the
+// alignment has fewer tiles), on consecutive devices starting at device_
+void Partition::CreateEngines(unsigned int clv_buffers, unsigned int scale_buffers,
+                              unsigned int rate_cats, unsigned int wanted_shards)
+{
+  const unsigned int kTile = 256;  // the engine's reduction tile (kernels.cuh kTileSites)
+  const unsigned int tiles = (site_count_ + kTile - 1) / kTile;
+  unsigned int n = std::max(1u, std::min(std::min(wanted_shards, 8u), tiles));
+  const unsigned int per = (tiles + n - 1) / n;
+  n = (tiles + per - 1) / per;   // no empty shard
+  shard_begin_.assign(1, 0u);
+  for (unsigned int s = 0; s < n; ++s)
+    shard_begin_.push_back(std::min<unsigned long long>(site_count_, 1ull * (s + 1) * per * kTile));
+  const int ndev = std::max(1, ptgpu_device_count());
+  try {
+    for (unsigned int s = 0; s < n; ++s) {
+      ptgpu_engine* e = nullptr;
+      Check(ptgpu_create(tip_node_count_, clv_buffers, shard_begin_[s + 1] - shard_begin_[s], rate_cats,
+                         branch_count(), scale_buffers, (device_ + static_cast<int>(s)) % ndev, &e));
+      shards_.push_back(e);
+      if (n > 1) Check(ptgpu_set_shard(e, shard_begin_[s], site_count_));
+    }
+    if (n > 1) {
+      Check(ptgpu_comm_init(shards_.data(), n));
+      pool_ = std::make_shared<ShardPool>(n);
+    }
+  } catch (...) {
+    DestroyEngines();
+    throw;
+  }
+  engine_ = shards_[0];
+}
+
+void Partition::DestroyEngines()
+{
+  pool_.reset();
+  // no shard may still be writing into a peer's mailbox when that peer goes away
+  for (ptgpu_engine* e : shards_) ptgpu_synchronize(e);
+  for (ptgpu_engine* e : shards_) ptgpu_destroy(e);
+  shards_.clear();
+  engine_ = nullptr;
+}
+
 // PTPLL/pll_partition.cpp:25-65
 Partition::Partition(pll_utree_t* tree,
                      const Model& model,
@@ -165,16 +318,22 @@ Partition::Partition(pll_utree_t* tree,
     }
   }
   device_ = pick_device();
-  Check(ptgpu_create(tip_node_count_, inner_node_count() + extra, site_count_,
-                     static_cast<unsigned int>(model.category_rates.size()), branch_count(),
-                     inner_node_count() + extra, device_, &engine_));
+  unsigned int wanted_shards = 1;
+  if (const char* env = std::getenv("PTGPU_SITE_SHARDS")) wanted_shards = std::max(1, std::atoi(env));
+  CreateEngines(inner_node_count() + extra, inner_node_count() + extra,
+                static_cast<unsigned int>(model.category_rates.size()), wanted_shards);
+  // the whole-tree step program on a shard is ONE persistent kernel per GPU; the call-by-call
+  // form would pay a launch and an exchange per Newton step
+  if (shards_.size() > 1 && !std::getenv("PTGPU_STEPWISE_ALL_BRANCHES")) stepwise_all_branches_ = false;
   try {
     SetModel(model);
     SetTipStates(tree, labels, *tip_sequences);
-    if (!weights.empty()) Check(ptgpu_set_pattern_weights(engine_, weights.data()));
+    if (!weights.empty())
+      OnShards([&](ptgpu_engine* e, unsigned int s) {
+        return ptgpu_set_pattern_weights(e, weights.data() + shard_begin_[s]);
+      });
   } catch (...) {
-    ptgpu_destroy(engine_);
-    engine_ = nullptr;
+    DestroyEngines();
     throw;
   }
   AllocateScratchBuffers();
@@ -305,15 +464,15 @@ Partition::Partition(const Partition& proto, ReplicaTag) :
     stepwise_all_branches_(proto.stepwise_all_branches_),
     is_replica_(true)
 {
-  Check(ptgpu_create(tip_node_count_, inner_node_count(), site_count_,
-                     static_cast<unsigned int>(proto.model_.category_rates.size()), branch_count(),
-                     inner_node_count(), device_, &engine_));
+  if (proto.shards_.size() > 1)
+    throw std::logic_error("Replica() of a site-sharded partition is not supported");
+  CreateEngines(inner_node_count(), inner_node_count(),
+                static_cast<unsigned int>(proto.model_.category_rates.size()), 1);
   try {
     SetModel(proto.model_);
     Check(ptgpu_copy_tip_states(engine_, proto.engine_));
   } catch (...) {
-    ptgpu_destroy(engine_);
-    engine_ = nullptr;
+    DestroyEngines();
     throw;
   }
   AllocateScratchBuffers();
@@ -334,9 +493,13 @@ Partition::Partition(Partition&& rhs) :
     device_(rhs.device_),
     directional_base_(rhs.directional_base_),
     stepwise_all_branches_(rhs.stepwise_all_branches_),
-    is_replica_(rhs.is_replica_)
+    is_replica_(rhs.is_replica_),
+    shards_(std::move(rhs.shards_)),
+    shard_begin_(std::move(rhs.shard_begin_)),
+    pool_(std::move(rhs.pool_))
 {
   rhs.engine_ = nullptr;
+  rhs.shards_.clear();
   AllocateScratchBuffers();
 }
 
@@ -344,7 +507,7 @@ Partition::~Partition()
 {
   if (engine_) {
     PrintStats();
-    ptgpu_destroy(engine_);
+    DestroyEngines();
   }
 }
 
@@ -367,8 +530,10 @@ void Partition::SetModel(const Model& model)
   // count; the engine takes all three at once, so the check comes first)
   if (model_.category_rates.size() && model.category_rates.size() != model_.category_rates.size())
     throw std::invalid_argument("Invalid number of category rates");
-  Check(ptgpu_set_model(engine_, model.frequencies.data(), model.subst_params.data(),
-                        model.category_rates.data()));
+  OnShards([&](ptgpu_engine* e, unsigned int) {
+    return ptgpu_set_model(e, model.frequencies.data(), model.subst_params.data(),
+                           model.category_rates.data());
+  });
   model_ = model;
   model_.model_name = name;
 }
@@ -406,7 +571,11 @@ void Partition::SetTipStates(pll_utree_t* tree,
     raw[i] = sequences[i].c_str();
   }
   // the reference's per-tip pll_set_tip_states loop, as one upload + one encoding kernel
-  Check(ptgpu_set_tip_states_batch(engine_, tip_node_count_, tips.data(), raw.data()));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    std::vector<const char*> slice(raw);
+    for (const char*& p : slice) p += shard_begin_[s];   // this shard's columns of every row
+    return ptgpu_set_tip_states_batch(e, tip_node_count_, tips.data(), slice.data());
+  });
 }
 
 // sum over all branches of log(lambda) - lambda*length in post-order, the edge
@@ -431,9 +600,14 @@ double Partition::LogLikelihood(pll_unode_t* tree, double* per_site_lnl)
 {
   StatScope stat(kStatLogLikelihood);
   double lnl = 0.0;
-  Check(ptgpu_compute_edge_loglikelihood(engine_, tree->clv_index, tree->scaler_index,
-                                         tree->back->clv_index, tree->back->scaler_index,
-                                         tree->pmatrix_index, per_site_lnl, &lnl));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    double mine = 0.0;   // the same global sum on every shard
+    const int rc = ptgpu_compute_edge_loglikelihood(
+        e, tree->clv_index, tree->scaler_index, tree->back->clv_index, tree->back->scaler_index,
+        tree->pmatrix_index, per_site_lnl ? per_site_lnl + shard_begin_[s] : nullptr, &mine);
+    if (s == 0) lnl = mine;
+    return rc;
+  });
   if (map_mode_) {
     // the reference adds the terms one by one to lnl, in this order
     std::vector<pll_unode_t*> nodes(node_count(), nullptr);
@@ -477,11 +651,13 @@ unsigned int Partition::TraversalUpdate(pll_unode_t* root, TraversalType type)
   pll_utree_create_operations(travbuffer_.data(), traversal_size, branch_lengths_.data(),
                               matrix_indices_.data(), operations_.data(), &matrix_count,
                               &ops_count);
-  Check(ptgpu_update_prob_matrices(engine_, matrix_indices_.data(), branch_lengths_.data(),
-                                   matrix_count));
-  Check(ptgpu_update_partials(engine_,
-                              reinterpret_cast<const ptgpu_operation_t*>(operations_.data()),
-                              ops_count));
+  OnShards([&](ptgpu_engine* e, unsigned int) {
+    const int rc = ptgpu_update_prob_matrices(e, matrix_indices_.data(), branch_lengths_.data(),
+                                              matrix_count);
+    if (rc != PTGPU_OK) return rc;
+    return ptgpu_update_partials(e, reinterpret_cast<const ptgpu_operation_t*>(operations_.data()),
+                                 ops_count);
+  });
   return ops_count;
 }
 
@@ -490,7 +666,9 @@ void Partition::UpdateBranchLength(pll_unode_t* node, double length)
 {
   node->length = length;
   node->back->length = length;
-  Check(ptgpu_update_prob_matrices(engine_, &node->pmatrix_index, &node->length, 1));
+  OnShards([&](ptgpu_engine* e, unsigned int) {
+    return ptgpu_update_prob_matrices(e, &node->pmatrix_index, &node->length, 1);
+  });
 }
 
 // PTPLL/pll_partition.cpp:408-488.  The sumtable, the <= MAX_ITER Newton steps
@@ -501,9 +679,14 @@ double Partition::OptimizeBranch(pll_unode_t* node)
   StatScope stat(kStatOptimizeBranch);
   pll_unode_t* child = node->back;
   double len = node->length;
-  Check(ptgpu_optimize_branch(engine_, node->clv_index, node->scaler_index, child->clv_index,
-                              child->scaler_index, node->pmatrix_index, node->length, MAX_ITER,
-                              EPSILON, map_mode_ ? kMapLambda : 0.0, &len, nullptr));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    double mine = node->length;
+    const int rc = ptgpu_optimize_branch(e, node->clv_index, node->scaler_index, child->clv_index,
+                                         child->scaler_index, node->pmatrix_index, node->length,
+                                         MAX_ITER, EPSILON, map_mode_ ? kMapLambda : 0.0, &mine, nullptr);
+    if (s == 0) len = mine;
+    return rc;
+  });
   node->length = len;
   node->back->length = len;
   return len;
@@ -592,13 +775,21 @@ bool Partition::OptimizeEdgeBounded(pll_unode_t* p, double bl_min, double bl_max
 
   double len = guess;
   int status = 0;
-  Check(ptgpu_optimize_branch_bounded(engine_, p->clv_index, p->scaler_index, p->back->clv_index,
-                                      p->back->scaler_index, guess, bl_min, bl_max, tolerance, 30,
-                                      &len, &status, nullptr));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    double mine = guess;
+    int mine_status = 0;
+    const int rc = ptgpu_optimize_branch_bounded(e, p->clv_index, p->scaler_index, p->back->clv_index,
+                                                 p->back->scaler_index, guess, bl_min, bl_max,
+                                                 tolerance, 30, &mine, &mine_status, nullptr);
+    if (s == 0) { len = mine; status = mine_status; }
+    return rc;
+  });
   if (status != 0) return false;
 
   if (std::fabs(p->length - len) > 1e-10)
-    Check(ptgpu_update_prob_matrices(engine_, &p->pmatrix_index, &len, 1));
+    OnShards([&](ptgpu_engine* e, unsigned int) {
+      return ptgpu_update_prob_matrices(e, &p->pmatrix_index, &len, 1);
+    });
   p->length = len;
   p->back->length = len;
 
@@ -613,7 +804,7 @@ bool Partition::OptimizeEdgeBounded(pll_unode_t* p, double bl_min, double bl_max
       op.child2_clv_index = c2->back->clv_index;
       op.child2_matrix_index = c2->back->pmatrix_index;
       op.child2_scaler_index = c2->back->scaler_index;
-      Check(ptgpu_update_partials(engine_, &op, 1));
+      OnShards([&](ptgpu_engine* e, unsigned int) { return ptgpu_update_partials(e, &op, 1); });
     };
     reorient(q, p, z);
     if (!OptimizeEdgeBounded(q->back, bl_min, bl_max, tolerance, radius - 1)) return false;
@@ -632,9 +823,14 @@ double Partition::LocalBranchOptimization(pll_unode_t* tree, double bl_min, doub
 {
   auto edge_lnl = [this, tree]() {
     double v = 0.0;
-    Check(ptgpu_compute_edge_loglikelihood(engine_, tree->back->clv_index,
-                                           tree->back->scaler_index, tree->clv_index,
-                                           tree->scaler_index, tree->pmatrix_index, nullptr, &v));
+    OnShards([&](ptgpu_engine* e, unsigned int s) {
+      double mine = 0.0;
+      const int rc = ptgpu_compute_edge_loglikelihood(e, tree->back->clv_index, tree->back->scaler_index,
+                                                      tree->clv_index, tree->scaler_index,
+                                                      tree->pmatrix_index, nullptr, &mine);
+      if (s == 0) v = mine;
+      return rc;
+    });
     return v;
   };
   double lnl = edge_lnl();
@@ -800,12 +996,19 @@ void Partition::OptimizeAllBranchesFused(pll_unode_t* tree)
                         tree->back->scaler_index, tree->pmatrix_index, 0};
   double lnl = 0.0;
   int status = 0, passes = 0;
-  Check(ptgpu_optimize_all_branches(engine_, static_cast<unsigned int>(prologue.size()),
-                                    static_cast<unsigned int>(n_body),
-                                    static_cast<unsigned int>(bodies.size()), steps.data(), &edge,
-                                    lengths.data(), prior.data(), static_cast<unsigned int>(prior.size()),
-                                    MAX_ITER, EPSILON, map_mode_ ? kMapLambda : 0.0, max_passes,
-                                    optimised.data(), &lnl, &status, &passes));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    // every shard runs the same program and ends with the same lengths; shard 0's are taken
+    std::vector<double> mine(s == 0 ? 0 : branch_count());
+    double mine_lnl = 0.0;
+    int mine_status = 0, mine_passes = 0;
+    const int rc = ptgpu_optimize_all_branches(
+        e, static_cast<unsigned int>(prologue.size()), static_cast<unsigned int>(n_body),
+        static_cast<unsigned int>(bodies.size()), steps.data(), &edge, lengths.data(), prior.data(),
+        static_cast<unsigned int>(prior.size()), MAX_ITER, EPSILON, map_mode_ ? kMapLambda : 0.0,
+        max_passes, s == 0 ? optimised.data() : mine.data(), &mine_lnl, &mine_status, &mine_passes);
+    if (s == 0) { lnl = mine_lnl; status = mine_status; passes = mine_passes; }
+    return rc;
+  });
 
   for (pll_unode_t* n : nodes) {
     pll_unode_t* r = n;
@@ -883,8 +1086,9 @@ void Partition::UpdateDirectionalClvs(pll_utree_t* tree, const std::vector<unsig
       mlen.push_back(r->length);
     }
   }
-  Check(ptgpu_update_prob_matrices(engine_, midx.data(), mlen.data(),
-                                   static_cast<unsigned int>(midx.size())));
+  OnShards([&](ptgpu_engine* e, unsigned int) {
+    return ptgpu_update_prob_matrices(e, midx.data(), mlen.data(), static_cast<unsigned int>(midx.size()));
+  });
 
   // one op per inner-node record, children before parents (iterative post-order)
   std::vector<ptgpu_operation_t> plan;
@@ -929,7 +1133,9 @@ void Partition::UpdateDirectionalClvs(pll_utree_t* tree, const std::vector<unsig
       if (wanted[r->node_index - tips]) schedule(r);
   }
   if (!plan.empty())
-    Check(ptgpu_update_partials(engine_, plan.data(), static_cast<unsigned int>(plan.size())));
+    OnShards([&](ptgpu_engine* e, unsigned int) {
+      return ptgpu_update_partials(e, plan.data(), static_cast<unsigned int>(plan.size()));
+    });
 }
 
 std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree, int radius)
@@ -994,9 +1200,13 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tr
 
   std::vector<double> len(cands.size()), lnl(cands.size());
   std::vector<int> status(cands.size());
-  Check(ptgpu_score_nni_batch(engine_, cands.data(), static_cast<unsigned int>(cands.size()),
-                              MAX_ITER, EPSILON, map_mode_ ? kMapLambda : 0.0, len.data(),
-                              lnl.data(), status.data()));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    std::vector<double> l2(s == 0 ? 0 : cands.size()), v2(s == 0 ? 0 : cands.size());
+    std::vector<int> s2(s == 0 ? 0 : cands.size());
+    return ptgpu_score_nni_batch(e, cands.data(), static_cast<unsigned int>(cands.size()), MAX_ITER,
+                                 EPSILON, map_mode_ ? kMapLambda : 0.0, s == 0 ? len.data() : l2.data(),
+                                 s == 0 ? lnl.data() : v2.data(), s == 0 ? status.data() : s2.data());
+  });
   double prior = 0.0;
   if (map_mode_) prior = MapLogPrior(GetVirtualRoot(tree));
   for (size_t i = 0; i < out.size(); ++i) {
@@ -1269,11 +1479,16 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhoodLocal(pll_utree_
   std::vector<double> lengths(lengths0.size()), lnl(count);
   std::vector<int> status(count);
   // PLLMOD_OPT_MIN/MAX_BRANCH_LEN, EPSILON, MAX_ITER: PTPLL/pll_partition.cpp:629-637
-  Check(ptgpu_optimize_local_batch(engine_, count, n_private, n_lengths, 2,
-                                   static_cast<unsigned int>(body.size()), types.data(), steps.data(),
-                                   smooth.data(), final_edge.data(), lengths0.data(), 1.0e-4, 100.0,
-                                   EPSILON, MAX_ITER, lengths.data(), lnl.data(), status.data(),
-                                   nullptr));
+  OnShards([&](ptgpu_engine* e, unsigned int s) {
+    std::vector<double> l2(s == 0 ? 0 : lengths0.size()), v2(s == 0 ? 0 : count);
+    std::vector<int> s2(s == 0 ? 0 : count);
+    return ptgpu_optimize_local_batch(e, count, n_private, n_lengths, 2,
+                                      static_cast<unsigned int>(body.size()), types.data(), steps.data(),
+                                      smooth.data(), final_edge.data(), lengths0.data(), 1.0e-4, 100.0,
+                                      EPSILON, MAX_ITER, s == 0 ? lengths.data() : l2.data(),
+                                      s == 0 ? lnl.data() : v2.data(), s == 0 ? status.data() : s2.data(),
+                                      nullptr);
+  });
   double prior = 0.0;
   if (map_mode_) prior = MapLogPrior(GetVirtualRoot(tree));
   for (unsigned int i = 0; i < count; ++i) {

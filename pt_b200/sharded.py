@@ -10,7 +10,18 @@ is the one the reference's own (unused) multi-partition hooks foresee
 candidates' final lnL -- issued by the engine through its allreduce hook on the
 engine's own stream, so the Newton loop stays on the device between steps.
 
-This module is plumbing: ranges, the hook, and slicing of tip sequences.  All
+Two ways to do that exchange:
+
+* `exchange="peer"` (default on CUDA): the engines' own exchange -- every rank exports a
+  handle to its mailbox (ptgpu_shard_export), the handles go round once through
+  torch.distributed, every rank maps the others' (ptgpu_shard_connect), and from then on the
+  KERNELS sum the scalars over NVLink peer memory themselves, in rank order.  No call leaves
+  the engine between Newton steps, and the whole-tree step program
+  (ptgpu_optimize_all_branches) runs on a shard as one persistent kernel per GPU.
+* `exchange="hook"`: a torch.distributed.all_reduce per reduction through the engine's
+  allreduce hook (NCCL on GPUs; gloo with the CPU test-suite's stand-in engine).
+
+This module is plumbing: ranges, the exchange set-up, and slicing of tip sequences.  All
 arithmetic is in the CUDA engine; there is no CPU path (the `engine_factory`
 argument exists so the CPU test-suite can exercise this plumbing over gloo with
 a stand-in engine built from the test oracle).
@@ -45,7 +56,7 @@ class SiteShardedEngine:
     """Engine-compatible front-end whose reductions span all ranks of `group`."""
 
     def __init__(self, tips, clv_buffers, sites, rate_cats, prob_matrices, scale_buffers,
-                 group=None, device=None, engine_factory=Engine):
+                 group=None, device=None, engine_factory=Engine, exchange=None):
         import torch
         import torch.distributed as dist
         self._torch, self._dist, self.group = torch, dist, group
@@ -62,11 +73,25 @@ class SiteShardedEngine:
                                      scale_buffers, **kw)
         self.on_cuda = bool(getattr(self.engine, "on_cuda", True))
         self.engine.set_shard(self.begin, sites)
-        self._hook = ALLREDUCE_FN(self._allreduce)
-        self.engine.set_allreduce(self._hook)
+        self.exchange = exchange or ("peer" if (self.on_cuda and engine_factory is Engine) else "hook")
+        self._hook = None
         self.allreduce_calls = 0
         self.allreduce_doubles = 0
         self._views = {}
+        if self.exchange == "peer":
+            handles = [None] * self.world
+            dist.all_gather_object(handles, self.engine.shard_export(), group=group)
+            self.engine.shard_connect(self.rank, handles)
+            dist.barrier(group=group)   # nobody computes before everybody is connected
+        else:
+            self._hook = ALLREDUCE_FN(self._allreduce)
+            self.engine.set_allreduce(self._hook)
+
+    def exchanges(self):
+        """scalar exchanges between the shards so far (peer mode: counted on the device)"""
+        if self.exchange == "peer":
+            return self.engine.shard_status()[2]
+        return self.allreduce_calls
 
     # the hook the engine calls between its local reduction and the scalar update
     def _allreduce(self, ctx, ptr, count, stream):
@@ -121,5 +146,11 @@ class SiteShardedEngine:
         return torch.cat([o.cpu()[: e - b] for o, (b, e) in zip(outs, sizes)]).numpy().astype(np.uint32)
 
     def close(self):
-        self.engine.set_allreduce(None)
+        if self.exchange == "peer":
+            # a peer's mailbox must outlive every kernel that may still write into it
+            self.engine.synchronize()
+            self._dist.barrier(group=self.group)
+            self.engine.shard_disconnect()
+        else:
+            self.engine.set_allreduce(None)
         self.engine.close()
