@@ -40,12 +40,10 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from pytree import Tree, cand_array, random_tree_newick  # noqa: E402
-
-from synth import (FREQS, RATES, SEED_ALN, SEED_TREE, SUBST, parent_tree,  # noqa: E402
-                   simulate)
+from pt_b200.pytree import Tree, cand_array, random_tree_newick  # noqa: E402
+from pt_b200.synth import (FREQS, RATES, SEED_ALN, SEED_TREE, SUBST, parent_tree,  # noqa: E402
+                           simulate)
 
 
 class ClockSampler(threading.Thread):
@@ -423,6 +421,14 @@ def run_ours(args):
         t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_s = float(t[0]), float(t[1])
+    # BASELINE configs[2] after the main timed region, in the same run: the same alignment with
+    # its SITES sharded over the N GPUs, one tree visited (full-tree lnL + OptimizeAllBranches)
+    sharded = None
+    if not args.no_sharded and args.radius == 0 and weights is None:
+        e.close()
+        del host_aln
+        sharded = sharded_visit(n, S, rank, world, local, dist, steps=min(max(args.steps, 2), 3), warmup=1,
+                                aln=aln)
     if rank != 0:
         if dist:
             dist.destroy_process_group()
@@ -497,6 +503,8 @@ def run_ours(args):
                  note="raw alignment in pinned host memory uploaded + encoded every step"),
         lnl_checksum=float(np.sum(lnls)),
     )
+    if sharded is not None:
+        line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline_single(n, S, aln, tree, min(S, args.cpu_sample_sites), args.radius)
         if cb:
@@ -598,20 +606,143 @@ def sharded_reference_leg(taxa, sites, sample, steps=1):
                        f"{1 + steps} ({best:.2f} s), scaled by sites ratio", seconds_at_sample=best)
 
 
-def run_sharded(args):
-    """`--workload sharded`: BASELINE configs[2] -- synthetic 64 taxa x 1M sites, full-tree lnL +
-    OptimizeAllBranches, the SITES split over the ranks (contiguous tile-aligned ranges).  The
-    only collective is the allreduce of per-tree scalars the engine issues on its own stream
-    (1 double per edge lnL, 3 per Newton step); strong scaling: the tree and the alignment are
-    the same at every N.  One STEP = what Wanderer::MoveForward does for a tree it visits
-    (src/wanderer.cpp:150-210): FULL TraversalUpdate, LogLikelihood, OptimizeAllBranches
-    (call by call: the step-program kernel is a single-device procedure), LogLikelihood."""
+def sharded_visit(n, S, rank, world, local, dist, steps, warmup, call_by_call=False, exchange="peer",
+                  parity=True, aln=None):
+    """BASELINE configs[2]: one tree, the SITES split over the ranks (contiguous tile-aligned
+    ranges).  One unit = what Wanderer::MoveForward does for a tree it visits
+    (src/wanderer.cpp:150-210): FULL TraversalUpdate, LogLikelihood, OptimizeAllBranches,
+    LogLikelihood -- four engine calls per rank, the whole-tree optimisation being ONE persistent
+    kernel per GPU that sums d1/d2 and lnL over the shards itself (NVLink peer memory, rank
+    order).  Strong scaling: same tree and alignment at every N.  Returns rank 0's record (None
+    elsewhere): ms per tree (CUDA events on the engine's stream, max over ranks), the same
+    procedure unsharded on rank 0's GPU in the same run (=> efficiency), launches / exchanges per
+    tree, and the parity verdict against the unsharded run (scaler counts integer-identical,
+    lnL within 1e-12)."""
+    import hashlib
     import torch
-    import torch.distributed as dist
-    import all_branches as ab
-    from pt_b200.engine import ops_array
+    from pt_b200 import all_branches as ab
+    from pt_b200.engine import Engine
     from pt_b200.sharded import SiteShardedEngine, shard_range
 
+    tree = parent_tree(n, 0)
+    if aln is None:
+        aln = simulate(tree, S, np.random.default_rng(SEED_ALN))
+    newick = tree.newick()
+    tip_ids = np.arange(n, dtype=np.uint32)
+
+    def pinned_rows(b0, b1):
+        host = torch.empty((n, b1 - b0), dtype=torch.uint8).pin_memory()
+        for tip in tree.nodes[:n]:
+            host[tip.clv_index].copy_(torch.from_numpy(np.ascontiguousarray(aln[tip.label][b0:b1])))
+        return host, [host[t].data_ptr() for t in range(n)]
+
+    def scaler_digests(e, ranges):
+        """sha256 over all n-2 scaler rows, one digest per site range"""
+        hs = [hashlib.sha256() for _ in ranges]
+        for i in range(n - 2):
+            row = e.get_scaler(i)
+            for h, (b, e_) in zip(hs, ranges):
+                h.update(np.ascontiguousarray(row[b:e_]).tobytes())
+        return [h.hexdigest() for h in hs]
+
+    def timed(e, stream_dev, barrier):
+        info = {}
+
+        def unit():
+            t = Tree(newick)              # every unit starts from the input lengths
+            info["lnl0"], info["lnl"], info["passes"] = ab.visit(e, t, call_by_call=call_by_call)
+            info["lengths"] = t.branches()
+
+        for _ in range(warmup):
+            unit()
+        stream = torch.cuda.ExternalStream(e.stream(), device=torch.device("cuda", stream_dev))
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0 = e.counters()
+        barrier()
+        torch.cuda.synchronize()
+        ev0.record(stream)
+        for _ in range(steps):
+            unit()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        barrier()
+        c1 = e.counters()
+        info["ms"] = ev0.elapsed_time(ev1) / steps
+        info["launches"] = (c1["launches"] - c0["launches"]) / steps
+        info["site_updates"] = (c1["site_updates"] - c0["site_updates"]) / steps
+        info["newton_passes"] = (c1["newton_passes"] - c0["newton_passes"]) / steps
+        return info
+
+    bar = (lambda: dist.barrier()) if (dist and world > 1) else (lambda: None)
+    b0, b1 = shard_range(S, world, rank)
+    if world > 1:
+        e = SiteShardedEngine(n, n - 2, S, 4, 2 * n - 3, n - 2, device=local, exchange=exchange)
+        eng = e.engine
+    else:
+        e = eng = Engine(n, n - 2, S, 4, 2 * n - 3, n - 2, device=local)
+    e.set_model(FREQS, SUBST, RATES)
+    host, ptrs = pinned_rows(b0, b1)
+    eng.set_tip_states_batch(tip_ids, ptrs)
+    x0 = e.exchanges() if world > 1 else 0
+    info = timed(e, local, bar)
+    exchanges = ((e.exchanges() - x0) / (warmup + steps)) if world > 1 else 0
+    digest = scaler_digests(eng, [(0, b1 - b0)])[0] if parity else None
+    ms = info["ms"]
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        upd = torch.tensor([info["site_updates"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(upd, op=dist.ReduceOp.SUM)
+        site_updates = float(upd[0])
+        digests = [None] * world
+        dist.all_gather_object(digests, digest)
+    else:
+        site_updates, digests = info["site_updates"], [digest]
+    e.close()
+    del host
+    rec = None
+    if rank == 0:
+        rec = dict(ms_per_tree=ms, trees_per_s=1e3 / ms, n_gpus=world, sites_per_gpu=b1 - b0,
+                   procedure=("call by call" if call_by_call else
+                              "one persistent step-program kernel per GPU (ptgpu_optimize_all_branches)"),
+                   exchange=(("in-kernel sums over NVLink peer memory, rank order" if exchange == "peer"
+                              else "torch.distributed allreduce hook") if world > 1 else "none (one GPU)"),
+                   gpu_launches_per_tree=info["launches"], engine_calls_per_tree=4 if not call_by_call else None,
+                   host_round_trips_inside_optimize_all_branches=0 if not call_by_call else None,
+                   cross_gpu_exchanges_per_tree=exchanges,
+                   nvlink_payload_bytes_per_tree_per_gpu=int(exchanges * 2 * 16 * max(0, world - 1)),
+                   optimize_all_branches_passes=info["passes"], newton_evaluations_per_tree=info["newton_passes"],
+                   clv_site_updates_per_s=site_updates / (ms * 1e-3),
+                   lnl_start=info["lnl0"], lnl_optimised=info["lnl"])
+        if world > 1 and parity:
+            # the same procedure unsharded on this rank's GPU, in the same run
+            e1 = Engine(n, n - 2, S, 4, 2 * n - 3, n - 2, device=local)
+            e1.set_model(FREQS, SUBST, RATES)
+            host, ptrs = pinned_rows(0, S)
+            e1.set_tip_states_batch(tip_ids, ptrs)
+            one = timed(e1, local, lambda: None)
+            ranges = [shard_range(S, world, r) for r in range(world)]
+            same = scaler_digests(e1, ranges) == digests
+            e1.close()
+            rel = abs(info["lnl"] - one["lnl"]) / abs(one["lnl"])
+            rel0 = abs(info["lnl0"] - one["lnl0"]) / abs(one["lnl0"])
+            len_rel = max(abs(info["lengths"][k] - v) / max(1e-8, abs(v)) for k, v in one["lengths"].items())
+            rec.update(ms_per_tree_1gpu_same_run=one["ms"],
+                       strong_scaling_efficiency=one["ms"] / (world * ms),
+                       speedup_vs_1gpu=one["ms"] / ms,
+                       parity=dict(scaler_counts_identical=bool(same), lnl_rel_diff=rel, lnl_start_rel_diff=rel0,
+                                   passes_equal=info["passes"] == one["passes"], max_length_rel_diff=len_rel,
+                                   passed=bool(same and rel <= 1e-12 and rel0 <= 1e-12)))
+    if world > 1:
+        dist.barrier()
+    return rec
+
+
+def run_sharded(args):
+    """`--workload sharded`: BASELINE configs[2] as the line's own metric (trees visited/s, strong
+    scaling); the default workload carries the same record as its `sharded` sub-record."""
+    import torch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -636,149 +767,38 @@ def run_sharded(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local)
-    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    os.environ.setdefault("MASTER_PORT", "29577")
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29577")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    n, S = args.taxa, args.sites
-    tree = parent_tree(n, 0)
-    aln = simulate(tree, S, np.random.default_rng(SEED_ALN))
-    e = SiteShardedEngine(n, n - 2, S, 4, 2 * n - 3, n - 2, device=local)
-    e.set_model(FREQS, SUBST, RATES)
-    b0, b1 = shard_range(S, world, rank)
-    # this rank's slice of the raw alignment in pinned host memory
-    host_aln = torch.empty((n, b1 - b0), dtype=torch.uint8).pin_memory()
-    for tip in tree.nodes[:n]:
-        host_aln[tip.clv_index].copy_(torch.from_numpy(np.ascontiguousarray(aln[tip.label][b0:b1])))
-    tip_ids = np.arange(n, dtype=np.uint32)
-    tip_ptrs = [host_aln[t].data_ptr() for t in range(n)]
-    e.engine.set_tip_states_batch(tip_ids, tip_ptrs)
-    lengths0 = {r.node_index: r.length for r in tree.by_index.values()}
-    root = tree.root
-    info = {}
-    count = dict(partials_bytes=0)      # per site, over ALL steps run (warm-up, timed, e2e)
-    raw_update_partials = e.engine.update_partials
-
-    def counted_update_partials(ops):
-        for c in ("child1_clv_index", "child2_clv_index"):
-            count["partials_bytes"] += int(np.where(ops[c] < n, 1, 132).sum())
-        count["partials_bytes"] += 132 * len(ops)
-        raw_update_partials(ops)
-
-    e.engine.update_partials = counted_update_partials
-
-    def step():
-        for r in tree.by_index.values():          # every step starts from the input lengths
-            r.length = lengths0[r.node_index]
-        flags = ab.Flags()
-        mats, ops = ab.traverse(root, flags, partial=False)
-        e.update_prob_matrices([m.pmatrix_index for m in mats], [m.length for m in mats])
-        e.update_partials(ops_array(ops))
-        rb = root.back
-        info["lnl0"] = e.edge_loglikelihood(root.clv_index, root.scaler_index, rb.clv_index,
-                                            rb.scaler_index, root.pmatrix_index)
-        info["lnl"], info["passes"] = ab.stepwise(e, root, flags)
-
-    for _ in range(args.warmup):
-        step()
-    stream = torch.cuda.ExternalStream(e.stream(), device=torch.device("cuda", local))
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    c0, calls0, dbl0 = e.counters(), e.allreduce_calls, e.allreduce_doubles
-    dist.barrier()
-    torch.cuda.synchronize()
     wall0 = time.time()
-    ev0.record(stream)
-    for _ in range(args.steps):
-        step()
-    ev1.record(stream)
-    torch.cuda.synchronize()
-    dist.barrier()
-    ms = ev0.elapsed_time(ev1)
-    c1, calls1, dbl1 = e.counters(), e.allreduce_calls, e.allreduce_doubles
-    # per-kernel CUDA events in a SEPARATE pass: two event records around each of the ~20 k
-    # launches of a step would weigh on the timed region
-    e.set_profiling(True)
-    e.kernel_times(reset=True)
-    torch.cuda.synchronize()
-    tp0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    torch.cuda.synchronize()
-    ms_profiled = 1e3 * (time.perf_counter() - tp0)
-    kt = e.kernel_times(reset=True)
-    e.set_profiling(False)
-    t_e2e = []
-    for i in range(1 + args.steps):
-        dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        e.engine.set_tip_states_batch(tip_ids, tip_ptrs)
-        step()
-        torch.cuda.synchronize()
-        if i:
-            t_e2e.append(time.perf_counter() - t0)
+    rec = sharded_visit(args.taxa, args.sites, rank, world, local, dist, args.steps, args.warmup,
+                        call_by_call=args.call_by_call, exchange=args.exchange)
     clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
-    t = torch.tensor([ms, sum(t_e2e)], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_s = float(t[0]), float(t[1])
-    upd = torch.tensor([float(c1["site_updates"] - c0["site_updates"]),
-                        float(c1["newton_passes"] - c0["newton_passes"])], dtype=torch.float64, device="cuda")
-    dist.all_reduce(upd, op=dist.ReduceOp.SUM)
-    if rank != 0:
+    if rank == 0:
+        n, S = args.taxa, args.sites
+        line = dict(metric="trees_visited_per_s", value=rec["trees_per_s"], unit="trees/s", n_gpus=world,
+                    steps=args.steps, warmup=args.warmup, ms_per_step=rec["ms_per_tree"], higher_is_better=True,
+                    scaling="strong", vs_baseline=None, dtype="f64", data="synthetic",
+                    config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]): per step FULL "
+                                         "traversal + lnL + OptimizeAllBranches + lnL of ONE tree, sites sharded over "
+                                         "the GPUs (contiguous tile-aligned ranges), per-tree scalars summed between "
+                                         "the GPUs only", taxa=n, sites=S, rate_cats=4,
+                                parallelism=f"site-sharded x{world}",
+                                l2="every pass streams this rank's CLVs (>= 16 MB each): no flush needed"),
+                    gpu_launches=int(rec["gpu_launches_per_tree"] * args.steps), sharded=rec, clocks=clocks,
+                    e2e=dict(value=rec["trees_per_s"], unit="trees/s", h2d_bytes_per_step=0, d2h_bytes_per_step=16,
+                             note="alignment resident; the visit's scalars come back to the host"))
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = sharded_reference_leg(n, S, min(S, 20000))
+        print(json.dumps(line))
+    if dist:
         dist.destroy_process_group()
-        return
-    steps = args.steps
-    site_updates = float(upd[0])                      # all ranks, all timed steps
-    peak, peak_kind = measured_peak()
-    Sl = b1 - b0
-    # rank 0's kernels on its shard (CUDA events on the engine's stream); algorithmic bytes:
-    # CLV updates exactly from the op lists, sumtable 384 B/site (256 in, 128 out), a derivative
-    # sweep 128 B/site (one sweep + one reduce + one update kernel per Newton step), edge lnL 268 B/site
-    kernels = {}
-    sweeps = kt["newton"][1] / 3.0 / steps
-    algo = dict(partials=count["partials_bytes"] / (1 + args.warmup + 3 * steps) * steps * Sl,
-                sumtable=kt["sumtable"][1] * 384.0 * Sl, newton=sweeps * steps * 128.0 * Sl,
-                edge_lnl=kt["edge_lnl"][1] * 268.0 * Sl)
-    for k in ("partials", "sumtable", "newton", "edge_lnl", "pmatrix"):
-        k_ms, k_n = kt[k]
-        if k_n:
-            kernels[k] = dict(ms_total_per_step=k_ms / steps, launches_per_step=k_n / steps,
-                              share_of_step=k_ms / ms_profiled)
-            if k in algo:
-                kernels[k]["achieved_gbs"] = algo[k] / (k_ms * 1e-3) / 1e9
-    gap = 1.0 - sum(v["share_of_step"] for v in kernels.values())
-    dom = max(kernels, key=lambda k: kernels[k]["share_of_step"]) if kernels else None
-    value = steps / (ms * 1e-3)
-    line = dict(
-        metric="trees_visited_per_s", value=value, unit="trees/s", n_gpus=world, steps=steps,
-        warmup=args.warmup, ms_per_step=ms / steps, higher_is_better=True, scaling="strong",
-        vs_baseline=None, dtype="f64", data="synthetic",
-        config=dict(workload=f"synthetic {n} taxa x {S} sites GTR+G4 (BASELINE configs[2]): per step FULL "
-                             "traversal + lnL + OptimizeAllBranches + lnL of ONE tree, sites sharded over the "
-                             "GPUs (contiguous tile-aligned ranges), allreduce of per-tree scalars only",
-                    taxa=n, sites=S, sites_per_gpu=Sl, rate_cats=4, parallelism=f"site-sharded x{world}",
-                    l2="every pass streams this rank's CLVs (>= 128 MB each at N <= 8): larger than L2; no flush"),
-        clv_site_updates_per_s=site_updates / (ms * 1e-3),
-        optimize_all_branches_passes=info["passes"], newton_sweeps_per_step=sweeps,
-        allreduce_calls_per_step=(calls1 - calls0) / steps,
-        allreduce_doubles_per_step=(dbl1 - dbl0) / steps,
-        lnl_start=info["lnl0"], lnl_optimised=info["lnl"],
-        gpu_launches=int(c1["launches"] - c0["launches"]), kernels=kernels,
-        outside_kernels_share=gap,   # launch gaps, the allreduce and the Python driver between ~20 k launches
-        ms_per_step_with_kernel_events=ms_profiled / steps,
-        roofline=(dict(bound="hbm", kernel=dom, achieved=kernels[dom]["achieved_gbs"], peak=peak, unit="GB/s",
-                       frac=kernels[dom]["achieved_gbs"] / peak, peak_source=peak_kind, traffic=None)
-                  if dom else None),
-        clocks=clocks,
-        e2e=dict(value=steps / e2e_s, unit="trees/s", h2d_bytes_per_step=n * Sl, d2h_bytes_per_step=16,
-                 note="every rank uploads + encodes its slice of the raw alignment (pinned host memory) "
-                      "every step; bytes are per rank"))
-    if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = sharded_reference_leg(n, S, min(S, 20000))
-    print(json.dumps(line))
-    dist.destroy_process_group()
 
 
 def main():
@@ -797,6 +817,12 @@ def main():
     ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1", "sharded"])
     ap.add_argument("--compress-patterns", action="store_true",
                     help="score the alignment's unique columns with weights (SURVEY 8f-4; not the headline)")
+    ap.add_argument("--call-by-call", action="store_true",
+                    help="sharded: OptimizeAllBranches as the reference's call sequence instead of one kernel")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "hook"],
+                    help="sharded: in-kernel peer-memory sums (default) or the NCCL allreduce hook")
+    ap.add_argument("--no-sharded", action="store_true",
+                    help="default workload: skip the site-sharded sub-record (BASELINE configs[2])")
     ap.add_argument("--wanderers", type=int, default=1,
                     help="ptw-ds1: wanderer threads of ptw_batched (each owns an engine on the GPU)")
     args = ap.parse_args()

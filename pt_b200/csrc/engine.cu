@@ -42,6 +42,13 @@ int fail(int code, const char *fmt, ...)
   return code;
 }
 
+// Scratch that grows while the engine is in use comes from the stream-ordered allocator:
+// cudaMalloc / cudaFree synchronise the whole device (and, with peer access enabled, touch
+// the peers' page tables), which must not happen while a site shard's kernel on that device
+// is waiting for a peer whose host thread would be the one blocked in the allocation.
+#define PT_MALLOC(e, ptr, bytes) cudaMallocAsync((void **)(ptr), (bytes), (e)->stream)
+#define PT_FREE(e, ptr) ((ptr) ? cudaFreeAsync((void *)(ptr), (e)->stream) : cudaSuccess)
+
 #define CU(call)                                                                        \
   do                                                                                    \
   {                                                                                     \
@@ -123,6 +130,7 @@ struct ptgpu_engine
   // many-wanderer process to two kernels in flight
   unsigned char *h_pin = nullptr;
   size_t h_pin_cap = 0;
+  std::vector<unsigned char *> h_pin_old;
   unsigned int *d_weights = nullptr; // pattern weights (ptgpu_set_pattern_weights), model.weights points here
   bool counted = false;             // included in g_live_engines
   int coop_blocks_per_sm = 0;
@@ -139,6 +147,7 @@ struct ptgpu_engine
   unsigned long long *d_mailbox = nullptr;   // this shard's mailbox (peers write into it)
   unsigned long long *d_seq = nullptr;
   void *ipc_open[kMaxShards] = {};           // peers' mailboxes opened from IPC handles
+  int same_device_shards = 1;                // shards of this alignment on this device (tests: several)
   unsigned int *d_active = nullptr;
   unsigned long long counters[4] = {0, 0, 0, 0};
   unsigned long long lnl_sweeps = 0, final_sweeps = 0;
@@ -167,7 +176,10 @@ unsigned int coop_grid_share(const ptgpu_engine *e, unsigned int full)
 {
   const int live = g_live_engines[e->device & 63].load(std::memory_order_relaxed);
   static const int max_div = [] { const char *v = getenv("PTGPU_COOP_SHARE_MAX"); return v ? std::max(1, atoi(v)) : 2; }();
-  const unsigned int div = (unsigned int)std::min(std::max(live, 1), max_div);
+  unsigned int div = (unsigned int)std::min(std::max(live, 1), max_div);
+  // shards of one alignment that share a device wait for one another inside their kernels:
+  // their cooperative grids must all be resident at the same time
+  div = std::max(div, (unsigned int)e->same_device_shards);
   return std::max(std::min(full, 16u), full / div);
 }
 
@@ -406,6 +418,7 @@ void ptgpu_destroy(ptgpu_engine *e)
   for (auto ev : e->event_pool) cudaEventDestroy(ev);
   if (e->stg.host) cudaFreeHost(e->stg.host);
   if (e->h_pin) cudaFreeHost(e->h_pin);
+  for (unsigned char *p : e->h_pin_old) cudaFreeHost(p);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
 }
@@ -453,7 +466,7 @@ int ptgpu_set_tip_states(ptgpu_engine *e, unsigned int tip_index, const char *se
     return t;
   }();
   CU(cudaSetDevice(e->device));
-  if (!e->d_raw) CU(cudaMalloc(&e->d_raw, e->sites));
+  if (!e->d_raw) CU(PT_MALLOC(e, &e->d_raw, e->sites));
   // the characters are encoded on the device: one H2D copy of the raw bytes
   // (asynchronous when the caller's buffer is pinned) and one byte-map kernel
   unsigned int *bad_h = (unsigned int *)(e->stg.host + kStgBad);
@@ -493,7 +506,7 @@ int ptgpu_set_pattern_weights(ptgpu_engine *e, const unsigned int *weights)
   }
   for (unsigned int i = 0; i < e->sites; ++i)
     if (!weights[i]) return fail(PTGPU_ERR_ARG, "ptgpu_set_pattern_weights: weight of pattern %u is zero", i);
-  if (!e->d_weights) CU(cudaMalloc(&e->d_weights, (size_t)e->sites * sizeof(unsigned int)));
+  if (!e->d_weights) CU(PT_MALLOC(e, &e->d_weights, (size_t)e->sites * sizeof(unsigned int)));
   int rc;
   if ((rc = pin_reserve(e, (size_t)e->sites * sizeof(unsigned int)))) return rc;
   memcpy(e->h_pin, weights, (size_t)e->sites * sizeof(unsigned int));
@@ -514,7 +527,7 @@ int ptgpu_copy_tip_states(ptgpu_engine *dst, ptgpu_engine *src)
                      dst->stream));
   if (src->model.weights)
   {
-    if (!dst->d_weights) CU(cudaMalloc(&dst->d_weights, (size_t)dst->sites * sizeof(unsigned int)));
+    if (!dst->d_weights) CU(PT_MALLOC(dst, &dst->d_weights, (size_t)dst->sites * sizeof(unsigned int)));
     CU(cudaMemcpyAsync(dst->d_weights, src->d_weights, (size_t)src->sites * sizeof(unsigned int),
                        cudaMemcpyDeviceToDevice, dst->stream));
     dst->model.weights = dst->d_weights;
@@ -604,14 +617,14 @@ int ptgpu_set_tip_states_batch(ptgpu_engine *e, unsigned int count, const unsign
   const size_t S = e->sites;
   if (e->raw_all_cap < (size_t)count * S)
   {
-    if (e->d_raw_all) CU(cudaFree(e->d_raw_all));
+    if (e->d_raw_all) CU(PT_FREE(e, e->d_raw_all));
     e->d_raw_all = nullptr;
     e->raw_all_cap = 0;
-    CU(cudaMalloc(&e->d_raw_all, (size_t)e->tips * S));
+    CU(PT_MALLOC(e, &e->d_raw_all, (size_t)e->tips * S));
     e->raw_all_cap = (size_t)e->tips * S;
   }
-  if (!e->d_tip_of) CU(cudaMalloc(&e->d_tip_of, e->tips * sizeof(unsigned int)));
-  if (!e->d_bad) CU(cudaMalloc(&e->d_bad, sizeof(unsigned long long)));
+  if (!e->d_tip_of) CU(PT_MALLOC(e, &e->d_tip_of, e->tips * sizeof(unsigned int)));
+  if (!e->d_bad) CU(PT_MALLOC(e, &e->d_bad, sizeof(unsigned long long)));
   unsigned long long *bad_h = (unsigned long long *)(e->stg.host + kStgBad);
   unsigned long long *bad_d = e->d_bad;
   CU(cudaStreamSynchronize(e->stream));
@@ -657,17 +670,18 @@ namespace {
 constexpr size_t kUploadOff = 4096;
 
 template <typename T>
-int ensure(T **ptr, size_t *cap, size_t need)
+int ensure_on(ptgpu_engine *e, T **ptr, size_t *cap, size_t need)
 {
   if (need <= *cap) return PTGPU_OK;
-  if (*ptr) CU(cudaFree(*ptr));
+  if (*ptr) CU(PT_FREE(e, *ptr));
   *ptr = nullptr;
   *cap = 0;
   size_t n = std::max<size_t>(need, 64);
-  CU(cudaMalloc(ptr, n * sizeof(T)));
+  CU(PT_MALLOC(e, ptr, n * sizeof(T)));
   *cap = n;
   return PTGPU_OK;
 }
+#define ensure(ptr, cap, need) ensure_on(e, ptr, cap, need)
 
 // pinned host arena of at least `bytes` (contents are NOT kept when it grows; the stream is
 // drained first, so nothing in flight still reads or writes the old one)
@@ -675,7 +689,7 @@ int pin_reserve(ptgpu_engine *e, size_t bytes)
 {
   if (bytes <= e->h_pin_cap) return PTGPU_OK;
   CU(cudaStreamSynchronize(e->stream));
-  if (e->h_pin) CU(cudaFreeHost(e->h_pin));
+  if (e->h_pin) e->h_pin_old.push_back(e->h_pin);   // freed with the engine: cudaFreeHost synchronises the device
   e->h_pin = nullptr;
   e->h_pin_cap = 0;
   const size_t n = std::max<size_t>(bytes + bytes / 2, 1 << 16);
@@ -802,7 +816,7 @@ int newton_split(ptgpu_engine *e, NewtonArgs &a)
 {
   int rc;
   if ((rc = ensure(&e->d_red, &e->red_cap, (size_t)a.B * 3))) return rc;
-  if (!e->d_active) CU(cudaMalloc(&e->d_active, 2 * sizeof(unsigned int)));
+  if (!e->d_active) CU(PT_MALLOC(e, &e->d_active, 2 * sizeof(unsigned int)));
   const unsigned int work = std::max(1u, a.B * a.nchunks);
   const unsigned int grid = std::min(work, (unsigned int)e->sm_count * 8u);
   constexpr int FS = few_work_stages<C>();
@@ -928,7 +942,7 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
   double *d_persite = nullptr;
   if (persite_lnl)
   {
-    if (!e->d_persite) CU(cudaMalloc(&e->d_persite, (size_t)e->sites * sizeof(double)));
+    if (!e->d_persite) CU(PT_MALLOC(e, &e->d_persite, (size_t)e->sites * sizeof(double)));
     d_persite = e->d_persite;
   }
   double *result = (double *)(e->stg.dev + kStgResult);
@@ -1014,7 +1028,7 @@ int ptgpu_compute_likelihood_derivatives(ptgpu_engine *e, double branch_length, 
   CU(cudaStreamSynchronize(e->stream));
   *d_f = hs->d1;
   *dd_f = hs->d2;
-  return PTGPU_OK;
+  return shard_check(e);
 }
 
 int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
@@ -1041,6 +1055,7 @@ int ptgpu_optimize_branch(ptgpu_engine *e, unsigned int parent_clv_index,
   CU(cudaStreamSynchronize(e->stream));
   *length_out = hs->len;
   if (iterations) *iterations = hs->iters;
+  if ((rc = shard_check(e))) return rc;
   if (hs->status == 1) return fail(PTGPU_ERR_NOT_FINITE, "d1 is not finite");
   if (hs->status == 2) return fail(PTGPU_ERR_NOT_FINITE, "d2 is not finite");
   return PTGPU_OK;
@@ -1071,7 +1086,7 @@ int ptgpu_optimize_branch_bounded(ptgpu_engine *e, unsigned int parent_clv_index
   *length_out = hs->len;
   *status = hs->status;
   if (iterations) *iterations = hs->iters;
-  return PTGPU_OK;
+  return shard_check(e);
 }
 
 int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
@@ -1111,14 +1126,14 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
   }
   if (chunk > e->bcap)
   {
-    cudaFree(e->d_bsum); cudaFree(e->d_bsclr); cudaFree(e->d_bstate); cudaFree(e->d_bpartials); cudaFree(e->d_bcands);
+    PT_FREE(e, e->d_bsum); PT_FREE(e, e->d_bsclr); PT_FREE(e, e->d_bstate); PT_FREE(e, e->d_bpartials); PT_FREE(e, e->d_bcands);
     e->d_bsum = nullptr; e->d_bsclr = nullptr; e->d_bstate = nullptr; e->d_bpartials = nullptr; e->d_bcands = nullptr;
     e->bcap = 0;
-    CU(cudaMalloc(&e->d_bsum, chunk * stride * sizeof(double)));
-    CU(cudaMalloc(&e->d_bsclr, chunk * (size_t)e->sites * sizeof(unsigned int)));
-    CU(cudaMalloc(&e->d_bstate, chunk * sizeof(NewtonState)));
-    CU(cudaMalloc(&e->d_bpartials, chunk * (size_t)e->ntiles * 3 * sizeof(double)));
-    CU(cudaMalloc(&e->d_bcands, chunk * sizeof(DevGroup)));
+    CU(PT_MALLOC(e, &e->d_bsum, chunk * stride * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_bsclr, chunk * (size_t)e->sites * sizeof(unsigned int)));
+    CU(PT_MALLOC(e, &e->d_bstate, chunk * sizeof(NewtonState)));
+    CU(PT_MALLOC(e, &e->d_bpartials, chunk * (size_t)e->ntiles * 3 * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_bcands, chunk * sizeof(DevGroup)));
     e->bcap = chunk;
   }
   // per-candidate Newton states go up and come back through the pinned arena
@@ -1205,6 +1220,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     if ((rc = run_newton(e, a))) return rc;
     CU(cudaMemcpyAsync(hst, e->d_bstate, nb * sizeof(NewtonState), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    if ((rc = shard_check(e))) return rc;
     for (unsigned int i = 0; i < nb; ++i)
     {
       length_out[base + i] = hst[i].len;
@@ -1379,6 +1395,35 @@ int ptgpu_synchronize(ptgpu_engine *e)
 // ---- the engines' own exchange between site shards (kernels.cuh, ShardComm) --------------
 namespace {
 
+int blo_prepare_kernel(ptgpu_engine *e);
+
+// With lazy module loading (the CUDA 12 default) the FIRST launch of a kernel loads it, which
+// can synchronise the context -- fatal if a peer shard's kernel on the same device is already
+// waiting for this one.  Every kernel a shard can run is therefore loaded before the shards
+// are connected.
+template <int C>
+int shard_preload()
+{
+  cudaFuncAttributes fa;
+  constexpr int FS = few_work_stages<C>();
+#define PT_LOAD(fn) CU(cudaFuncGetAttributes(&fa, fn))
+  PT_LOAD(tip_encode_kernel); PT_LOAD(tip_encode_batch_kernel); PT_LOAD(shard_allreduce_kernel);
+  PT_LOAD(sum_partials_kernel); PT_LOAD(newton_update_kernel); PT_LOAD(newton_store_lnl_kernel);
+  PT_LOAD(newton_reduce_kernel<false>); PT_LOAD(newton_reduce_kernel<true>);
+  PT_LOAD(pmatrix_kernel<C>); PT_LOAD(partials_kernel<C>); PT_LOAD(partials_kernel_v4<C>);
+  PT_LOAD(edge_lnl_kernel<C>); PT_LOAD(sumtable_kernel<C>);
+  PT_LOAD(nni_prepare_kernel<C>); PT_LOAD(nni_prepare_kernel_v2<C>);
+  PT_LOAD((newton_kernel<C, false>)); PT_LOAD((newton_kernel<C, true>));
+  PT_LOAD((newton_kernel<C, false, FS>)); PT_LOAD((newton_kernel<C, true, FS>));
+  PT_LOAD((newton_sweep_kernel<C, false, false>)); PT_LOAD((newton_sweep_kernel<C, true, false>));
+  PT_LOAD((newton_sweep_kernel<C, true, true>));
+  PT_LOAD((newton_sweep_kernel<C, false, false, FS>)); PT_LOAD((newton_sweep_kernel<C, true, false, FS>));
+  PT_LOAD((newton_sweep_kernel<C, true, true, FS>));
+  PT_LOAD((blo_kernel<C, false>)); PT_LOAD((blo_kernel<C, true>));
+#undef PT_LOAD
+  return PTGPU_OK;
+}
+
 int shard_alloc(ptgpu_engine *e)
 {
   CU(cudaSetDevice(e->device));
@@ -1388,6 +1433,11 @@ int shard_alloc(ptgpu_engine *e)
   CU(cudaMemset(e->d_mailbox, 0, shard_mailbox_bytes()));
   CU(cudaMemset(e->d_seq, 0, sizeof(unsigned long long)));
   *(volatile int *)(e->stg.host + kStgShardErr) = 0;
+  int rc = PTGPU_OK;
+  DISPATCH_CATS(e, rc = shard_preload<C>());
+  if (rc) return rc;
+  if ((rc = blo_prepare_kernel(e))) return rc;
+  if (!e->d_active) CU(PT_MALLOC(e, &e->d_active, 2 * sizeof(unsigned int)));
   CU(cudaDeviceSynchronize());
   return PTGPU_OK;
 }
@@ -1410,6 +1460,7 @@ void shard_close(ptgpu_engine *e)
   for (void *&p : e->ipc_open)
     if (p) { cudaIpcCloseMemHandle(p); p = nullptr; }
   e->comm = ShardComm{};
+  e->same_device_shards = 1;
 }
 
 } // namespace
@@ -1484,7 +1535,13 @@ int ptgpu_comm_init(ptgpu_engine *const *shards, unsigned int nshards)
     }
   for (unsigned int a = 0; a < nshards; ++a)
   {
-    for (unsigned int b = 0; b < nshards; ++b) shards[a]->comm.box[b] = shards[b]->d_mailbox;
+    int same = 0;
+    for (unsigned int b = 0; b < nshards; ++b)
+    {
+      shards[a]->comm.box[b] = shards[b]->d_mailbox;
+      same += shards[b]->device == shards[a]->device;
+    }
+    shards[a]->same_device_shards = same;
     shard_fill(shards[a], a, nshards);
   }
   return PTGPU_OK;
@@ -1706,23 +1763,23 @@ int run_blo(ptgpu_engine *e, const BloRequest &r)
   {
     const size_t nc = std::max<size_t>(chunk, e->lcap_cand), ncl = std::max<size_t>(npriv, e->lcap_clvs),
                  nl = std::max<size_t>(nlen, e->lcap_lens);
-    cudaFree(e->d_lclv); cudaFree(e->d_lscal); cudaFree(e->d_lmat); cudaFree(e->d_lsum); cudaFree(e->d_llens);
-    cudaFree(e->d_lpart); cudaFree(e->d_ltile); cudaFree(e->d_ledges); cudaFree(e->d_lcand); cudaFree(e->d_lnst);
-    cudaFree(e->d_lfin);
+    PT_FREE(e, e->d_lclv); PT_FREE(e, e->d_lscal); PT_FREE(e, e->d_lmat); PT_FREE(e, e->d_lsum); PT_FREE(e, e->d_llens);
+    PT_FREE(e, e->d_lpart); PT_FREE(e, e->d_ltile); PT_FREE(e, e->d_ledges); PT_FREE(e, e->d_lcand); PT_FREE(e, e->d_lnst);
+    PT_FREE(e, e->d_lfin);
     e->d_lclv = e->d_lsum = e->d_lmat = e->d_llens = e->d_lpart = e->d_ltile = nullptr;
     e->d_lscal = nullptr; e->d_ledges = nullptr; e->d_lcand = nullptr; e->d_lnst = nullptr; e->d_lfin = nullptr;
     e->lcap_cand = e->lcap_clvs = e->lcap_lens = 0;
-    CU(cudaMalloc(&e->d_lclv, std::max<size_t>(1, nc * ncl) * stride * sizeof(double)));
-    CU(cudaMalloc(&e->d_lscal, std::max<size_t>(1, nc * ncl) * e->dev.scaler_stride * sizeof(unsigned int)));
-    CU(cudaMalloc(&e->d_lmat, nc * nl * e->cats * 16 * sizeof(double)));
-    CU(cudaMalloc(&e->d_lsum, nc * stride * sizeof(double)));
-    CU(cudaMalloc(&e->d_llens, nc * nl * sizeof(double)));
-    CU(cudaMalloc(&e->d_lpart, 2 * nc * e->nchunks * 3 * sizeof(double)));
-    CU(cudaMalloc(&e->d_ltile, nc * e->ntiles * sizeof(double)));
-    CU(cudaMalloc(&e->d_ledges, nc * 2 * sizeof(BloEdge)));
-    CU(cudaMalloc(&e->d_lcand, nc * sizeof(BloCand)));
-    CU(cudaMalloc(&e->d_lnst, 2 * nc * sizeof(NewtonState)));
-    CU(cudaMalloc(&e->d_lfin, nc * sizeof(int)));
+    CU(PT_MALLOC(e, &e->d_lclv, std::max<size_t>(1, nc * ncl) * stride * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_lscal, std::max<size_t>(1, nc * ncl) * e->dev.scaler_stride * sizeof(unsigned int)));
+    CU(PT_MALLOC(e, &e->d_lmat, nc * nl * e->cats * 16 * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_lsum, nc * stride * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_llens, nc * nl * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_lpart, 2 * nc * e->nchunks * 3 * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_ltile, nc * e->ntiles * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_ledges, nc * 2 * sizeof(BloEdge)));
+    CU(PT_MALLOC(e, &e->d_lcand, nc * sizeof(BloCand)));
+    CU(PT_MALLOC(e, &e->d_lnst, 2 * nc * sizeof(NewtonState)));
+    CU(PT_MALLOC(e, &e->d_lfin, nc * sizeof(int)));
     e->lcap_cand = nc; e->lcap_clvs = ncl; e->lcap_lens = nl;
   }
   if ((rc = ensure(&e->d_lsteps, &e->lcap_steps, (size_t)nsteps * chunk))) return rc;
