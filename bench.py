@@ -195,18 +195,25 @@ class RefWorker:
             p.traversal_update(pidx, True)
         return time.perf_counter() - t0
 
-    def run_pass(self):
+    def run_pass(self, limit=None, keep=None):
+        """one pass over the candidates (the first `limit`, or those with index in `keep`);
+        self.ops counts the CLV operations the reference's TraversalUpdate ran
+        (lib/libptpll/src/pll_partition.cpp:348-393: its return value, summed)"""
         if self.radius > 0:
             return self.run_pass_neighborhood()
         p = self.p
+        self.ops = 0
+        self.scores = {}
         t0 = time.perf_counter()
-        p.traversal_update(p.root, True)
-        for (pidx, kind, _, _, l0) in self.cands:
+        self.ops += len(p.traversal_update(p.root, True))
+        for i, (pidx, kind, _, _, l0) in enumerate(self.cands):
+            if (limit is not None and i >= limit) or (keep is not None and i not in keep):
+                continue
             p.nni(pidx, kind)
             p.invalidate_edge(pidx)
-            p.traversal_update(pidx, False)
-            p.optimize_branch(pidx)
-            p.loglikelihood(pidx)
+            self.ops += len(p.traversal_update(pidx, False))
+            length = p.optimize_branch(pidx)
+            self.scores[i] = (length, p.loglikelihood(pidx))
             p.update_branch_length(pidx, l0)
             p.nni(pidx, kind)
             p.invalidate_edge(pidx)
@@ -247,6 +254,62 @@ def cpu_baseline_single(taxa, sites_full, aln_sample, tree, sample_sites, radius
                 raw_candidates_per_s_at_sample=ncand / best)
 
 
+def parity_at_full_size(e, tree, aln, cand_rows, plan_rows, scores, n, S, k):
+    """The compiled reference (oracle/_ref/libpllref.so, one thread, one ~16 GB partition at
+    64 x 1M) on the bench's own tree and FULL alignment, outside every timed region: k candidates
+    spread over the list scored with SingleBranchOptimizer::EvaluateMove's call sequence, and the
+    per-site scaler counts of every directional CLV the batch used that the reference's FULL
+    traversal also produces.  Index arithmetic beyond 2^31 bytes per buffer is exactly what a
+    size-independent property cannot vouch for."""
+    from oracle.pyoracle import RefLib, have_ref
+    if not have_ref():
+        return dict(skipped="oracle/_ref/libpllref.so missing (build() needs /root/reference)")
+    labels = tree.labels()
+    t0 = time.perf_counter()
+    try:
+        w = RefWorker(RefLib(), tree.newick(), labels, [bytes(aln[l]) for l in labels], 0)
+    except MemoryError as exc:
+        return dict(skipped="MemoryError: %s" % exc)
+    keep = sorted(set(int(x) for x in np.linspace(0, len(cand_rows) - 1, k)))
+    w.run_pass(keep=set(keep))
+    lens, lnls, _ = scores
+    rel_lnl = max(abs(lnls[i] - w.scores[i][1]) / abs(w.scores[i][1]) for i in keep)
+    rel_len = max(abs(lens[i] - w.scores[i][0]) / max(1.0, abs(w.scores[i][0])) for i in keep)
+    # scaler counts: the reference's CLV of an inner node after a FULL traversal towards the
+    # root is the directional CLV of the record that faces the root
+    p = w.p
+    p.traversal_update(p.root, True)
+    recs = p.records()
+    have = set(int(r[0]) for r in plan_rows)
+    facing = []
+
+    def post(r):
+        if r.is_tip:
+            return
+        post(r.next.back)
+        post(r.next.next.back)
+        facing.append(r)
+
+    post(tree.root.back)
+    post(tree.root)
+    compared, mismatched, total = 0, 0, 0
+    for r in facing:
+        if r.node_index not in have:
+            continue
+        ref = p.scaler(recs[r.node_index]["scaler"])
+        got = e.get_scaler(r.node_index - n)
+        compared += 1
+        mismatched += int(not np.array_equal(ref, got))
+        total += int(ref.sum(dtype=np.int64))
+    w.close()
+    ok = rel_lnl <= 1e-9 and rel_len <= 1e-6 and mismatched == 0 and compared > 0
+    return dict(sites=S, candidates_compared=len(keep), candidate_indices=keep, max_rel_lnl=rel_lnl,
+                max_rel_len=rel_len, scaler_buffers_compared=compared, scaler_buffers_mismatched=mismatched,
+                scaler_sum=total, scaler_sum_equal=mismatched == 0, passed=bool(ok),
+                reference="oracle/_ref/libpllref.so (the reference compiled in place), 1 thread",
+                seconds=time.perf_counter() - t0)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -275,10 +338,40 @@ def run_reference(args):
             dt = time.perf_counter() - t0
             if i >= args.warmup:
                 step_s.append(dt)
-    for w in workers:
+    ops_per_pass = sum(getattr(w, "ops", 0) for w in workers)
+    # one thread alone on the sample (what a core does without its neighbours' memory traffic)
+    alone = min(workers[0].run_pass() for _ in range(2))
+    for w in workers[1:]:
         w.close()
     total = sum(step_s)
-    value = ncand * len(step_s) / total * sample / args.sites
+    sampled = ncand * len(step_s) / total * sample / args.sites
+    # the extrapolation checked, not assumed: ONE thread at the FULL site count (the same
+    # config as the GPU arm: 16 GB partition at 64 x 1M) on a bounded share of the candidates
+    full = None
+    if args.radius == 0 and args.sites > sample and not args.no_full_size_check:
+        try:
+            aln_full = simulate(base, args.sites, np.random.default_rng(SEED_ALN))
+            t0 = trees[0]
+            wf = RefWorker(R, t0.newick(), t0.labels(), [bytes(aln_full[l]) for l in t0.labels()], 0)
+            k = min(len(wf.cands), args.full_size_candidates)
+            t_full = wf.run_pass(limit=k)
+            ops_full = wf.ops
+            wf.close()
+            # the same share on the sample, alone, for the per-site ratio
+            t_small = min(workers[0].run_pass(limit=k) for _ in range(2))
+            per_site_full, per_site_small = t_full / args.sites, t_small / sample
+            full = dict(sites=args.sites, threads=1, candidates=k, seconds=t_full,
+                        candidates_per_s=k / t_full,
+                        clv_site_updates_per_s=ops_full * args.sites / t_full,
+                        per_site_cost_full_over_sample=per_site_full / per_site_small,
+                        note="FULL traversal + the first %d candidates of one tree; the same on the %d-site sample "
+                             "took %.3f s" % (k, sample, t_small))
+        except MemoryError as exc:   # a 16 GB partition did not fit this host
+            full = dict(skipped="MemoryError: %s" % exc)
+    workers[0].close()
+    # value = the sampled all-core figure, corrected by the measured cost of a site at full size
+    scale = full["per_site_cost_full_over_sample"] if full and "seconds" in full else 1.0
+    value = sampled / scale
     line = dict(metric="nni_candidates_scored_per_s", value=value, unit="candidates/s",
                 impl="reference", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                 ms_per_step=1e3 * total / len(step_s), higher_is_better=True, scaling="weak",
@@ -289,7 +382,14 @@ def run_reference(args):
                             taxa=args.taxa, sites=args.sites, rate_cats=4),
                 cpu_baseline=dict(value=value, unit="candidates/s", cores=T, kind="reference",
                                   sample=f"{T} threads x one tree ({ncand // T} candidates) x {sample} "
-                                         f"of {args.sites} sites per step, scaled by sites ratio"),
+                                         f"of {args.sites} sites per step, scaled by the sites ratio and by the "
+                                         f"measured per-site cost at the full size ({scale:.3f}x the sample's)"),
+                # Sum of TraversalUpdate's ops_count x sites / time, all threads
+                clv_site_updates_per_s=ops_per_pass * len(step_s) * sample / total / scale,
+                sampled_all_cores=dict(value_scaled_by_sites_ratio_only=sampled, threads=T, sites_per_thread=sample,
+                                       one_thread_alone_s_per_pass=alone,
+                                       all_threads_s_per_pass=total / len(step_s)),
+                full_size_one_thread=full, same_config=bool(full and "seconds" in full),
                 e2e=dict(value=value, unit="candidates/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line))
 
@@ -421,6 +521,13 @@ def run_ours(args):
         t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_s = float(t[0]), float(t[1])
+    # parity at the headline size against the compiled reference, outside the timed regions
+    parity = None
+    if rank == 0 and world == 1 and args.radius == 0 and weights is None and not args.no_parity_at_size:
+        parity = parity_at_full_size(e, tree, aln, cand_rows, plan_rows, out, n, S,
+                                     max(3, min(args.full_size_candidates, 8)))
+        if "passed" in parity and not parity["passed"]:
+            raise SystemExit("parity at the full size FAILED against the reference: " + json.dumps(parity))
     # BASELINE configs[2] after the main timed region, in the same run: the same alignment with
     # its SITES sharded over the N GPUs, one tree visited (full-tree lnL + OptimizeAllBranches)
     sharded = None
@@ -503,6 +610,8 @@ def run_ours(args):
                  note="raw alignment in pinned host memory uploaded + encoded every step"),
         lnl_checksum=float(np.sum(lnls)),
     )
+    if parity is not None:
+        line["parity_at_size"] = parity
     if sharded is not None:
         line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
@@ -539,10 +648,10 @@ def run_ptw_ds1(args):
                     moves = int(line.split()[3])
             return dt, good, ntested, moves
 
-    ours = os.path.join(ROOT, "oracle", "_ref", "gpu", "ptw_batched")
+    ours = os.path.join(ROOT, "pt_b200", "bin", "ptw_batched")
     ref = os.path.join(ROOT, "oracle", "_ref", "ptw_threads")
     if not os.path.exists(ours):
-        raise SystemExit("oracle/_ref/gpu/ptw_batched is not built (needs /root/reference at build time)")
+        raise SystemExit("pt_b200/bin/ptw_batched is not built (make -C pt_b200/host drivers REF=<pt checkout>)")
     sampler = ClockSampler(0)
     sampler.start()
     W = max(1, args.wanderers)
@@ -814,6 +923,12 @@ def main():
                          "BranchNeighborhoodOptimizer semantics (BASELINE configs[1]'s tester)")
     ap.add_argument("--cpu-sample-sites", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-full-size-check", action="store_true",
+                    help="reference arm: skip the one-thread run at the full site count")
+    ap.add_argument("--full-size-candidates", type=int, default=24,
+                    help="reference arm / parity at size: candidates the reference scores at the full site count")
+    ap.add_argument("--no-parity-at-size", action="store_true",
+                    help="skip the comparison with the compiled reference at the full site count")
     ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1", "sharded"])
     ap.add_argument("--compress-patterns", action="store_true",
                     help="score the alignment's unique columns with weights (SURVEY 8f-4; not the headline)")

@@ -329,7 +329,10 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
   e->nheavy = (sites + kHeavyTile - 1) / kHeavyTile;
-  e->chunk_tiles = std::min(32u, std::max(1u, e->ntiles / 128u));
+  // Reduction units of every sum over sites: chunks of <= 8 tiles, at least ~768 of them on a long
+  // alignment, so that ONE branch's sweep (B = 1: OptimizeBranch, every Newton step of a whole-tree
+  // optimisation) still spreads over all SMs with several CTAs each.  A function of `sites` only.
+  e->chunk_tiles = std::min(8u, std::max(1u, e->ntiles / 768u));
   e->nchunks = (e->ntiles + e->chunk_tiles - 1) / e->chunk_tiles;
   const size_t clv_stride = (size_t)sites * rate_cats * 4;
 #define CU_NEW(call)                                                                    \
@@ -755,13 +758,16 @@ bool few_long_items(const ptgpu_engine *e, unsigned int work, unsigned int chunk
 template <int C>
 int launch_newton(ptgpu_engine *e, NewtonArgs &a)
 {
-  const unsigned int work = std::max(1u, a.B * a.nchunks);
   const unsigned int maxg = coop_grid_share(e, (unsigned int)(e->coop_blocks_per_sm * e->sm_count));
+  // work items of ~32 tiles when there are plenty (a batch of candidates), single chunks when
+  // one branch has to fill the device
+  a.group = std::max(1u, std::min(32u / std::max(1u, a.chunk_tiles), a.B * a.nchunks / (4u * maxg)));
+  const unsigned int work = std::max(1u, a.B * ((a.nchunks + a.group - 1) / a.group));
   const unsigned int grid = std::min(work, maxg);
   void *params[] = {&a};
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);
-    if (few_long_items(e, work, a.chunk_tiles))
+    if (few_long_items(e, work, a.chunk_tiles * a.group))
     {
       constexpr int FS = few_work_stages<C>();
       void *fn = a.want_lnl ? (void *)newton_kernel<C, true, FS> : (void *)newton_kernel<C, false, FS>;

@@ -378,6 +378,38 @@ __device__ __forceinline__ double block_sum(double v, double *smem /* >= THREADS
   return t;
 }
 
+// N CTA-wide sums at once: the same reduction tree per value as block_sum (so the same bits),
+// but one pair of CTA barriers for all N instead of one pair each.  smem >= N * THREADS/32.
+// Results valid in thread 0.
+template <int THREADS, int N>
+__device__ __forceinline__ void block_sum_n(double (&v)[N], double *smem)
+{
+  constexpr int W = THREADS / 32 < 1 ? 1 : THREADS / 32;
+#pragma unroll
+  for (int k = 0; k < N; ++k)
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v[k] = __dadd_rn(v[k], __shfl_down_sync(0xffffffffu, v[k], d));
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0)
+  {
+#pragma unroll
+    for (int k = 0; k < N; ++k) smem[k * W + w] = v[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 32)
+  {
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+    {
+      double t = (threadIdx.x < THREADS / 32) ? smem[k * W + threadIdx.x] : 0.0;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) t = __dadd_rn(t, __shfl_down_sync(0xffffffffu, t, d));
+      v[k] = t;
+    }
+  }
+  __syncthreads();
+}
+
 // Tip encoding: raw alignment characters -> 4-bit state masks through a
 // 256-entry table (pll_map_nt semantics, LIBPLL/maps.c:46-64); the position
 // of the first illegal character (if any) is reported through *bad.
@@ -1131,6 +1163,9 @@ struct NewtonArgs
   NewtonState *st;          // [B]
   double *partials;         // [B][nchunks][3]: d1, d2 and (if want_lnl) lnL sums per chunk
   unsigned int sites, B, ntiles, chunk_tiles, nchunks, max_iter;
+  // the cooperative kernel hands out `group` consecutive chunks of a branch per work item (a
+  // scheduling unit only: partials stay per chunk, so results do not depend on it)
+  unsigned int group;
   double eps, lambda;
   int want_lnl;
   int mode;                 // 0: Partition::OptimizeBranch, 1: pllmod_opt_minimize_newton
@@ -1274,22 +1309,22 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
   constexpr int T = kSitesPerPass * C;
   cg::grid_group grid = cg::this_grid();
   extern __shared__ __align__(16) double ring[];
-  __shared__ double red[T / 32 < 1 ? 1 : T / 32];
-  const unsigned int nwork = a.B * a.nchunks;
+  __shared__ double red[3 * (T / 32 < 1 ? 1 : T / 32)];
+  const unsigned int group = a.group ? a.group : 1u;
+  const unsigned int ngroups = (a.nchunks + group - 1) / group;
+  const unsigned int nwork = a.B * ngroups;
   const int cat = threadIdx.x % C;
 
-  for (unsigned int it = 0; it < a.max_iter; ++it)
-  {
-    for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
+  // one sweep of the chunks [c0, c1) of branch e at its current length; FINAL: lnL only
+  auto sweep_item = [&](unsigned int e, unsigned int c0, unsigned int c1, bool final_pass) {
+    double dg[4][3];
+    diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
+    const bool with_lnl = LNL && (final_pass || __ldcg(&a.st[e].try_lnl));
+    for (unsigned int chunk = c0; chunk < c1; ++chunk)
     {
-      const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
-      if (__ldcg(&a.st[e].done)) continue;
-      double dg[4][3];
-      diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
       double out[3] = {0.0, 0.0, 0.0};
       LnlProd lp;
       const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-      const bool with_lnl = LNL && __ldcg(&a.st[e].try_lnl);
       if (with_lnl)
         sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                               a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
@@ -1297,31 +1332,47 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
       else
         sweep_chunk<C, false, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
                                chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
-      const double s1 = block_sum<T>(out[0], red);
-      const double s2 = block_sum<T>(out[1], red);
-      const double s3 = LNL ? block_sum<T>(with_lnl ? lp.value() : 0.0, red) : 0.0;
-      if (threadIdx.x == 0)
+      double *dst = a.partials + ((size_t)e * a.nchunks + chunk) * 3;
+      if (LNL)
       {
-        a.partials[(size_t)w * 3 + 0] = s1;
-        a.partials[(size_t)w * 3 + 1] = s2;
-        if (LNL) a.partials[(size_t)w * 3 + 2] = s3;
+        double s[3] = {out[0], out[1], with_lnl ? lp.value() : 0.0};
+        block_sum_n<T, 3>(s, red);
+        if (threadIdx.x == 0)
+        {
+          if (!final_pass) { dst[0] = s[0]; dst[1] = s[1]; }
+          dst[2] = s[2];
+        }
       }
+      else
+      {
+        double s[2] = {out[0], out[1]};
+        block_sum_n<T, 2>(s, red);
+        if (threadIdx.x == 0) { dst[0] = s[0]; dst[1] = s[1]; }
+      }
+    }
+  };
+
+  for (unsigned int it = 0; it < a.max_iter; ++it)
+  {
+    for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
+    {
+      const unsigned int e = w / ngroups, g = w % ngroups;
+      if (__ldcg(&a.st[e].done)) continue;
+      sweep_item(e, g * group, min((g + 1) * group, a.nchunks), false);
     }
     grid.sync();
     for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
     {
       if (__ldcg(&a.st[e].done)) continue;
-      double a1 = 0.0, a2 = 0.0, a3 = 0.0;
+      double s[3] = {0.0, 0.0, 0.0};
       for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
       {
-        a1 = __dadd_rn(a1, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 0));
-        a2 = __dadd_rn(a2, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 1));
-        if (LNL) a3 = __dadd_rn(a3, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 2));
+        s[0] = __dadd_rn(s[0], __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 0));
+        s[1] = __dadd_rn(s[1], __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 1));
+        if (LNL) s[2] = __dadd_rn(s[2], __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 2));
       }
-      a1 = block_sum<T>(a1, red);
-      a2 = block_sum<T>(a2, red);
-      if (LNL) a3 = block_sum<T>(a3, red);
-      if (threadIdx.x == 0) newton_scalar_update(a, e, a1, a2, a3);
+      block_sum_n<T, 3>(s, red);
+      if (threadIdx.x == 0) newton_scalar_update(a, e, s[0], s[1], s[2]);
     }
     grid.sync();
     int active = 0;
@@ -1337,18 +1388,9 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
   if (!__syncthreads_or(pending)) return;   // uniform over the grid: every CTA reads the same flags
   for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
   {
-    const unsigned int e = w / a.nchunks, chunk = w % a.nchunks;
+    const unsigned int e = w / ngroups, g = w % ngroups;
     if (__ldcg(&a.st[e].lnl_valid)) continue;
-    double dg[4][3];
-    diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
-    double out[3] = {0.0, 0.0, 0.0};
-    LnlProd lp;
-    const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
-    sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
-                              a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
-                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
-    const double sm = block_sum<T>(lp.value(), red);
-    if (threadIdx.x == 0) a.partials[(size_t)w * 3 + 2] = sm;
+    sweep_item(e, g * group, min((g + 1) * group, a.nchunks), true);
   }
   grid.sync();
   for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)

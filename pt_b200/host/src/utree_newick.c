@@ -1,12 +1,13 @@
 /*
- * oracle/refglue/utree_newick.c  --  TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ * pt_b200/host/src/utree_newick.c -- the host build's unrooted-Newick reader.
  *
- * The reference's unrooted-Newick reader is a bison/flex pair
- * (LIBPLL/parse_utree.y, LIBPLL/lex_utree.l); neither tool exists in this
- * image, so the six entry points that live in the bison file are restated here
- * by hand as a recursive-descent reader over the reference's own pll_unode_t /
- * pll_utree_t types (this file is compiled against /root/reference's pll.h and
- * linked ONLY into oracle/_ref artefacts).
+ * The reference's reader is a bison/flex pair (LIBPLL/parse_utree.y,
+ * LIBPLL/lex_utree.l); a build without those tools needs the six entry points
+ * that live in the bison file from somewhere, so they are written here by hand
+ * as a recursive-descent reader over libpll's public pll_unode_t / pll_utree_t
+ * types (compiled against libpll's pll.h; host-only pointer work, no likelihood
+ * code).  The ptw drivers of this repository link it; so does the in-place
+ * build of the reference that serves as test oracle (oracle/Makefile.ref).
  *
  * Behaviour followed (citations into /root/reference/lib/libptpll/lib/
  * pll-modules/libs/libpll/src/):

@@ -3,7 +3,7 @@
 reference (oracle/_ref/ptw_threads, built by oracle/Makefile.ref) at --threads 1.
 
 Run here (needs /root/reference at build time); the GPU tests compare
-oracle/_ref/gpu/ptw_threads_gpu (same pt sources, GPU-backed Partition) with the
+pt_b200/bin/ptw_threads_gpu (same pt sources, GPU-backed Partition) with the
 file this writes: tests/golden/ptw_golden.json.  Lines are compared SORTED:
 their order in the output is cuckoo-table iteration order.
 """

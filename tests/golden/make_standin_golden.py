@@ -23,18 +23,23 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 sys.path.insert(0, HERE)
 
 from make_ptw_golden import summarise  # noqa: E402
-from pytree import Tree, random_tree_newick  # noqa: E402
-import synth  # noqa: E402
+from pt_b200.pytree import Tree, random_tree_newick  # noqa: E402
+from pt_b200 import synth  # noqa: E402
 
 DATA = os.path.join(HERE, "data", "standins")
 # published shapes: name -> (taxa, sites, walk arguments)
+CONFIG2 = ["--lnl-offset", "-5", "--optimization-radius", "1"]   # BASELINE configs[1]'s own flags
 SETS = {
+    "DS2": (29, 2520, CONFIG2),
     "DS3": (36, 1812, ["--lnl-offset", "-2", "--optimization-radius", "1"]),
+    "DS4": (41, 1137, CONFIG2),
+    "DS5": (50, 378, ["--lnl-offset", "-1", "--optimization-radius", "1"]),
     "DS6": (50, 1133, ["--lnl-offset", "-2", "--optimization-radius", "0"]),
+    "DS7": (59, 1824, CONFIG2),
     "DS8": (64, 1008, ["--lnl-offset", "-1.5", "--optimization-radius", "0"]),
 }
 

@@ -89,6 +89,69 @@ def test_config5_deep_tree_scalers_bit_exact_vs_oracle(oracle, alpha, mean_len):
         e.close()
 
 
+@pytest.mark.parametrize("alpha,mean_len", [(0.134946, 0.05), (0.05, 0.3)])
+def test_config5_full_size_every_scaler_and_lnl_vs_oracle(oracle, alpha, mean_len):
+    """BASELINE configs[4] at its FULL size, 1000 taxa x 50,000 sites, compared with the oracle
+    directly (~50 M site-updates, seconds on one core): EVERY one of the 998 scaler buffers
+    integer-identical, the two root-edge CLVs bit-identical (given the oracle's P matrices), the
+    per-site lnL within 2 ulp with libpll's -inf sites reproduced, the sum within 1e-12; also at
+    alpha = 0.05 with long branches (scaler counts >> 1)"""
+    from pt_b200.engine import ops_array
+    taxa, sites = 1000, 50000
+    rates = gamma_rates(alpha)
+    tree, aln, e = build(taxa, sites, 4242, mean_len, rates)
+    try:
+        ops, midx, mlen = tree.full_traversal()
+        ev, iv, el = oracle.eigen_gtr(FREQS, SUBST)
+        pm = {i: oracle.pmatrix(el, ev, iv, rates, t) for i, t in tree.branches().items()}
+        for i, m in pm.items():
+            e.set_pmatrix(i, m)
+        e.update_partials(ops_array(ops))
+        tip_of = {tip.clv_index: tip for tip in tree.nodes[:taxa]}
+        clv, scal = {}, {}
+        root, rb = tree.root, tree.root.back
+        keep = {root.clv_index, rb.clv_index}
+        deepest, total = 0, 0
+
+        def fetch(c):
+            if c in tip_of:
+                return oracle.tip_clv(bytes(aln[tip_of[c].label]), 4)
+            return clv[c] if c in keep else clv.pop(c)   # every inner CLV is consumed once
+
+        for op in ops:
+            pc, ps, c1, m1, s1, c2, m2, s2 = op
+            clv[pc], sc = oracle.update_partial(sites, 4, fetch(c1), fetch(c2), pm[m1], pm[m2],
+                                                scal.get(s1), scal.get(s2))
+            scal[ps] = sc
+            got = e.get_scaler(ps)
+            assert np.array_equal(got, sc), f"scaler buffer {ps}"
+            deepest = max(deepest, int(sc.max()))
+            total += int(sc.sum(dtype=np.int64))
+            for s_ in (s1, s2):
+                if s_ >= 0 and s_ not in (root.scaler_index, rb.scaler_index):
+                    scal.pop(s_, None)
+        assert len(ops) == taxa - 2
+        assert deepest >= (3 if alpha < 0.1 else 1), deepest
+        if not rb.is_tip:
+            assert sha(e.get_clv(rb.clv_index)) == sha(clv[rb.clv_index])
+        assert sha(e.get_clv(root.clv_index)) == sha(clv[root.clv_index])
+        lnl, ps = e.edge_loglikelihood(root.clv_index, root.scaler_index, rb.clv_index,
+                                       rb.scaler_index, root.pmatrix_index, persite=True)
+        rbclv = clv[rb.clv_index] if not rb.is_tip else oracle.tip_clv(bytes(aln[rb.label]), 4)
+        ref, rps = oracle.edge_lnl(sites, 4, clv[root.clv_index], scal.get(root.scaler_index), rbclv,
+                                   scal.get(rb.scaler_index), pm[root.pmatrix_index], FREQS, persite=True)
+        assert np.array_equal(np.isinf(ps), np.isinf(rps))
+        fin = np.isfinite(rps)
+        assert ulp_diff(ps[fin], rps[fin]) <= 2
+        if np.isfinite(ref):
+            assert abs(lnl - ref) <= 1e-12 * abs(ref)
+        else:
+            assert lnl == ref
+        print(f"1000 x 50000, alpha {alpha}: scaler sum {total}, deepest count {deepest}, lnL {lnl!r}")
+    finally:
+        e.close()
+
+
 def test_config5_full_size_pulley_and_idempotence():
     """1000 taxa x 50,000 sites on the device: lnL agrees from three different edges (pulley
     principle) within 1e-9, and recomputing the traversal reproduces the same bits"""

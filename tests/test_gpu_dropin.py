@@ -16,15 +16,16 @@ sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
 pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-GPU = os.path.join(ROOT, "oracle", "_ref", "gpu")
+GPU = os.path.join(ROOT, "oracle", "_ref", "gpu")   # the reference's Catch suites (test infrastructure)
+BIN = os.path.join(ROOT, "pt_b200", "bin")          # the product's ptw drivers
 
 
 def need(name):
-    p = os.path.join(GPU, name)
+    p = os.path.join(BIN if name.startswith("ptw_") else GPU, name)
     if not os.path.exists(p):
         # the binaries are built where /root/reference is mounted and travel to the GPU box with
         # the snapshot: on a GPU box their absence is a broken build, not a reason to skip
-        msg = f"{p} not built (oracle/Makefile.gpu needs /root/reference at build time)"
+        msg = f"{p} not built (pt_b200/host/Makefile drivers / oracle/Makefile.gpu need a pt checkout at build time)"
         if os.environ.get("PTGPU_ALLOW_MISSING_DROPIN"):
             pytest.skip(msg)
         pytest.fail(msg)

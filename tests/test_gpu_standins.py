@@ -26,9 +26,9 @@ with open(os.path.join(HERE, "golden", "standin_golden.json")) as _f:
 def test_walk_tables_equal_the_reference_s(name):
     from make_ptw_golden import summarise
     from make_standin_golden import run
-    exe = os.path.join(ROOT, "oracle", "_ref", "gpu", "ptw_batched")
+    exe = os.path.join(ROOT, "pt_b200", "bin", "ptw_batched")
     if not os.path.exists(exe):
-        pytest.skip("oracle/_ref/gpu/ptw_batched not built (needs /root/reference at build time)")
+        pytest.fail("pt_b200/bin/ptw_batched not built (pt_b200/host/Makefile drivers needs a pt checkout at build time)")
     gold = GOLD[name]
     got = summarise(run(exe, name, gold["args"]))
     assert got["counts"] == gold["counts"]
