@@ -447,6 +447,7 @@ def run_ours(args):
         e.set_tip_states_batch(tip_ids, tip_ptrs)
 
     upload_tips()
+    e_sumtable_doubles = e.batch_sumtable_doubles()
     br = tree.branches()
     midx = np.array(list(br.keys()), dtype=np.uint32)
     mlen = np.array(list(br.values()), dtype=np.float64)
@@ -550,12 +551,13 @@ def run_ours(args):
     final_sweeps = c1["final_sweeps"] - c0["final_sweeps"]
     peak, peak_kind = measured_peak()
     child_bytes = sum((1 if c < n else 132) for row in cand_rows for c in (row[2][2], row[2][5], row[3][2], row[3][5]))
+    st_bytes = 8 * e_sumtable_doubles     # a candidate's sumtable: 128 B/site, or 104 (compact)
     algo = dict(
         partials=op_bytes(plan_rows, n, S),                                  # per launch
-        nni_prepare=(child_bytes + ncand * 132) * S,                          # per launch
-        # per launch: every derivative sweep reads the candidate's sumtable (128 B/site); the
-        # sweeps that also sum the site lnL read the scaler word too; rare extra lnL-only sweeps
-        newton=(passes * 128 + lnl_sweeps * 4 + final_sweeps * 132) / steps * S,
+        nni_prepare=(child_bytes + ncand * (st_bytes + 4)) * S,               # per launch
+        # per launch: every derivative sweep reads the candidate's sumtable; the sweeps that
+        # also sum the site lnL read the scaler word too; rare extra lnL-only sweeps
+        newton=(passes * st_bytes + lnl_sweeps * 4 + final_sweeps * (st_bytes + 4)) / steps * S,
     )
     if prog is not None:
         # the persistent local-optimisation kernel (timed under the "newton" slot): per

@@ -371,6 +371,13 @@ int ptgpu_get_pmatrix(ptgpu_engine *e, unsigned int matrix_index, double *out);
 int ptgpu_set_pmatrix(ptgpu_engine *e, unsigned int matrix_index, const double *in);
 int ptgpu_get_sumtable(ptgpu_engine *e, double *out);
 
+/* doubles per site of the sumtables ptgpu_score_nni_batch keeps per candidate: 4 x rate_cats
+   (the layout of pll_update_sumtable), or 3 x rate_cats + 1 when the model has a zero
+   eigenvalue (every reversible model) -- that column multiplies exp(0) = 1 in every Newton
+   evaluation (LIBPLL/core_derivatives.c:560-575) and is folded into one double per site.
+   What bench.py's algorithmic byte count of a Newton sweep is based on. */
+unsigned int ptgpu_batch_sumtable_doubles(ptgpu_engine *e);
+
 /* counters since create: [0] kernel launches, [1] CLV site-updates,
    [2] Newton derivative passes (site sweeps), [3] NNI candidates scored,
    [4] batch sweeps that also summed the site log-likelihoods (they read the

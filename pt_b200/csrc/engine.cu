@@ -154,6 +154,11 @@ struct ptgpu_engine
   int partials_version = 4; // PTGPU_PARTIALS=3 selects the register-resident-matrix walker
   double lnl_margin = 100.0; // PTGPU_LNL_MARGIN
   int prepare_version = 2;  // PTGPU_PREPARE=1 selects the register-resident-matrix prepare kernel
+  // batched NNI scoring keeps compact sumtables (13 instead of 16 doubles per site: the column of
+  // the model's zero eigenvalue folded into one double per site, kernels.cuh); PTGPU_COMPACT_SUMTABLE=0
+  // turns it off; zero_col = -1 if the model has no (numerically) zero eigenvalue
+  bool compact_sumtable = true;
+  int zero_col = -1;
   // optional per-kernel timing (ptgpu_set_profiling): CUDA events on e->stream
   bool profiling = false;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> pending;
@@ -323,6 +328,7 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   if (const char *pv = getenv("PTGPU_PARTIALS")) e->partials_version = atoi(pv);
   if (const char *pv = getenv("PTGPU_PREPARE")) e->prepare_version = atoi(pv);
   if (const char *pv = getenv("PTGPU_LNL_MARGIN")) e->lnl_margin = atof(pv);
+  if (const char *pv = getenv("PTGPU_COMPACT_SUMTABLE")) e->compact_sumtable = atoi(pv) != 0;
   if (const char *pv = getenv("PTGPU_BLO_CLUSTER_WORK")) e->blo_cluster_work = (unsigned int)atoi(pv);
   if (const char *pv = getenv("PTGPU_BLO_MAX_CHUNK")) e->blo_max_chunk = (unsigned int)atoi(pv);
   e->tips = tips; e->clv_buffers = clv_buffers; e->sites = sites; e->cats = rate_cats;
@@ -438,6 +444,17 @@ int ptgpu_set_model(ptgpu_engine *e, const double freqs[4], const double subst[6
   for (unsigned int c = 0; c < kMaxCats; ++c) m.rates[c] = c < e->cats ? category_rates[c] : 0.0;
   m.rate_weight = 1.0 / e->cats;
   m.log_scale_thr = std::log(1.0 / std::ldexp(1.0, 256));
+  // the eigenvalue 0 of a reversible model comes out of the QL iteration as ~1e-17 (its exact
+  // value is 0): exp(lambda r t) is 1.0 to within 1e-15 for every length an optimiser can reach
+  {
+    double big = 0.0;
+    for (int j = 0; j < 4; ++j) big = std::max(big, std::fabs(m.evals[j]));
+    e->zero_col = -1;
+    int hits = 0;
+    for (int j = 0; j < 4; ++j)
+      if (std::fabs(m.evals[j]) <= 1e-12 * big) { e->zero_col = j; ++hits; }
+    if (hits != 1) e->zero_col = -1;
+  }
   e->model_set = true;
   return PTGPU_OK;
 }
@@ -1112,10 +1129,16 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     if (!(cands[i].length0 >= 0)) return fail(PTGPU_ERR_ARG, "candidate %u: bad start length", i);
   }
   CU(cudaSetDevice(e->device));
-  const size_t stride = e->dev.clv_stride;
+  // compact sumtables: tile-blocked, 3 C + 1 doubles per site (never more than the full form's
+  // 4 C except on alignments shorter than a tile)
+  const int compact = (e->compact_sumtable && e->zero_col >= 0 && e->prepare_version != 1) ? e->zero_col + 1 : 0;
+  const size_t stride = std::max(e->dev.clv_stride,
+                                 compact ? (size_t)e->ntiles * kTileSites * (3 * e->cats + 1) : (size_t)0);
   // candidates are processed in chunks whose sumtables fit the scratch budget
+  // chunk partials: one per chunk, or one per chunk and WARP for the site-per-thread sweep
+  const size_t nparts = std::max<size_t>(e->ntiles, (size_t)e->nchunks * 16);
   const size_t per_cand = stride * sizeof(double) + (size_t)e->sites * sizeof(unsigned int) +
-                          (size_t)e->ntiles * 3 * sizeof(double) + sizeof(NewtonState) + sizeof(DevGroup);
+                          nparts * 3 * sizeof(double) + sizeof(NewtonState) + sizeof(DevGroup);
   size_t chunk = count;
   if (chunk > e->bcap)
   {
@@ -1138,7 +1161,7 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
     CU(PT_MALLOC(e, &e->d_bsum, chunk * stride * sizeof(double)));
     CU(PT_MALLOC(e, &e->d_bsclr, chunk * (size_t)e->sites * sizeof(unsigned int)));
     CU(PT_MALLOC(e, &e->d_bstate, chunk * sizeof(NewtonState)));
-    CU(PT_MALLOC(e, &e->d_bpartials, chunk * (size_t)e->ntiles * 3 * sizeof(double)));
+    CU(PT_MALLOC(e, &e->d_bpartials, chunk * nparts * 3 * sizeof(double)));
     CU(PT_MALLOC(e, &e->d_bcands, chunk * sizeof(DevGroup)));
     e->bcap = chunk;
   }
@@ -1211,10 +1234,11 @@ int ptgpu_score_nni_batch(ptgpu_engine *e, const ptgpu_nni_candidate_t *cands,
                            e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr))); }
       else
       { DISPATCH_CATS(e, (nni_prepare_kernel_v2<C><<<e->nheavy * ng, kHeavySites * C, sizeof(PrepSmem2<C>), e->stream>>>(
-                           e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr))); }
+                           e->dev, e->model, e->d_bcands, ng, e->d_bsum, stride, e->d_bsclr, compact))); }
     }
     CU(cudaGetLastError());
     NewtonArgs a{};
+    a.compact = compact;
     a.m = e->model;
     a.sumtables = e->d_bsum;
     a.entry_stride = stride;
@@ -1343,6 +1367,13 @@ int ptgpu_get_sumtable(ptgpu_engine *e, double *out)
   CU(cudaMemcpyAsync(out, e->d_sumtable, e->dev.clv_stride * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   return PTGPU_OK;
+}
+
+unsigned int ptgpu_batch_sumtable_doubles(ptgpu_engine *e)
+{
+  if (!e) return 0;
+  const bool compact = e->compact_sumtable && e->zero_col >= 0 && e->prepare_version != 1;
+  return compact ? 3 * e->cats + 1 : 4 * e->cats;
 }
 
 int ptgpu_get_counters(ptgpu_engine *e, unsigned long long out[6])

@@ -1073,6 +1073,168 @@ __device__ __forceinline__ void sweep_tile(const ModelConst &m, const double *su
   sweep_tile_compute<C, WITH_LNL>(m, sv, scv, sites, tile, dg, out, lp, vec_end);
 }
 
+// ---- compact sumtables (batched NNI scoring) ------------------------------------------
+// A reversible model has one eigenvalue 0 (numerically ~1e-17): column z of the sumtable then
+// multiplies exp(0) = 1 in L and (numerically) nothing in L' and L'', whatever the branch
+// length.  The batch path stores, per candidate, only the three other columns per (site,
+// category) plus ONE double per site, Z = sum over categories of column z -- 13 instead of 16
+// doubles per site and Newton evaluation (LIBPLL/core_derivatives.c:560-575 is where the
+// reference multiplies by these constants every time).  Layout, per tile of kTileSites sites:
+//   [3 planes][kTileSites][C] doubles, then [kTileSites] doubles of Z
+// so a warp reads 32 consecutive doubles per plane.  L = (sum over categories of the three-term
+// sums) + Z differs from the 16-double form only by the association of one addition per site.
+template <int C>
+__host__ __device__ constexpr size_t compact_tile_doubles() { return (size_t)kTileSites * (3 * C + 1); }
+
+__device__ __forceinline__ double ld64_stream(const double *p)
+{
+  double v;
+  asm volatile("ld.global.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+
+template <int C, bool WITH_LNL>
+__device__ __forceinline__ void sweep_tile_compact(const ModelConst &m, const double *sumtable,
+                                                   const unsigned int *sclr, unsigned int sites,
+                                                   unsigned int tile, const double (&dg)[4][3], int zero_col,
+                                                   double out[3], LnlProd &lp, unsigned long long vec_end)
+{
+  constexpr int NQ = 3;
+  const int cat = threadIdx.x % C;
+  const unsigned int lsite0 = threadIdx.x / C;
+  const double *base = sumtable + (size_t)tile * compact_tile_doubles<C>();
+  const unsigned int last = sites - 1 - tile * kTileSites;   // local index of the last valid site (if in this tile)
+  double sv[kPasses][3];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+    const unsigned int ls = min(lsite0 + ps * kSitesPerPass, last);
+#pragma unroll
+    for (int p = 0; p < 3; ++p) sv[ps][p] = ld64_stream(base + (size_t)p * kTileSites * C + (size_t)ls * C + cat);
+  }
+  unsigned int scv[kPasses];
+  load_scaler_words<C, WITH_LNL>(sclr, sites, tile, scv);
+  // the three live columns' constants, in column order
+  double dc[3][3];
+#pragma unroll
+  for (int p = 0; p < 3; ++p)
+  {
+    const int j = p + (p >= zero_col ? 1 : 0);
+#pragma unroll
+    for (int q = 0; q < 3; ++q) dc[p][q] = j == 1 ? dg[1][q] : (j == 2 ? dg[2][q] : (j == 3 ? dg[3][q] : dg[0][q]));
+  }
+  double ck[kPasses][NQ];
+#pragma unroll
+  for (int ps = 0; ps < kPasses; ++ps)
+  {
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+    {
+      double a = __dadd_rn(0.0, __dmul_rn(sv[ps][0], dc[0][q]));
+      a = __dadd_rn(a, __dmul_rn(sv[ps][1], dc[1][q]));
+      ck[ps][q] = __dadd_rn(a, __dmul_rn(sv[ps][2], dc[2][q]));
+    }
+  }
+  const double *zp = base + (size_t)3 * kTileSites * C;
+  const unsigned int site0 = tile * kTileSites + lsite0;
+  const unsigned int full =
+      vec_end == ~0ull ? sites / 4 * 4 : (unsigned int)min((unsigned long long)sites, vec_end);
+  if (C == 4)
+  {
+    double r[NQ];
+    quad_transpose_sum<NQ>(ck, cat, r);
+    const unsigned int lsite = lsite0 + quad_pass(cat) * kSitesPerPass;
+    const double z = ld64_stream(zp + min(lsite, last));
+    const unsigned int site = tile * kTileSites + lsite;
+    if (site < sites)
+    {
+      r[0] = __dadd_rn(r[0], z);
+      double terma = 0.0;
+      if (WITH_LNL) { terma = __dmul_rn(r[0], m.rate_weight); if (!(terma > 0.0)) terma = terma != terma ? terma : 0.0; }
+      site_terms<WITH_LNL>(m, r, terma, site, full, scv[0], out, lp);
+    }
+  }
+  else
+  {
+#pragma unroll
+    for (int ps = 0; ps < kPasses; ++ps)
+    {
+      const unsigned int site = site0 + ps * kSitesPerPass;
+      double lk[NQ];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) lk[q] = ck[ps][q];
+#pragma unroll
+      for (int k = 1; k < C; ++k)
+#pragma unroll
+        for (int q = 0; q < NQ; ++q)
+          lk[q] = __dadd_rn(lk[q], __shfl_down_sync(0xffffffffu, ck[ps][q], k, C));
+      if (cat == 0 && site < sites)
+      {
+        lk[0] = __dadd_rn(lk[0], ld64_stream(zp + (lsite0 + ps * kSitesPerPass)));
+        double terma = 0.0;
+        if (WITH_LNL) { terma = __dmul_rn(lk[0], m.rate_weight); if (!(terma > 0.0)) terma = terma != terma ? terma : 0.0; }
+        site_terms<WITH_LNL>(m, lk, terma, site, full, scv[ps], out, lp);
+      }
+    }
+  }
+}
+
+// Compact sumtables, C = 4, one SITE per thread: the layout keeps a site's four categories next
+// to each other, so a thread fetches a whole plane entry with one 32-byte load (3 x LDG.256 + one
+// double of Z per site instead of 13 8-byte loads over four lanes), needs no shuffle for the
+// category sums, and every lane carries a site through the division.  The 36 constants of the
+// evaluation (4 categories x 3 live columns x {e, lr e, lr^2 e}) are read from shared memory
+// (`cst`, broadcast).  Per-site arithmetic is that of sweep_tile_compact, term for term.
+template <bool WITH_LNL>
+__device__ __forceinline__ void sweep_tile_sites4(const ModelConst &m, const double *sumtable,
+                                                  const unsigned int *sclr, unsigned int sites,
+                                                  unsigned int tile, const double *cst, double out[3],
+                                                  LnlProd &lp, unsigned long long vec_end)
+{
+  const double *base = sumtable + (size_t)tile * compact_tile_doubles<4>();
+  const unsigned int last = sites - 1 - tile * kTileSites;
+  const unsigned int ls = min((unsigned int)threadIdx.x, last);
+  double sv[3][4];
+#pragma unroll
+  for (int p = 0; p < 3; ++p) ld256_stream(base + (size_t)p * kTileSites * 4 + (size_t)ls * 4, sv[p]);
+  const double z = ld64_stream(base + (size_t)3 * kTileSites * 4 + ls);
+  const unsigned int site = tile * kTileSites + threadIdx.x;
+  unsigned int sc = 0u;
+  if (WITH_LNL && sclr) sc = __ldg(sclr + tile * kTileSites + ls);
+  double pair[2][3];
+#pragma unroll
+  for (int h = 0; h < 2; ++h)
+  {
+    double ck[2][3];
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk)
+    {
+      const int k = 2 * h + kk;
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+      {
+        double a = __dadd_rn(0.0, __dmul_rn(sv[0][k], cst[(k * 3 + 0) * 3 + q]));
+        a = __dadd_rn(a, __dmul_rn(sv[1][k], cst[(k * 3 + 1) * 3 + q]));
+        ck[kk][q] = __dadd_rn(a, __dmul_rn(sv[2][k], cst[(k * 3 + 2) * 3 + q]));
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) pair[h][q] = __dadd_rn(ck[0][q], ck[1][q]);
+  }
+  double lk[3];
+#pragma unroll
+  for (int q = 0; q < 3; ++q) lk[q] = __dadd_rn(pair[0][q], pair[1][q]);
+  lk[0] = __dadd_rn(lk[0], z);
+  if (site < sites)
+  {
+    const unsigned int full =
+        vec_end == ~0ull ? sites / 4 * 4 : (unsigned int)min((unsigned long long)sites, vec_end);
+    double terma = 0.0;
+    if (WITH_LNL) { terma = __dmul_rn(lk[0], m.rate_weight); if (!(terma > 0.0)) terma = terma != terma ? terma : 0.0; }
+    site_terms<WITH_LNL>(m, lk, terma, site, full, sc, out, lp);
+  }
+}
+
 // Streaming form: the tiles [t0, t1) of one sumtable flow through a per-thread
 // ring in shared memory.  Every thread copies ITS OWN entries of the tile that
 // lies kRingStages-1 tiles ahead with cp.async (LDGSTS) and later reads them
@@ -1105,8 +1267,15 @@ __device__ __forceinline__ void sweep_chunk(const ModelConst &m, const double *s
                                             const unsigned int *sclr, unsigned int sites,
                                             unsigned int t0, unsigned int t1, const double (&dg)[4][3],
                                             double *ring, double out[3], LnlProd &lp,
-                                            unsigned long long vec_end)
+                                            unsigned long long vec_end, int compact = 0)
 {
+  if (compact > 0)
+  {
+    // compact sumtable (eigen column compact-1 folded into one double per site): direct loads
+    for (unsigned int tile = t0; tile < t1; ++tile)
+      sweep_tile_compact<C, WITH_LNL>(m, sumtable, sclr, sites, tile, dg, compact - 1, out, lp, vec_end);
+    return;
+  }
   if constexpr (STAGES == 0)
   {
     for (unsigned int tile = t0; tile < t1; ++tile)
@@ -1170,6 +1339,7 @@ struct NewtonArgs
   int want_lnl;
   int mode;                 // 0: Partition::OptimizeBranch, 1: pllmod_opt_minimize_newton
   double xmin, xmax;        // mode 1 bounds
+  int compact;                // k + 1: sumtables are compact with eigen column k folded; 0: full sumtables
   double lnl_margin;          // predictor margin: carry the lnL when predicted |d1| < margin * eps
   unsigned long long vec_end; // ~0: unsharded; else local index where the global scalar tail starts
 };
@@ -1314,9 +1484,61 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
   const unsigned int ngroups = (a.nchunks + group - 1) / group;
   const unsigned int nwork = a.B * ngroups;
   const int cat = threadIdx.x % C;
+  // Compact sumtables with four categories take the site-per-thread sweep; its chunk partials are
+  // PER WARP (written straight after the warp's shuffle tree: no CTA barrier anywhere in a sweep,
+  // so a CTA's loads never drain between chunks), the reduction below sums nchunks x W of them.
+  constexpr int W = T / 32 < 1 ? 1 : T / 32;
+  const bool sites4 = C == 4 && a.compact > 0;
+  const unsigned int nparts = sites4 ? a.nchunks * W : a.nchunks;
+  __shared__ double cst[36];
+
+  auto sweep_item_sites4 = [&](unsigned int e, unsigned int c0, unsigned int c1, bool final_pass) {
+    __syncthreads();   // the previous work item's constants are no longer read
+    if (threadIdx.x < 4)
+    {
+      double dg[4][3];
+      diag_regs<C>(a.m, __ldcg(&a.st[e].len), threadIdx.x, dg);
+#pragma unroll
+      for (int p = 0; p < 3; ++p)
+      {
+        const int j = p + (p >= a.compact - 1 ? 1 : 0);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          cst[(threadIdx.x * 3 + p) * 3 + q] = j == 1 ? dg[1][q] : (j == 2 ? dg[2][q] : (j == 3 ? dg[3][q] : dg[0][q]));
+      }
+    }
+    __syncthreads();
+    const bool with_lnl = LNL && (final_pass || __ldcg(&a.st[e].try_lnl));
+    const double *table = a.sumtables + (size_t)e * a.entry_stride;
+    const unsigned int *sclr = a.sclr ? a.sclr + (size_t)e * a.sites : nullptr;
+    for (unsigned int chunk = c0; chunk < c1; ++chunk)
+    {
+      double out[3] = {0.0, 0.0, 0.0};
+      LnlProd lp;
+      const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
+      if (with_lnl)
+        for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+          sweep_tile_sites4<true>(a.m, table, sclr, a.sites, tile, cst, out, lp, a.vec_end);
+      else
+        for (unsigned int tile = chunk * a.chunk_tiles; tile < t1; ++tile)
+          sweep_tile_sites4<false>(a.m, table, nullptr, a.sites, tile, cst, out, lp, a.vec_end);
+      double v[3] = {out[0], out[1], (LNL && with_lnl) ? lp.value() : 0.0};
+#pragma unroll
+      for (int k = 0; k < (LNL ? 3 : 2); ++k)
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v[k] = __dadd_rn(v[k], __shfl_down_sync(0xffffffffu, v[k], d));
+      if ((threadIdx.x & 31) == 0)
+      {
+        double *dst = a.partials + (((size_t)e * a.nchunks + chunk) * W + (threadIdx.x >> 5)) * 3;
+        if (!final_pass) { dst[0] = v[0]; dst[1] = v[1]; }
+        if (LNL) dst[2] = v[2];
+      }
+    }
+  };
 
   // one sweep of the chunks [c0, c1) of branch e at its current length; FINAL: lnL only
   auto sweep_item = [&](unsigned int e, unsigned int c0, unsigned int c1, bool final_pass) {
+    if (sites4) { sweep_item_sites4(e, c0, c1, final_pass); return; }
     double dg[4][3];
     diag_regs<C>(a.m, __ldcg(&a.st[e].len), cat, dg);
     const bool with_lnl = LNL && (final_pass || __ldcg(&a.st[e].try_lnl));
@@ -1328,10 +1550,10 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
       if (with_lnl)
         sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                               a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
-                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
+                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end, a.compact);
       else
         sweep_chunk<C, false, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
-                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
+                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end, a.compact);
       double *dst = a.partials + ((size_t)e * a.nchunks + chunk) * 3;
       if (LNL)
       {
@@ -1352,55 +1574,56 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
     }
   };
 
-  for (unsigned int it = 0; it < a.max_iter; ++it)
+  // One loop for the Newton iterations and the (rare) final lnL-only pass, so that the sweep
+  // code has a single call site and inlines (the arguments stay in the parameter bank).
+  bool final_pass = false;
+  for (unsigned int it = 0;; ++it)
   {
     for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
     {
       const unsigned int e = w / ngroups, g = w % ngroups;
-      if (__ldcg(&a.st[e].done)) continue;
-      sweep_item(e, g * group, min((g + 1) * group, a.nchunks), false);
+      if (final_pass ? __ldcg(&a.st[e].lnl_valid) : __ldcg(&a.st[e].done)) continue;
+      sweep_item(e, g * group, min((g + 1) * group, a.nchunks), final_pass);
     }
     grid.sync();
     for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
     {
-      if (__ldcg(&a.st[e].done)) continue;
+      if (final_pass ? __ldcg(&a.st[e].lnl_valid) : __ldcg(&a.st[e].done)) continue;
       double s[3] = {0.0, 0.0, 0.0};
-      for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
+      for (unsigned int t = threadIdx.x; t < nparts; t += T)
       {
-        s[0] = __dadd_rn(s[0], __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 0));
-        s[1] = __dadd_rn(s[1], __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 1));
-        if (LNL) s[2] = __dadd_rn(s[2], __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 2));
+        if (!final_pass)
+        {
+          s[0] = __dadd_rn(s[0], __ldcg(a.partials + ((size_t)e * nparts + t) * 3 + 0));
+          s[1] = __dadd_rn(s[1], __ldcg(a.partials + ((size_t)e * nparts + t) * 3 + 1));
+        }
+        if (LNL) s[2] = __dadd_rn(s[2], __ldcg(a.partials + ((size_t)e * nparts + t) * 3 + 2));
       }
       block_sum_n<T, 3>(s, red);
-      if (threadIdx.x == 0) newton_scalar_update(a, e, s[0], s[1], s[2]);
+      if (threadIdx.x == 0)
+      {
+        if (!final_pass)
+          newton_scalar_update(a, e, s[0], s[1], s[2]);
+        else
+        {
+          a.st[e].lnl = s[2];
+          a.st[e].lnl_valid = 1;
+          a.st[e].final_sweeps = 1;
+        }
+      }
     }
+    if (final_pass) break;
     grid.sync();
     int active = 0;
     for (unsigned int e = threadIdx.x; e < a.B; e += T) active |= !__ldcg(&a.st[e].done);
-    if (!__syncthreads_or(active)) break;
-  }
-
-  if (!LNL) return;
-  // branches that stopped somewhere else than at the last evaluated length
-  // (second negative step, iteration limit): one more sweep at the final length
-  int pending = 0;
-  for (unsigned int e = threadIdx.x; e < a.B; e += T) pending |= !__ldcg(&a.st[e].lnl_valid);
-  if (!__syncthreads_or(pending)) return;   // uniform over the grid: every CTA reads the same flags
-  for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
-  {
-    const unsigned int e = w / ngroups, g = w % ngroups;
-    if (__ldcg(&a.st[e].lnl_valid)) continue;
-    sweep_item(e, g * group, min((g + 1) * group, a.nchunks), true);
-  }
-  grid.sync();
-  for (unsigned int e = blockIdx.x; e < a.B; e += gridDim.x)
-  {
-    if (__ldcg(&a.st[e].lnl_valid)) continue;
-    double acc = 0.0;
-    for (unsigned int t = threadIdx.x; t < a.nchunks; t += T)
-      acc = __dadd_rn(acc, __ldcg(a.partials + ((size_t)e * a.nchunks + t) * 3 + 2));
-    acc = block_sum<T>(acc, red);
-    if (threadIdx.x == 0) { a.st[e].lnl = acc; a.st[e].lnl_valid = 1; a.st[e].final_sweeps = 1; }
+    if (__syncthreads_or(active) && it + 1 < a.max_iter) continue;
+    if (!LNL) break;
+    // branches that stopped somewhere else than at the last evaluated length (second negative
+    // step, iteration limit): one more sweep at the final length, for the lnL only
+    int pending = 0;
+    for (unsigned int e = threadIdx.x; e < a.B; e += T) pending |= !__ldcg(&a.st[e].lnl_valid);
+    if (!__syncthreads_or(pending)) break;   // uniform over the grid: every CTA reads the same flags
+    final_pass = true;
   }
 }
 
@@ -1430,10 +1653,10 @@ __global__ void __launch_bounds__(kSitesPerPass *C) newton_sweep_kernel(NewtonAr
     if (with_lnl)
       sweep_chunk<C, true, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride,
                               a.sclr ? a.sclr + (size_t)e * a.sites : nullptr, a.sites,
-                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
+                              chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end, a.compact);
     else
       sweep_chunk<C, false, STAGES>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
-                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
+                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end, a.compact);
     const double s1 = block_sum<T>(out[0], red);
     const double s2 = block_sum<T>(out[1], red);
     const double s3 = LNL ? block_sum<T>(with_lnl ? lp.value() : 0.0, red) : 0.0;
@@ -1589,8 +1812,9 @@ template <int C>
 __device__ __forceinline__ void finish_candidate(const DevState &s, const ModelConst &m,
                                                  const double a[4], const double b[4],
                                                  const double c[4], const double d[4],
-                                                 unsigned int cnt, bool store, double *dst,
-                                                 unsigned int *sclr_dst, int cat)
+                                                 unsigned int cnt, bool store, double *table,
+                                                 unsigned int site, unsigned int *sclr_dst, int cat,
+                                                 int compact = -1)
 {
   double pp[4], qq[4];
 #pragma unroll
@@ -1617,9 +1841,36 @@ __device__ __forceinline__ void finish_candidate(const DevState &s, const ModelC
   }
   double sum[4];
   sumtable_entry<C>(m, pp, qq, sum);
+  if (compact >= 0)
+  {
+    // compact form (see sweep_tile_compact): the three live columns in their planes, and the
+    // folded column summed over the site's categories (c0 + c1 + ... in order) by lane cat 0
+    const double zc = compact == 0 ? sum[0] : (compact == 1 ? sum[1] : (compact == 2 ? sum[2] : sum[3]));
+    double z = zc;
+#pragma unroll
+    for (int k = 1; k < C; ++k) z = __dadd_rn(z, __shfl_down_sync(0xffffffffu, zc, k, C));
+    if (store)
+    {
+      double *base = table + (size_t)(site / kTileSites) * compact_tile_doubles<C>();
+      const unsigned int ls = site % kTileSites;
+#pragma unroll
+      for (int p = 0; p < 3; ++p)
+      {
+        const int j = p + (p >= compact ? 1 : 0);
+        base[(size_t)p * kTileSites * C + (size_t)ls * C + cat] =
+            j == 1 ? sum[1] : (j == 2 ? sum[2] : (j == 3 ? sum[3] : sum[0]));
+      }
+      if (cat == 0)
+      {
+        base[(size_t)3 * kTileSites * C + ls] = z;
+        *sclr_dst = cnt + (sp ? 1u : 0u) + (sq ? 1u : 0u);
+      }
+    }
+    return;
+  }
   if (store)
   {
-    st256(dst, sum);
+    st256(table + ((size_t)site * C + cat) * 4, sum);
     if (cat == 0) *sclr_dst = cnt + (sp ? 1u : 0u) + (sq ? 1u : 0u);
   }
 }
@@ -1679,13 +1930,12 @@ __global__ void __launch_bounds__(kHeavySites *C, PT_PREP_MINB)
     const unsigned int ls_raw = lsite0 + ps * kHeavySites;
     const bool ok = ls_raw < nvalid;
     const unsigned int site = site_base + min(ls_raw, nvalid - 1);
-    const size_t eoff = ((size_t)site * C + cat) * 4;
     finish_candidate<C>(s, m, proj[0][ps], proj[1][ps], proj[2][ps], proj[3][ps], cnt[ps], ok,
-                        sumtables + (size_t)gr.out[0] * entry_stride + eoff,
+                        sumtables + (size_t)gr.out[0] * entry_stride, site,
                         sclr + (size_t)gr.out[0] * s.sites + site, cat);
     if (gr.ncand > 1)
       finish_candidate<C>(s, m, proj[3][ps], proj[1][ps], proj[2][ps], proj[0][ps], cnt[ps], ok,
-                          sumtables + (size_t)gr.out[1] * entry_stride + eoff,
+                          sumtables + (size_t)gr.out[1] * entry_stride, site,
                           sclr + (size_t)gr.out[1] * s.sites + site, cat);
   }
 }
@@ -1712,7 +1962,7 @@ template <int C>
 __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 3 : 1))
     nni_prepare_kernel_v2(DevState s, ModelConst m, const DevGroup *__restrict__ groups,
                           unsigned int ngroups, double *sumtables, size_t entry_stride,
-                          unsigned int *sclr)
+                          unsigned int *sclr, int compact)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   PrepSmem2<C> &sm = *reinterpret_cast<PrepSmem2<C> *>(smem_raw);
@@ -1778,14 +2028,13 @@ __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 3 : 1))
       const unsigned int ls_raw = lsite0 + (half + j) * kHeavySites;
       const bool ok = ls_raw < nvalid;
       const unsigned int site = site_base + min(ls_raw, nvalid - 1);
-      const size_t eoff = ((size_t)site * C + cat) * 4;
       finish_candidate<C>(s, m, proj[0][j], proj[1][j], proj[2][j], proj[3][j], cnt[j], ok,
-                          sumtables + (size_t)gr.out[0] * entry_stride + eoff,
-                          sclr + (size_t)gr.out[0] * s.sites + site, cat);
+                          sumtables + (size_t)gr.out[0] * entry_stride, site,
+                          sclr + (size_t)gr.out[0] * s.sites + site, cat, compact - 1);
       if (gr.ncand > 1)
         finish_candidate<C>(s, m, proj[3][j], proj[1][j], proj[2][j], proj[0][j], cnt[j], ok,
-                            sumtables + (size_t)gr.out[1] * entry_stride + eoff,
-                            sclr + (size_t)gr.out[1] * s.sites + site, cat);
+                            sumtables + (size_t)gr.out[1] * entry_stride, site,
+                            sclr + (size_t)gr.out[1] * s.sites + site, cat, compact - 1);
     }
   }
 }

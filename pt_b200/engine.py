@@ -309,6 +309,11 @@ class Engine:
         self._chk(self.lib.ptgpu_get_sumtable(self.h, _d(out)))
         return out
 
+    def batch_sumtable_doubles(self):
+        """doubles per site of a candidate's sumtable in score_nni_batch (16, or 13 compact)"""
+        self.lib.ptgpu_batch_sumtable_doubles.restype = C.c_uint
+        return int(self.lib.ptgpu_batch_sumtable_doubles(self.h))
+
     def counters(self):
         out = (C.c_ulonglong * 6)()
         self._chk(self.lib.ptgpu_get_counters(self.h, out))
