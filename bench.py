@@ -167,8 +167,8 @@ class RefWorker:
     call sequence for every candidate of one tree
     (src/move_tester/single_branch_optimizer.cpp:23-64)"""
 
-    def __init__(self, R, newick, labels, seqs, radius=0):
-        self.p = R.open_mem(newick, labels, seqs, FREQS, SUBST, RATES)
+    def __init__(self, R, newick, labels, seqs, radius=0, rates=None):
+        self.p = R.open_mem(newick, labels, seqs, FREQS, SUBST, RATES if rates is None else rates)
         self.cands = Tree(newick).nni_candidates()
         self.radius = radius
         self.nrec = len(self.p.records())
@@ -235,16 +235,16 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_baseline_single(taxa, sites_full, aln_sample, tree, sample_sites, radius=0):
+def cpu_baseline_single(taxa, sites_full, aln_sample, tree, sample_sites, radius=0, rates=None, limit=None):
     from oracle.pyoracle import RefLib, have_ref
     if not have_ref():
         return None
     R = RefLib()
     labels = tree.labels()
     seqs = [bytes(aln_sample[l][:sample_sites]) for l in labels]
-    w = RefWorker(R, tree.newick(), labels, seqs, radius)
-    times = [w.run_pass() for _ in range(3)]
-    ncand = len(w.cands)
+    w = RefWorker(R, tree.newick(), labels, seqs, radius, rates=rates)
+    times = [w.run_pass(limit=limit) if radius == 0 else w.run_pass() for _ in range(3)]
+    ncand = len(w.cands) if limit is None else min(limit, len(w.cands))
     w.close()
     best = min(times[1:])
     return dict(value=ncand / best * sample_sites / sites_full, unit="candidates/s", cores=1,
@@ -626,6 +626,200 @@ def run_ours(args):
 
 
 # --------------------------------------------------------------------------
+# BASELINE configs[3] and configs[4]: the other named shapes
+# --------------------------------------------------------------------------
+def run_shape(args):
+    """`--workload cand100k`: BASELINE configs[3] -- 64 taxa x 100,000 sites, 10^5 NNI candidates
+    per batch = the 122 candidates of each of 820 parent trees (the seeded NNI walk of SURVEY 8d),
+    parents dealt round-robin to the GPUs, no collective (strong scaling: the batch is the same
+    at every N).  One STEP = the whole batch: per parent P matrices, the directional CLVs its
+    candidates read, and ptgpu_score_nni_batch.
+    `--workload stress1000`: BASELINE configs[4] -- 1000 taxa x 50,000 sites (25.5 GB of
+    directional CLVs, deep traversals, scaler counts; `--alpha 0.05` drives them up): per step
+    and GPU the P matrices, a FULL traversal (998 CLV updates) + the tree's lnL, then the
+    directional CLVs and all 1994 NNI candidates of the tree in one batch (weak scaling: every
+    GPU its own parent tree)."""
+    import torch
+    from pt_b200.engine import Engine, gamma_rates_mean, ops_array
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    stress = args.workload == "stress1000"
+    n = 1000 if stress else 64
+    S = 50000 if stress else 100000
+    parents_total = world if stress else args.parents
+    rates = RATES if args.alpha is None else gamma_rates_mean(args.alpha, 4)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    base = parent_tree(n, 0)
+    aln = simulate(base, S, np.random.default_rng(SEED_ALN))
+    host_aln = torch.empty((n, S), dtype=torch.uint8).pin_memory()
+    for tip in base.nodes[:n]:
+        host_aln[tip.clv_index].copy_(torch.from_numpy(aln[tip.label]))
+    nbuf = 3 * (n - 2)
+    e = Engine(n, nbuf, S, 4, 2 * n - 3, nbuf, device=local)
+    e.set_model(FREQS, SUBST, rates)
+    tip_ids = np.arange(n, dtype=np.uint32)
+    tip_ptrs = [host_aln[t].data_ptr() for t in range(n)]
+    e.set_tip_states_batch(tip_ids, tip_ptrs)
+    st_bytes = 8 * e.batch_sumtable_doubles()
+
+    # this rank's parents: descriptors prepared once (host integer work, like the alignment)
+    work, bytes_partials, bytes_prepare, ncand_rank, full_bytes = [], 0, 0, 0, 0
+    if not stress and args.parents <= 0:
+        # as many parents of the walk as it takes to reach 10^5 candidates (QueueMoves' enumeration
+        # yields up to 2(n-2) per tree, fewer where a node's first record faces a tip)
+        parents_total, total = 0, 0
+        while total < 100000:
+            total += len(parent_tree(n, parents_total).nni_candidates())
+            parents_total += 1
+    for pidx in range(rank, parents_total, world):
+        t = parent_tree(n, pidx)
+        br = t.branches()
+        rows = t.nni_candidates()
+        plan_rows = t.directional_plan(t.referenced_clvs(rows))
+        item = dict(midx=np.array(list(br.keys()), dtype=np.uint32),
+                    mlen=np.array(list(br.values()), dtype=np.float64),
+                    plan=ops_array(plan_rows), cands=cand_array(rows), root=t.root)
+        if stress:
+            ops, _, _ = t.full_traversal()
+            item["full"] = ops_array(ops)
+            full_bytes += op_bytes(ops, n, S) + 268 * S
+        bytes_partials += op_bytes(plan_rows, n, S)
+        child = sum((1 if c < n else 132) for row in rows for c in (row[2][2], row[2][5], row[3][2], row[3][5]))
+        bytes_prepare += (child + len(rows) * (st_bytes + 4)) * S
+        ncand_rank += len(rows)
+        work.append(item)
+    results = {}
+
+    def step():
+        for k, it in enumerate(work):
+            e.update_prob_matrices(it["midx"], it["mlen"])
+            if stress:
+                e.update_partials(it["full"])
+                r, rb = it["root"], it["root"].back
+                results["lnl"] = e.edge_loglikelihood(r.clv_index, r.scaler_index, rb.clv_index,
+                                                      rb.scaler_index, r.pmatrix_index)
+            e.update_partials(it["plan"])
+            results[k] = e.score_nni_batch(it["cands"])
+
+    for _ in range(args.warmup):
+        step()
+    for k in range(len(work)):
+        assert not results[k][2].any() and np.all(np.isfinite(results[k][1]) | np.isneginf(results[k][1]))
+    stream = torch.cuda.ExternalStream(e.stream(), device=torch.device("cuda", local))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e.set_profiling(True)
+    e.kernel_times(reset=True)
+    c0 = e.counters()
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    kt = e.kernel_times(reset=True)
+    c1 = e.counters()
+    e.set_profiling(False)
+    t_e2e = []
+    for i in range(1 + min(args.steps, 2)):
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e.set_tip_states_batch(tip_ids, tip_ptrs)
+        step()
+        torch.cuda.synchronize()
+        if i:
+            t_e2e.append(time.perf_counter() - t0)
+    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
+    e2e_s = sum(t_e2e) / len(t_e2e)
+    tot = torch.tensor([float(ncand_rank), float(c1["site_updates"] - c0["site_updates"])],
+                       dtype=torch.float64, device="cuda")
+    if dist:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ncand_all, site_updates = float(tot[0]), float(tot[1])
+    if rank != 0:
+        if dist:
+            dist.destroy_process_group()
+        return
+    steps = args.steps
+    passes = c1["newton_passes"] - c0["newton_passes"]
+    lnl_sweeps = c1["lnl_sweeps"] - c0["lnl_sweeps"]
+    final_sweeps = c1["final_sweeps"] - c0["final_sweeps"]
+    peak, peak_kind = measured_peak()
+    # rank 0's kernels, totals over the timed steps; algorithmic bytes as in the headline workload
+    algo = dict(partials=(bytes_partials + (full_bytes - 268 * S * len(work) if stress else 0)) * steps,
+                nni_prepare=bytes_prepare * steps,
+                newton=(passes * st_bytes + lnl_sweeps * 4 + final_sweeps * (st_bytes + 4)) * S,
+                edge_lnl=268 * S * len(work) * steps if stress else 0)
+    kernels = {}
+    for k, b in algo.items():
+        k_ms, k_n = kt[k]
+        if k_n:
+            kernels[k] = dict(ms_total_per_step=k_ms / steps, launches_per_step=k_n / steps,
+                              share_of_step=k_ms / ms, achieved_gbs=b / (k_ms * 1e-3) / 1e9,
+                              algorithmic_bytes_per_step=int(b / steps))
+    dom = max(kernels, key=lambda k: kernels[k]["share_of_step"])
+    value = ncand_all * steps / (ms * 1e-3)
+    h2d = n * S + sum(it["midx"].nbytes + it["mlen"].nbytes + it["plan"].nbytes + it["cands"].nbytes
+                      + (it["full"].nbytes if stress else 0) for it in work)
+    name = ("synthetic 1000 taxa x 50000 sites GTR+G4 (BASELINE configs[4]): per step and GPU P matrices, FULL "
+            "traversal (998 CLV updates) + lnL, the directional CLVs and all 1994 NNI candidates of one tree"
+            if stress else
+            f"synthetic 64 taxa x 100000 sites GTR+G4 (BASELINE configs[3]): per step a batch of {int(ncand_all)} NNI "
+            f"candidates = all 122 of each of {parents_total} parent trees (seeded NNI walk), parents dealt "
+            "round-robin to the GPUs")
+    line = dict(metric="nni_candidates_scored_per_s", value=value, unit="candidates/s", n_gpus=world, steps=steps,
+                warmup=args.warmup, ms_per_step=ms / steps, higher_is_better=True,
+                scaling="weak" if stress else "strong", vs_baseline=None, dtype="f64", data="synthetic",
+                config=dict(workload=name, taxa=n, sites=S, rate_cats=4, alpha=args.alpha,
+                            candidates_per_step=int(ncand_all), parents_per_step=parents_total,
+                            parallelism=f"candidate-parallel x{world}",
+                            l2="every parent's CLVs and sumtables (> 1 GB) exceed the 126 MB L2; no flush needed"),
+                clv_site_updates_per_s=site_updates / (ms * 1e-3),
+                newton_iterations_per_candidate=passes / steps / max(1, ncand_rank),
+                gpu_launches=int(c1["launches"] - c0["launches"]), kernels=kernels,
+                roofline=dict(bound="hbm", kernel=dom, achieved=kernels[dom]["achieved_gbs"], peak=peak,
+                              unit="GB/s", frac=kernels[dom]["achieved_gbs"] / peak, peak_source=peak_kind,
+                              traffic=None),
+                clocks=clocks,
+                e2e=dict(value=ncand_all / e2e_s, unit="candidates/s", h2d_bytes_per_step=int(h2d),
+                         d2h_bytes_per_step=int(ncand_rank * 20 + (8 if stress else 0)),
+                         note="raw alignment uploaded + encoded once per step, descriptors per parent; bytes per rank"),
+                lnl_checksum=float(sum(np.sum(results[k][1][np.isfinite(results[k][1])]) for k in range(len(work)))))
+    if stress:
+        line["tree_lnl"] = results["lnl"]
+    if world == 1 and not args.no_cpu_baseline:
+        t0 = parent_tree(n, 0)
+        sample = 1000 if stress else 20000
+        cb = cpu_baseline_single(n, S, aln, t0, sample, 0, rates=rates)
+        if cb:
+            line["cpu_baseline"] = cb
+    print(json.dumps(line))
+    if dist:
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------
 # BASELINE configs[1] on DS1: the real drivers, wall clock
 # --------------------------------------------------------------------------
 def run_ptw_ds1(args):
@@ -931,7 +1125,12 @@ def main():
                     help="reference arm / parity at size: candidates the reference scores at the full site count")
     ap.add_argument("--no-parity-at-size", action="store_true",
                     help="skip the comparison with the compiled reference at the full site count")
-    ap.add_argument("--workload", default="synthetic", choices=["synthetic", "ptw-ds1", "sharded"])
+    ap.add_argument("--workload", default="synthetic",
+                    choices=["synthetic", "ptw-ds1", "sharded", "cand100k", "stress1000"])
+    ap.add_argument("--parents", type=int, default=0,
+                    help="cand100k: parent trees per batch (0 = as many as give 10^5 candidates)")
+    ap.add_argument("--alpha", type=float, default=None,
+                    help="cand100k / stress1000: Gamma shape instead of DS1's 0.134946 (0.05: scaler stress)")
     ap.add_argument("--compress-patterns", action="store_true",
                     help="score the alignment's unique columns with weights (SURVEY 8f-4; not the headline)")
     ap.add_argument("--call-by-call", action="store_true",
@@ -948,6 +1147,11 @@ def main():
             run_ptw_ds1(args)
     elif args.workload == "sharded":
         run_sharded(args)
+    elif args.workload in ("cand100k", "stress1000"):
+        if args.impl == "reference":
+            raise SystemExit("--impl reference covers the default workload and --workload sharded; the other "
+                             "shapes carry the reference as their cpu_baseline leg")
+        run_shape(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

@@ -778,9 +778,10 @@ int launch_newton(ptgpu_engine *e, NewtonArgs &a)
   const unsigned int maxg = coop_grid_share(e, (unsigned int)(e->coop_blocks_per_sm * e->sm_count));
   // work items of ~32 tiles when there are plenty (a batch of candidates), single chunks when
   // one branch has to fill the device
-  a.group = std::max(1u, std::min(32u / std::max(1u, a.chunk_tiles), a.B * a.nchunks / (4u * maxg)));
+  // (the kernel lowers the group size itself when few branches are still running)
+  a.group = std::max(1u, std::min(32u / std::max(1u, a.chunk_tiles), a.B * a.nchunks / (8u * maxg)));
   const unsigned int work = std::max(1u, a.B * ((a.nchunks + a.group - 1) / a.group));
-  const unsigned int grid = std::min(work, maxg);
+  const unsigned int grid = std::min(std::max(1u, a.B * a.nchunks), maxg);
   void *params[] = {&a};
   {
     LaunchScope ls(e, PTGPU_KERNEL_NEWTON);

@@ -1480,9 +1480,12 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
   cg::grid_group grid = cg::this_grid();
   extern __shared__ __align__(16) double ring[];
   __shared__ double red[3 * (T / 32 < 1 ? 1 : T / 32)];
-  const unsigned int group = a.group ? a.group : 1u;
-  const unsigned int ngroups = (a.nchunks + group - 1) / group;
-  const unsigned int nwork = a.B * ngroups;
+  // consecutive chunks per work item: re-chosen every iteration from the number of branches still
+  // running, so that the last iterations of a batch (a handful of slow branches) still spread over
+  // the whole grid.  A scheduling unit only: partials stay per chunk.
+  const unsigned int max_group = a.group ? a.group : 1u;
+  unsigned int group = max_group, ngroups = (a.nchunks + group - 1) / group, nwork = a.B * ngroups;
+  __shared__ unsigned int sh_running;
   const int cat = threadIdx.x % C;
   // Compact sumtables with four categories take the site-per-thread sweep; its chunk partials are
   // PER WARP (written straight after the warp's shuffle tree: no CTA barrier anywhere in a sweep,
@@ -1579,6 +1582,19 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && STAGES <= 3 ? (ST
   bool final_pass = false;
   for (unsigned int it = 0;; ++it)
   {
+    {
+      if (threadIdx.x == 0) sh_running = 0u;
+      __syncthreads();
+      unsigned int mine = 0u;
+      for (unsigned int e = threadIdx.x; e < a.B; e += T)
+        mine += final_pass ? !__ldcg(&a.st[e].lnl_valid) : !__ldcg(&a.st[e].done);
+      if (mine) atomicAdd(&sh_running, mine);
+      __syncthreads();
+      const unsigned int running = sh_running;   // the same in every CTA: flags are stable here
+      group = max(1u, min(max_group, running * a.nchunks / (8u * gridDim.x)));
+      ngroups = (a.nchunks + group - 1) / group;
+      nwork = a.B * ngroups;
+    }
     for (unsigned int w = blockIdx.x; w < nwork; w += gridDim.x)
     {
       const unsigned int e = w / ngroups, g = w % ngroups;

@@ -37,7 +37,7 @@ SETS = {
     "DS2": (29, 2520, CONFIG2),
     "DS3": (36, 1812, ["--lnl-offset", "-2", "--optimization-radius", "1"]),
     "DS4": (41, 1137, CONFIG2),
-    "DS5": (50, 378, ["--lnl-offset", "-1", "--optimization-radius", "1"]),
+    "DS5": (50, 378, ["--lnl-offset", "-0.25", "--optimization-radius", "1"]),
     "DS6": (50, 1133, ["--lnl-offset", "-2", "--optimization-radius", "0"]),
     "DS7": (59, 1824, CONFIG2),
     "DS8": (64, 1008, ["--lnl-offset", "-1.5", "--optimization-radius", "0"]),
