@@ -159,6 +159,26 @@ int ptgpu_compute_edge_loglikelihood(ptgpu_engine *e, unsigned int parent_clv_in
                                      unsigned int matrix_index,
                                      double *persite_lnl, double *lnl_out);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers
+   that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+   that forbid it).  The same computation as ptgpu_compute_edge_loglikelihood (without the
+   per-site output) by the same kernel, but its scratch -- one partial per tile of 256 sites,
+   the arrival counter, the result -- lives in a file-scope `static __device__` array of the
+   library instead of engine-allocated buffers, and the call makes no cudaMalloc / cudaFree /
+   allocating library call.  Limit: engines of at most ptgpu_noalloc_max_sites() = 2,097,152
+   sites (8192 tiles; the array is 64 KiB and every GPU that loads the library holds it until
+   exit); a larger engine gets PTGPU_ERR_ARG, a site shard PTGPU_ERR_STATE.  ALL engines on a
+   device share the one array and it keeps the last call's contents (the call clears the counter
+   word, everything else is overwritten before it is read): calls that overlap on the same GPU
+   race -- issue them one after the other.  The result equals the other entry point's bit for
+   bit (same reduction tree). */
+unsigned int ptgpu_noalloc_max_sites(void);
+int ptgpu_compute_edge_loglikelihood_noalloc(ptgpu_engine *e, unsigned int parent_clv_index,
+                                             int parent_scaler_index,
+                                             unsigned int child_clv_index,
+                                             int child_scaler_index, unsigned int matrix_index,
+                                             double *lnl_out);
+
 /* pll_update_sumtable (LIBPLL/derivatives.c:164-234) into the engine-owned
    device sumtable (PTPLL keeps one scratch sumtable per partition too). */
 int ptgpu_update_sumtable(ptgpu_engine *e, unsigned int parent_clv_index,

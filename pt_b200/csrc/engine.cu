@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -2015,5 +2016,80 @@ extern "C" int ptgpu_optimize_all_branches(ptgpu_engine *e, unsigned int n_prolo
   }
   if (status_out && *status_out)
     return fail(PTGPU_ERR_NOT_FINITE, *status_out == 1 ? "d1 is not finite" : "d2 is not finite");
+  return PTGPU_OK;
+}
+
+// ---- an entry point that allocates nothing --------------------------------------------------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  ptgpu_compute_edge_loglikelihood's kernel needs scratch (one partial per tile of
+// 256 sites, the arrival counter of its fixed-order finish, the result): here that scratch is a
+// file-scope device array of a fixed, modest size that every GPU loading this library holds until
+// exit.  The array's NAME is only a host-side stand-in in host code; the address a kernel can use
+// comes from cudaGetSymbolAddress, taken once per device with that device current.
+namespace {
+
+constexpr unsigned int kNoAllocMaxTiles = 8192;                        // 8192 x 256 = 2,097,152 sites
+constexpr unsigned int kNoAllocMaxSites = kNoAllocMaxTiles * kTileSites;
+// [0, kNoAllocMaxTiles): tile partials; [kNoAllocMaxTiles]: the result; [kNoAllocMaxTiles + 1]: the counter word
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocMaxTiles + 2];
+
+std::mutex g_noalloc_mutex;
+double *g_noalloc_ptr[64] = {};   // per device: device address of g_noalloc_scratch
+
+int noalloc_setup(int device, double **out)
+{
+  if (device < 0 || device >= 64) return fail(PTGPU_ERR_ARG, "no-alloc entry point: device %d out of range", device);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[device])
+  {
+    void *p = nullptr;
+    CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));   // the current device's copy of the array
+    g_noalloc_ptr[device] = static_cast<double *>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return PTGPU_OK;
+}
+
+} // namespace
+
+extern "C" unsigned int ptgpu_noalloc_max_sites(void) { return kNoAllocMaxSites; }
+
+extern "C" int ptgpu_compute_edge_loglikelihood_noalloc(ptgpu_engine *e, unsigned int parent_clv_index,
+                                                        int parent_scaler_index, unsigned int child_clv_index,
+                                                        int child_scaler_index, unsigned int matrix_index,
+                                                        double *lnl_out)
+{
+  if (!e || !lnl_out) return fail(PTGPU_ERR_ARG, "ptgpu_compute_edge_loglikelihood_noalloc: null argument");
+  if (!e->model_set) return fail(PTGPU_ERR_STATE, "model not set");
+  if (e->sites > kNoAllocMaxSites || e->ntiles > kNoAllocMaxTiles)
+    return fail(PTGPU_ERR_ARG, "ptgpu_compute_edge_loglikelihood_noalloc: %u sites exceed the fixed scratch "
+                               "(at most %u sites); use ptgpu_compute_edge_loglikelihood", e->sites, kNoAllocMaxSites);
+  if (is_sharded(e))
+    return fail(PTGPU_ERR_STATE, "ptgpu_compute_edge_loglikelihood_noalloc: not available on a site shard");
+  int rc;
+  if ((rc = check_clv(e, parent_clv_index, "edge_lnl.parent"))) return rc;
+  if ((rc = check_clv(e, child_clv_index, "edge_lnl.child"))) return rc;
+  if ((rc = check_scaler(e, parent_scaler_index, "edge_lnl.parent"))) return rc;
+  if ((rc = check_scaler(e, child_scaler_index, "edge_lnl.child"))) return rc;
+  if ((rc = check_matrix(e, matrix_index, "edge_lnl"))) return rc;
+  CU(cudaSetDevice(e->device));
+  double *scratch = nullptr;
+  if ((rc = noalloc_setup(e->device, &scratch))) return rc;
+  double *partials = scratch, *result = scratch + kNoAllocMaxTiles;
+  unsigned int *counter = reinterpret_cast<unsigned int *>(scratch + kNoAllocMaxTiles + 1);
+  // the array keeps the last call's contents: the arrival counter must start at zero (the kernel
+  // re-arms it, but a call that was cut short would not have); partials and result are overwritten
+  CU(cudaMemsetAsync(counter, 0, sizeof(double), e->stream));
+  e->counters[0]++;
+  e->kernel_launches[PTGPU_KERNEL_EDGE_LNL]++;
+  DISPATCH_CATS(e, (edge_lnl_kernel<C><<<e->ntiles, kSitesPerPass * C, 0, e->stream>>>(
+                       e->dev, e->model, parent_clv_index, parent_scaler_index, child_clv_index,
+                       child_scaler_index, matrix_index, nullptr, partials, counter, result)));
+  CU(cudaGetLastError());
+  // the engine's pinned staging page (allocated when the engine was created) receives the result
+  CU(cudaMemcpyAsync(e->stg.host + kStgResult, result, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  *lnl_out = *(volatile double *)(e->stg.host + kStgResult);
   return PTGPU_OK;
 }
