@@ -132,34 +132,55 @@ class Partition
 
   // ---- visits computed ahead of time (pt_b200/host/ptw/visit_prefetcher) ----
   //
-  // Wanderer::MoveForward visits every move it queued: clone the tree with the move applied,
-  // OptimizeAllBranches, LogLikelihood (src/wanderer.cpp:150-210).  The result is a pure
-  // function of that tree, so it can be computed as soon as the move is queued, on another
-  // engine, while the wanderer goes on.  A Replica() is such an engine (same alignment, model
-  // and mode, tips copied on the device, no batch buffers); PublishVisit() registers the
-  // pending result of OptimizeAllBranches for the tree with the given fingerprint, and
-  // OptimizeAllBranches() of a non-replica partition takes a registered result instead of
-  // computing it: it writes the optimised lengths into the tree and marks every CLV stale, so
-  // the PARTIAL traversal + LogLikelihood the caller does next recompute CLVs and score with
-  // the same kernels on the same lengths -- bit-identical to having optimised here.
+  // Wanderer::MoveForward visits every move it queued: apply the NNI, InvalidateEdgeClvs, clone,
+  // OptimizeAllBranches, LogLikelihood (src/wanderer.cpp:150-210).  What that OptimizeAllBranches
+  // computes is a function of three things only: the partition's CLV / P-matrix CONTENT when it
+  // starts, the tree (topology + lengths) and the tree's per-record orientation flags -- the
+  // reference starts it from the PARENT tree's CLVs with just the two ends of the NNI edge
+  // flagged invalid, so the CLVs between that edge and the root are stale on purpose, and the
+  // result depends on it.  The content is known exactly at the two moments that matter: after a
+  // FULL TraversalUpdate and after an OptimizeAllBranches it is "the exact CLVs of that tree at
+  // those lengths, oriented at that root" (every stale CLV has been recomputed by then).  So a
+  // visit can be computed ahead of time on another engine that is put into the same state (FULL
+  // traversal of the parent tree, same flags), and is then bit-identical to the one the
+  // wanderer would have run: VisitKey() names the start state, PublishVisit() registers a
+  // pending result under it, and OptimizeAllBranches() of a non-replica partition takes a
+  // registered result whose key matches its own present state instead of computing -- it writes
+  // the optimised lengths into the tree and brings the CLVs up with one FULL traversal, which
+  // is the state the computation would have left.  Any other start state simply finds nothing
+  // registered and is computed in place.
   struct VisitResult {
     std::vector<double> lengths;   // by node_index of every record of the tree
   };
-  std::unique_ptr<Partition> Replica() const;
+  // `directional`: with the buffers ScoreNniNeighborhood needs (4x the CLV memory)
+  std::unique_ptr<Partition> Replica(bool directional = false) const;
   bool is_replica() const { return is_replica_; }
   // order-independent hash of (node_index, back->node_index, length) over all records
   static uint64_t TreeFingerprint(const pll_utree_t* tree);
-  static void PublishVisit(uint64_t fingerprint, std::shared_future<VisitResult> result);
-  static bool VisitKnown(uint64_t fingerprint);
+  // "the exact CLVs of the tree with this fingerprint, oriented at record `root_index`"
+  static uint64_t ExactContentId(uint64_t tree_fingerprint, unsigned int root_index);
+  // key of OptimizeAllBranches(root) started from content `content_id` on the tree `root`
+  // belongs to, flags included (0 if the tree cannot be traversed)
+  static uint64_t VisitKeyFor(uint64_t content_id, pll_unode_t* root, unsigned int node_count);
+  // the same for this partition's present content; 0 when that is not known exactly
+  uint64_t VisitKey(pll_unode_t* root) const;
+  static void PublishVisit(uint64_t key, std::shared_future<VisitResult> result);
+  static bool VisitKnown(uint64_t key);
   static void ClearVisits();
   // (visits served from the registry, visits computed here) since process start
   static std::pair<unsigned long long, unsigned long long> VisitStatistics();
+  // device memory one Replica() of this partition takes, roughly
+  size_t ReplicaBytes(bool directional = false) const;
 
  private:
   int device_;
   unsigned int directional_base_;  // first extra CLV / scaler buffer (0 = none allocated)
   bool stepwise_all_branches_ = false;  // PTGPU_STEPWISE_ALL_BRANCHES: one engine call per step (A/B testing)
   bool is_replica_ = false;
+  // what the per-node CLVs and the P matrices hold, when that is known exactly
+  // (ExactContentId); 0 = unknown
+  uint64_t content_id_ = 0;
+  uint64_t content_fp_ = 0;   // TreeFingerprint of the tree content_id_ was formed from
 
   // all engines of this partition; shards_[0] == engine_, shard s holds the sites
   // [shard_begin_[s], shard_begin_[s + 1]) of the alignment
@@ -175,9 +196,9 @@ class Partition
   void DestroyEngines();
 
   struct ReplicaTag {};
-  Partition(const Partition& proto, ReplicaTag);
+  Partition(const Partition& proto, ReplicaTag, bool directional);
   uint64_t FingerprintFrom(pll_unode_t* root);
-  bool TakePublishedVisit(pll_unode_t* root);
+  bool TakePublishedVisit(uint64_t key, pll_unode_t* root);
 
   void SetTipStates(pll_utree_t* tree, const std::vector<std::string>& labels,
                     const std::vector<std::string>& sequences);

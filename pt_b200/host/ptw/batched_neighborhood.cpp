@@ -65,7 +65,9 @@ std::pair<bool, double> BatchedNeighborhood::EvaluateMove(pll::Partition& partit
     // partition's per-node CLVs, the tree and its orientation flags stay as they
     // are (the batch works on directional and private buffers), which is the
     // state the reference's testers restore before they return.
-    scores->moves = partition.ScoreNniNeighborhood(tree, radius_);
+    // (a background worker may already have scored this very tree: visit_prefetcher.hpp)
+    if (!VisitPrefetcher::Instance().TakeNeighborhood(tree, &scores->moves))
+      scores->moves = partition.ScoreNniNeighborhood(tree, radius_);
     scores->tree = tree;
     scores->fingerprint = fp;
     std::lock_guard<std::mutex> lock(mutex_);
@@ -75,14 +77,9 @@ std::pair<bool, double> BatchedNeighborhood::EvaluateMove(pll::Partition& partit
     if (m.node == node && m.type == static_cast<int>(type)) {
       // testing only: the score is not reported to the authority here
       const bool accept = m.lnl >= authority.GetThresholdScore();
-      if (accept && VisitPrefetcher::Instance().enabled()) {
-        // the wanderer will visit this move if the authority grants it (src/wanderer.cpp:262-272):
-        // start that visit now, on the tree the move leads to (applied and undone as
-        // Guru::RequestMove does, src/guru.cpp:219-244)
-        pll_utree_nni(node, static_cast<int>(type), nullptr);
-        VisitPrefetcher::Instance().Submit(partition, tree);
-        pll_utree_nni(node, static_cast<int>(type), nullptr);
-      }
+      // the wanderer will visit this move if the authority grants it (src/wanderer.cpp:262-272):
+      // start that visit now, on another engine (the wanderer's tree is not touched; never throws)
+      if (accept) VisitPrefetcher::Instance().Submit(partition, tree, node, static_cast<int>(type), authority);
       return std::make_pair(accept, m.lnl);
     }
   }

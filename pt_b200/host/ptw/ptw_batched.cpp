@@ -7,6 +7,7 @@
 // neighbourhood in one engine call instead of one move at a time.  Everything else
 // (option parsing, guru, wanderers, authority, tables) is pt's own code, linked
 // unchanged.
+#include <algorithm>
 #include <cstdio>
 #include <exception>
 #include <fstream>
@@ -56,10 +57,14 @@ int Run(int argc, const char* argv[])
     options.move_tester = batched;
   }
 
-  // visits of queued moves ahead of time: opt-in (PTGPU_PREFETCH_VISITS=n workers), because the
-  // scores then agree with the reference's only to the optimiser's own tolerance, not to the
-  // last printed digit (pt_b200/host/ptw/visit_prefetcher.hpp)
-  if (batched) pt::move_tester::VisitPrefetcher::Instance().Start(0);
+  // visits of queued moves ahead of time (pt_b200/host/ptw/visit_prefetcher.hpp: bit-identical
+  // to the in-place visit, tables line for line).  Worth it for few wanderers, whose visits would
+  // otherwise run one after the other; PTGPU_PREFETCH_VISITS=n overrides, 0 turns it off.
+  if (batched) {
+    const size_t threads = std::max<size_t>(1, options.thread_count);
+    pt::move_tester::VisitPrefetcher::Instance().Start(threads == 1 ? 6 : (threads <= 4 ? 2 : 0),
+                                                       options.optimization_radius);
+  }
 
   TreeSet input;
   input.trees = pt::pll::ParseMultiNewick(options.newick_path);
@@ -82,8 +87,12 @@ int Run(int argc, const char* argv[])
 
   if (pt::move_tester::VisitPrefetcher::Instance().enabled()) {
     const auto visits = pt::pll::Partition::VisitStatistics();
-    std::fprintf(stderr, "visits ahead of time: %llu submitted, %llu taken by OptimizeAllBranches, %llu computed in place\n",
-                 pt::move_tester::VisitPrefetcher::Instance().submitted(), visits.first, visits.second);
+    pt::move_tester::VisitPrefetcher& pf = pt::move_tester::VisitPrefetcher::Instance();
+    std::fprintf(stderr, "visits ahead of time: %llu submitted (%llu declined), %llu taken by OptimizeAllBranches, "
+                         "%llu computed in place; %llu neighbourhoods scored ahead, %llu visits queued by workers "
+                         "walking ahead\n",
+                 pf.submitted(), pf.declined(), visits.first, visits.second, pf.neighborhoods_taken(),
+                 pf.walked_ahead());
   }
   pt::move_tester::VisitPrefetcher::Instance().Shutdown();   // before the partitions and the CUDA runtime go
   if (batched) {

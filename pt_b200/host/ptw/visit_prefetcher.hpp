@@ -1,39 +1,53 @@
-// pt_b200/host/ptw/visit_prefetcher.hpp -- the visits of queued moves, computed in the
-// background.
+// pt_b200/host/ptw/visit_prefetcher.hpp -- the visits of queued moves, computed ahead of time
+// (SURVEY 8f-1).
 //
 // Wanderer::QueueMoves (src/wanderer.cpp:242-285) queues every move that passes its test and
-// Wanderer::MoveForward (:150-210) later visits each of them: clone the tree with the move
-// applied, Partition::OptimizeAllBranches, LogLikelihood.  On a small alignment such a visit
-// is a chain of several thousand dependent device phases (6-10 ms on 8 CTAs) and the walk
-// spends most of its time waiting for them one after the other.  The visit of a queued move
-// depends on nothing but the tree it leads to, so BatchedNeighborhood hands that tree to this
-// class the moment the move passes its test; worker threads, each with a Replica() of the
-// wanderer's partition (own engine + stream on the same GPU), run the identical call
-// sequence on a private clone and register the optimised lengths with
-// pt::pll::Partition::PublishVisit.  When MoveForward gets to the move, its
-// OptimizeAllBranches finds the lengths there.  The wanderer still commits visits in its own
+// Wanderer::MoveForward (:150-210) later visits each of them: apply the NNI, InvalidateEdgeClvs,
+// clone, Partition::OptimizeAllBranches, LogLikelihood.  On a small alignment such a visit is a
+// chain of several thousand dependent device phases (6-10 ms on 8 CTAs) and a one-wanderer walk
+// spends most of its time waiting for them one after the other.  BatchedNeighborhood hands a move
+// to this class the moment it passes its test; worker threads, each with a Replica() of the
+// wanderer's partition (own engine + stream on the same GPU), compute the visit and register the
+// optimised lengths with pt::pll::Partition::PublishVisit; when MoveForward gets to the move, its
+// OptimizeAllBranches finds them there.  The wanderer still commits visits in its own
 // depth-first order.
 //
-// OPT-IN, and why.  A visit computed here starts from CLVs that are all exact for the tree
-// (FULL traversal).  The reference's own visit does not: Wanderer::MoveForward invalidates only
-// the two CLVs at the ends of the NNI edge (InvalidateEdgeClvs, PTPLL/pll_util.cpp:353-366;
-// src/wanderer.cpp:160-186), so CLVs between that edge and the virtual root stay flagged valid
-// although the move changed what they summarise -- and after a move that did not lead to a
-// good tree the partition still holds THAT tree's CLVs (src/wanderer.cpp:176-186) -- and the
-// first branch optimisations of the visit read them.  OptimizeAllBranches converges to the
-// same optimum either way, but only to its own tolerance (passes stop at |dlnL| < 1e-6), so
-// optimised lengths differ in their last bits.  The in-place visit (the default) reproduces the
-// reference's state and therefore its tables line for line; with prefetching, good and visited
-// tables came out identical on DS1 and the three stand-ins, while a few of the ~10^4 tested-tree
-// scores differ in the last of their 6 printed digits (tests/test_gpu_dropin.py).
+// LINE FOR LINE, and how.  The reference's visit is not a function of the tree alone: it starts
+// from the PARENT tree's CLVs with only the two ends of the NNI edge flagged invalid
+// (PTPLL/pll_util.cpp:353-366), so the CLVs between that edge and the root are stale when the
+// first branches are optimised, and the optimum found (to OptimizeAllBranches' own 1e-6
+// tolerance) depends on it in the last digits.  A worker therefore reproduces that very start
+// state -- FULL traversal of the parent tree T at its root (the partition's content whenever the
+// wanderer visits the first move of T's queue, or returns to T by MoveBack), then the NNI and
+// the two invalid flags -- and runs the identical procedure: same kernels, same inputs, same
+// bits.  The result is registered under a key that names the start state (content, tree,
+// flags: Partition::VisitKey); a visit whose actual start state is another one -- the move
+// after a visit that did NOT lead to a good tree starts from that tree's CLVs instead -- finds
+// nothing under its key and is computed in place, as before.  tests/test_gpu_dropin.py requires
+// the good / visited / tested tables to be identical to the reference's, scores included.
 //
-// Start(n) spawns n worker threads (0 = off); PTGPU_PREFETCH_VISITS=n overrides.  It pays for ONE
-// wanderer, whose visits otherwise run one after the other (DS8 stand-in: 27.6 -> 12.0 s with 8
-// workers, DS1: 4.9 -> 3.6 s with 2); with many wanderers the visits of different wanderers
-// already overlap on the device and more engines only add contention (measured).
+// The same workers also score the NNI neighbourhood of every tree they have just optimised
+// (Partition::ScoreNniNeighborhood is a pure function of the tree, its lengths and the model:
+// it recomputes all matrices and directional CLVs itself) and register the scores under the
+// optimised tree's fingerprint; BatchedNeighborhood takes them from there when the wanderer,
+// having found the tree good, asks about its first move.
+//
+// Walking ahead.  A depth-first walk descends into a tree the moment it has been found good, so
+// the visits of ITS moves would only be asked for when the wanderer gets there.  A worker that
+// has optimised a tree and scored its neighbourhood therefore submits the visits of that tree's
+// promising moves itself (tree good and move score above the authority's present threshold, move
+// not leading to a tree already visited: what QueueMoves will decide, read from the same
+// Authority), PTGPU_PREFETCH_DEPTH levels ahead of the wanderer at most (default 1; measured on
+// DS1: deeper speculation costs more device time than it hides).  A guess that turns out wrong
+// costs device time, never correctness: results are only ever taken by exact start state.
+//
+// On by default in ptw_batched: Start(n) spawns n worker threads (PTGPU_PREFETCH_VISITS=n
+// overrides, 0 = off).  It pays for few wanderers, whose visits otherwise run one after the
+// other; with many wanderers the visits of different wanderers already overlap on the device.
 #ifndef PT_B200_HOST_PTW_VISIT_PREFETCHER_HPP_
 #define PT_B200_HOST_PTW_VISIT_PREFETCHER_HPP_
 
+#include <atomic>
 #include <condition_variable>
 #include <deque>
 #include <future>
@@ -44,7 +58,10 @@
 #include <vector>
 
 #include <libpll/pll.h>
+#include <model.hpp>
 #include <pll_partition.hpp>
+
+#include "authority.hpp"
 
 namespace pt { namespace move_tester {
 
@@ -53,19 +70,30 @@ class VisitPrefetcher
  public:
   static VisitPrefetcher& Instance();
 
-  bool enabled() const { return !workers_.empty(); }
+  bool enabled() const { return !workers_.empty() && !disabled_.load(std::memory_order_relaxed); }
 
-  // before the walk starts; PTGPU_PREFETCH_VISITS, if set, takes the place of `workers`
-  void Start(int workers);
+  // before the walk starts; PTGPU_PREFETCH_VISITS, if set, takes the place of `workers`.
+  // `radius` is the move tester's (the workers score neighbourhoods with it).
+  void Start(int workers, int radius);
 
-  // `tree` is the wanderer's tree WITH the move applied (the caller undoes the move after
-  // this returns); `owner` the wanderer's partition.  Returns at once.
-  void Submit(pll::Partition& owner, pll_utree_t* tree);
+  // The move (node, type) of the wanderer's tree `tree` has passed its test; `owner` is the
+  // wanderer's partition, whose content is exact for `tree` (it has just been visited).
+  // Nothing the wanderer owns is modified; returns at once.  Never throws: a failure turns
+  // prefetching off for the rest of the run and the visit is computed in place.
+  void Submit(pll::Partition& owner, pll_utree_t* tree, pll_unode_t* node, int type,
+              const Authority& authority) noexcept;
+
+  // the scores of `tree`'s NNI neighbourhood if a worker has computed (or is computing) them:
+  // node pointers are those of `tree`.  false = not registered (or the computation failed).
+  bool TakeNeighborhood(pll_utree_t* tree, std::vector<pll::Partition::NniScore>* out);
 
   // joins the workers and destroys their engines (before the CUDA runtime goes away)
   void Shutdown();
 
   unsigned long long submitted() const { return submitted_; }
+  unsigned long long declined() const { return declined_; }
+  unsigned long long neighborhoods_taken() const { return hoods_taken_; }
+  unsigned long long walked_ahead() const { return walked_ahead_; }
 
   ~VisitPrefetcher();
 
@@ -73,26 +101,54 @@ class VisitPrefetcher
   VisitPrefetcher();
 
   struct Task {
-    pll::Partition* owner;
-    pll_utree_t* tree;   // private clone, destroyed by the worker
-    unsigned long long batch;   // moves queued by the same QueueMoves share a batch
+    int device;
+    pll::Model model;
+    pll_utree_t* tree = nullptr;      // private clone WITH the move applied and the start flags set
+    unsigned int node_index;          // the move, by record index
+    unsigned int parent_root_index;   // virtual root of the parent tree (the content's orientation)
+    int type;
+    int depth = 0;                    // levels ahead of the wanderer (0: submitted by the wanderer)
+    unsigned long long batch;         // moves queued by the same QueueMoves share a batch
     std::promise<pll::Partition::VisitResult> result;
+    ~Task();
   };
+  struct IndexedScore { unsigned int node_index; int type; double length, lnl; };
+  typedef std::vector<IndexedScore> Neighborhood;
 
   void Work();
+  void SubmitOrThrow(pll::Partition& owner, pll_utree_t* tree, pll_unode_t* node, int type);
+  // queues the visit of move (node, type) of `tree`, whose exact CLVs (oriented at its virtual
+  // root) the visiting partition will hold; false if that visit is already known
+  bool Enqueue(int device, const pll::Model& model, pll_utree_t* tree, pll_unode_t* node, int type, int depth);
+  void WalkAhead(const Task& done, pll::Partition& rep, const std::vector<pll::Partition::NniScore>& scored);
 
-  // Replicas are made on the wanderer's own thread (Submit), one per worker, the first time a
-  // partition submits: a worker must not read the owner's state while its thread uses it.
-  std::map<pll::Partition*, std::vector<std::unique_ptr<pll::Partition>>> free_replicas_;
+  // One pool of replicas per device, shared by every wanderer on it (all partitions of a ptw
+  // run hold the same alignment).  Replicas are made on a wanderer's own thread (Submit): a
+  // worker must not read an owner's state while its thread uses it.  At most as many per
+  // device as there are workers and as the memory budget allows (PTGPU_PREFETCH_MAX_MB).
+  struct Pool {
+    std::vector<std::unique_ptr<pll::Partition>> free;
+    size_t made = 0;
+  };
+  std::map<int, Pool> pools_;
 
   std::vector<std::thread> workers_;
   std::mutex mutex_;
-  std::condition_variable wake_;
+  std::condition_variable wake_, replica_back_;
   std::deque<std::unique_ptr<Task>> queue_;
   bool stop_ = false;
+  std::atomic<bool> disabled_{false};
   unsigned long long batch_ = 0;
-  std::map<pll::Partition*, const pll_utree_t*> last_tree_;   // per owner: the tree of its latest batch
-  unsigned long long submitted_ = 0;
+  std::map<int, std::pair<const pll_utree_t*, uint64_t>> last_tree_;   // per device: latest batch's tree
+  unsigned long long submitted_ = 0, declined_ = 0;
+
+  std::map<uint64_t, std::shared_future<Neighborhood>> hoods_;
+  std::deque<uint64_t> hood_order_;
+  std::atomic<unsigned long long> hoods_taken_{0}, walked_ahead_{0};
+  std::atomic<const Authority*> authority_{nullptr};
+  int radius_ = 0;
+  int max_depth_ = 1;         // PTGPU_PREFETCH_DEPTH
+  bool score_hoods_ = true;   // PTGPU_PREFETCH_NEIGHBORHOODS=0 turns it off
 };
 
 } } // namespace pt::move_tester

@@ -16,6 +16,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#include <exception>
 #include <future>
 #include <map>
 #include <mutex>
@@ -389,17 +391,67 @@ uint64_t Partition::FingerprintFrom(pll_unode_t* root)
   return h;
 }
 
-void Partition::PublishVisit(uint64_t fingerprint, std::shared_future<VisitResult> result)
+uint64_t Partition::ExactContentId(uint64_t tree_fingerprint, unsigned int root_index)
+{
+  uint64_t h = tree_fingerprint ^ (0x9e3779b97f4a7c15ull * (root_index + 1));
+  h ^= h >> 31; h *= 0x7fb5d329728ea185ull; h ^= h >> 27; h *= 0x81dadef4bc2dd44dull; h ^= h >> 33;
+  return h ? h : 1;
+}
+
+// start state of OptimizeAllBranches(root): content, tree (topology + lengths), the per-record
+// orientation flags (a record without flags yet behaves like an invalid one), the root
+uint64_t Partition::VisitKeyFor(uint64_t content_id, pll_unode_t* root, unsigned int node_count)
+{
+  if (!content_id) return 0;
+  std::vector<pll_unode_t*> nodes(node_count, nullptr);
+  unsigned int found = 0;
+  if (!pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, visit_all, nodes.data(), &found)) return 0;
+  if (found != node_count) return 0;
+  uint64_t tree = 0, flags = 0;
+  for (unsigned int i = 0; i < found; ++i) {
+    tree += node_hash(nodes[i]);
+    pll_unode_t* r = nodes[i];
+    if (!r->next) continue;
+    do {
+      const int valid = r->data ? static_cast<node_info_t*>(r->data)->clv_valid : 0;
+      if (valid) {
+        uint64_t h = 0xd6e8feb86659fd93ull * (r->node_index + 1);
+        h ^= h >> 32; h *= 0xd6e8feb86659fd93ull; h ^= h >> 32;
+        flags += h;
+      }
+      r = r->next;
+    } while (r != nodes[i]);
+  }
+  uint64_t h = content_id;
+  h ^= tree + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+  h ^= flags + 0xc2b2ae3d27d4eb4full + (h << 6) + (h >> 2);
+  h ^= 0x165667b19e3779f9ull * (root->node_index + 1) + (h << 6) + (h >> 2);
+  h ^= h >> 29; h *= 0xbf58476d1ce4e5b9ull; h ^= h >> 32;
+  return h ? h : 1;
+}
+
+uint64_t Partition::VisitKey(pll_unode_t* root) const
+{
+  return VisitKeyFor(content_id_, root, node_count());
+}
+
+void Partition::PublishVisit(uint64_t key, std::shared_future<VisitResult> result)
 {
   std::lock_guard<std::mutex> lock(g_visit_mutex);
-  g_visits.emplace(fingerprint, std::move(result));
+  // results nobody came for (a predicted start state that did not occur) are dropped oldest first
+  static std::deque<uint64_t> order;
+  if (g_visits.emplace(key, std::move(result)).second) order.push_back(key);
+  while (order.size() > 4096) {
+    g_visits.erase(order.front());
+    order.pop_front();
+  }
   g_visits_used = true;
 }
 
-bool Partition::VisitKnown(uint64_t fingerprint)
+bool Partition::VisitKnown(uint64_t key)
 {
   std::lock_guard<std::mutex> lock(g_visit_mutex);
-  return g_visits.count(fingerprint) != 0;
+  return g_visits.count(key) != 0;
 }
 
 void Partition::ClearVisits()
@@ -413,17 +465,25 @@ std::pair<unsigned long long, unsigned long long> Partition::VisitStatistics()
   return std::make_pair(g_visits_served.load(), g_visits_computed.load());
 }
 
-// the registered result of OptimizeAllBranches for this very tree, if there is one: lengths into
-// the tree, every CLV marked stale (the caller's next traversal recomputes them all)
-bool Partition::TakePublishedVisit(pll_unode_t* root)
+size_t Partition::ReplicaBytes(bool directional) const
 {
-  if (is_replica_ || !g_visits_used.load(std::memory_order_relaxed)) return false;
-  const uint64_t fp = FingerprintFrom(root);   // fills travbuffer_ with one record per node
-  if (!fp) return false;
+  const size_t cats = model_.category_rates.size();
+  // per-node (+ directional) CLVs and scalers, sumtable, the step-program kernel's scratch of the
+  // same order; with directional buffers also one sumtable per NNI candidate
+  const size_t clvs = static_cast<size_t>(inner_node_count()) * (directional ? 4 : 1) + 3 +
+                      (directional ? 2 * inner_node_count() : 0);
+  return clvs * site_count_ * (cats * 32 + 4) + (64u << 20);
+}
+
+// the registered result of OptimizeAllBranches for exactly this start state, if there is one:
+// lengths into the tree, then the CLVs and matrices of the optimised tree by one FULL traversal
+// (the state the computation itself ends in: everything exact, oriented at `root`)
+bool Partition::TakePublishedVisit(uint64_t key, pll_unode_t* root)
+{
   std::shared_future<VisitResult> pending;
   {
     std::lock_guard<std::mutex> lock(g_visit_mutex);
-    auto it = g_visits.find(fp);
+    auto it = g_visits.find(key);
     if (it == g_visits.end()) return false;
     pending = it->second;
     g_visits.erase(it);
@@ -434,7 +494,11 @@ bool Partition::TakePublishedVisit(pll_unode_t* root)
   } catch (...) {
     return false;   // the background visit failed: compute here, where the caller sees the error
   }
-  for (unsigned int i = 0; i < node_count(); ++i) {
+  unsigned int found = 0;
+  if (!pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, visit_all, travbuffer_.data(), &found) ||
+      found != node_count())
+    return false;
+  for (unsigned int i = 0; i < found; ++i) {
     pll_unode_t* n = travbuffer_[i];
     pll_unode_t* r = n;
     do {
@@ -442,19 +506,19 @@ bool Partition::TakePublishedVisit(pll_unode_t* root)
       r = r->next;
     } while (r && r != n);
   }
-  for (unsigned int i = 0; i < node_count(); ++i) {
+  for (unsigned int i = 0; i < found; ++i) {
     pll_unode_t* n = travbuffer_[i];
     pll_unode_t* r = n;
     do {
       r->length = res.lengths[r->node_index];
-      if (r->next && r->data) static_cast<node_info_t*>(r->data)->clv_valid = 0;
       r = r->next;
     } while (r && r != n);
   }
+  TraversalUpdate(root, TraversalType::FULL);
   return true;
 }
 
-Partition::Partition(const Partition& proto, ReplicaTag) :
+Partition::Partition(const Partition& proto, ReplicaTag, bool directional) :
     tip_node_count_(proto.tip_node_count_),
     map_mode_(proto.map_mode_),
     engine_(nullptr),
@@ -466,7 +530,9 @@ Partition::Partition(const Partition& proto, ReplicaTag) :
 {
   if (proto.shards_.size() > 1)
     throw std::logic_error("Replica() of a site-sharded partition is not supported");
-  CreateEngines(inner_node_count(), inner_node_count(),
+  const unsigned int extra = directional ? 3 * inner_node_count() : 0;
+  directional_base_ = directional ? inner_node_count() : 0;
+  CreateEngines(inner_node_count() + extra, inner_node_count() + extra,
                 static_cast<unsigned int>(proto.model_.category_rates.size()), 1);
   try {
     SetModel(proto.model_);
@@ -478,9 +544,9 @@ Partition::Partition(const Partition& proto, ReplicaTag) :
   AllocateScratchBuffers();
 }
 
-std::unique_ptr<Partition> Partition::Replica() const
+std::unique_ptr<Partition> Partition::Replica(bool directional) const
 {
-  return std::unique_ptr<Partition>(new Partition(*this, ReplicaTag{}));
+  return std::unique_ptr<Partition>(new Partition(*this, ReplicaTag{}, directional));
 }
 
 // PTPLL/pll_partition.cpp:67-80: the engine moves, scratch is re-allocated
@@ -530,6 +596,7 @@ void Partition::SetModel(const Model& model)
   // count; the engine takes all three at once, so the check comes first)
   if (model_.category_rates.size() && model.category_rates.size() != model_.category_rates.size())
     throw std::invalid_argument("Invalid number of category rates");
+  content_id_ = 0;
   OnShards([&](ptgpu_engine* e, unsigned int) {
     return ptgpu_set_model(e, model.frequencies.data(), model.subst_params.data(),
                            model.category_rates.data());
@@ -658,6 +725,13 @@ unsigned int Partition::TraversalUpdate(pll_unode_t* root, TraversalType type)
     return ptgpu_update_partials(e, reinterpret_cast<const ptgpu_operation_t*>(operations_.data()),
                                  ops_count);
   });
+  // a FULL traversal leaves the exact CLVs and matrices of this tree, oriented at `root`; a
+  // PARTIAL one that recomputed something leaves a mixture nobody can name
+  if (type == TraversalType::FULL) {
+    content_fp_ = FingerprintFrom(root);
+    content_id_ = ExactContentId(content_fp_, root->node_index);
+  } else if (ops_count)
+    content_id_ = 0;
   return ops_count;
 }
 
@@ -666,6 +740,7 @@ void Partition::UpdateBranchLength(pll_unode_t* node, double length)
 {
   node->length = length;
   node->back->length = length;
+  content_id_ = 0;
   OnShards([&](ptgpu_engine* e, unsigned int) {
     return ptgpu_update_prob_matrices(e, &node->pmatrix_index, &node->length, 1);
   });
@@ -677,6 +752,7 @@ void Partition::UpdateBranchLength(pll_unode_t* node, double length)
 double Partition::OptimizeBranch(pll_unode_t* node)
 {
   StatScope stat(kStatOptimizeBranch);
+  content_id_ = 0;
   pll_unode_t* child = node->back;
   double len = node->length;
   OnShards([&](ptgpu_engine* e, unsigned int s) {
@@ -719,11 +795,26 @@ void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
 void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 {
   StatScope stat(kStatAllBranches);
-  if (!use_pllmod && TakePublishedVisit(tree)) {
-    g_visits_served += 1;
-    return;
+  if (!use_pllmod && !is_replica_ && g_visits_used.load(std::memory_order_relaxed)) {
+    const uint64_t key = VisitKey(tree);
+    if (key && TakePublishedVisit(key, tree)) {
+      g_visits_served += 1;
+      return;
+    }
   }
   if (!is_replica_) g_visits_computed += 1;
+  // whichever way it is computed, the procedure ends with every CLV and matrix exact for the
+  // optimised tree, oriented at `tree`
+  struct ContentNote {
+    Partition* p; pll_unode_t* root; bool armed;
+    ~ContentNote()
+    {
+      const bool ok = armed && std::uncaught_exceptions() == 0;
+      p->content_fp_ = ok ? p->FingerprintFrom(root) : 0;
+      p->content_id_ = ok ? ExactContentId(p->content_fp_, root->node_index) : 0;
+    }
+  } note{this, tree, !use_pllmod};
+  content_id_ = 0;
   if (!use_pllmod && !stepwise_all_branches_) {
     OptimizeAllBranchesFused(tree);
     return;
@@ -753,6 +844,7 @@ void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 void Partition::OptimizeBranchNeighborhood(pll_unode_t* node, int radius)
 {
   if (radius <= 0) throw std::invalid_argument("optimization radius must be positive");
+  content_id_ = 0;
   TraversalUpdate(node, TraversalType::PARTIAL);
   // PLLMOD_OPT_MIN_BRANCH_LEN, PLLMOD_OPT_MAX_BRANCH_LEN (pll_optimize.h:60-61)
   LocalBranchOptimization(node, 1.0e-4, 100.0, EPSILON, static_cast<int>(MAX_ITER), radius);
@@ -821,6 +913,7 @@ bool Partition::OptimizeEdgeBounded(pll_unode_t* p, double bl_min, double bl_max
 double Partition::LocalBranchOptimization(pll_unode_t* tree, double bl_min, double bl_max,
                                           double tolerance, int smoothings, int radius)
 {
+  content_id_ = 0;   // edges are re-optimised (and their matrices rewritten) below
   auto edge_lnl = [this, tree]() {
     double v = 0.0;
     OnShards([&](ptgpu_engine* e, unsigned int s) {
@@ -1086,6 +1179,9 @@ void Partition::UpdateDirectionalClvs(pll_utree_t* tree, const std::vector<unsig
       mlen.push_back(r->length);
     }
   }
+  // every matrix becomes P(this tree's length of that edge): the same bits as before if the
+  // content is this very tree's, something else otherwise
+  if (content_id_ && TreeFingerprint(tree) != content_fp_) content_id_ = 0;
   OnShards([&](ptgpu_engine* e, unsigned int) {
     return ptgpu_update_prob_matrices(e, midx.data(), mlen.data(), static_cast<unsigned int>(midx.size()));
   });
