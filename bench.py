@@ -128,14 +128,28 @@ class ClockSampler(threading.Thread):
                     samples=len(sm), source=self.source)
 
 
+def kernel_sources_stamp():
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("kernels.cuh", "blo.cuh", "engine.cu"):
+        with open(os.path.join(ROOT, "pt_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
 def ncu_traffic(kernel, taxa, sites):
     """dram__bytes_read + dram__bytes_write per launch of `kernel` from the committed
-    `ncu --set full` capture (profiles/r1_traffic.json), valid for the default workload only"""
+    `ncu --set full` capture (profiles/r2_traffic.json): valid for the default workload only, and
+    only while the kernel sources are the ones the capture was taken on (the file carries their
+    hash) -- otherwise None, not a stale number"""
     if (taxa, sites) != (64, 1000000):
         return None
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-            return json.load(f)[kernel]["dram_bytes_per_launch"]
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+            t = json.load(f)
+        if t.get("kernel_sources_sha16") != kernel_sources_stamp():
+            return None
+        return t[kernel]["dram_bytes_per_launch"]
     except (OSError, KeyError, ValueError):
         return None
 
@@ -834,7 +848,12 @@ def run_ptw_ds1(args):
                    "--polling-time", "1" if threads > 1 else "100", "--lnl-offset", "-5", "--optimization-radius", "1", "--tested-trees", tested,
                    os.path.join(ds1, "RAxML_bestTree.DS1"), os.path.join(ds1, "DS1.fasta"), out]
             t0 = time.perf_counter()
-            r = subprocess.run(cmd, capture_output=True, text=True, check=True)
+            env = dict(os.environ)
+            if binary == ours and args.gpus > 0:
+                # wanderer-parallel over the first N GPUs: every wanderer's Partition takes the next
+                # visible device round-robin (pt_b200/host/src/pll_partition.cpp, pick_device)
+                env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(args.gpus))
+            r = subprocess.run(cmd, capture_output=True, text=True, check=True, env=env)
             dt = time.perf_counter() - t0
             good = sum(1 for _ in open(out))
             ntested = sum(1 for _ in open(tested))
@@ -858,13 +877,13 @@ def run_ptw_ds1(args):
     clocks = sampler.stop(wall0, time.time())
     dt = sum(r[0] for r in runs) / len(runs)
     _, good, ntested, moves = runs[-1]
-    line = dict(metric="nni_candidates_scored_per_s", value=moves / dt, unit="candidates/s", n_gpus=1,
+    line = dict(metric="nni_candidates_scored_per_s", value=moves / dt, unit="candidates/s", n_gpus=args.gpus,
                 steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * dt, higher_is_better=True,
-                scaling="weak", vs_baseline=None, dtype="f64", data="DS1 (27 taxa x 1949 sites)",
+                scaling="strong", vs_baseline=None, dtype="f64", data="DS1 (27 taxa x 1949 sites)",
                 config=dict(workload="BASELINE configs[1] on DS1: ptw topography walk, --lnl-offset -5 "
-                                     "--optimization-radius 1, %d wanderer(s) with one engine each on the same GPU, "
-                                     "batched move testing (whole process, incl. ~1.1 s CUDA context "
-                                     "creation)" % W,
+                                     "--optimization-radius 1, %d wanderer(s) with one engine each, dealt round-robin "
+                                     "to %d GPU(s); batched move testing, visits ahead of time (whole process, incl. "
+                                     "~1.1 s CUDA context creation per GPU)" % (W, args.gpus),
                             wanderers=W,
                             taxa=27, sites=1949, rate_cats=4),
                 good_trees=good, tested_trees=ntested, evaluate_move_calls=moves, clocks=clocks,

@@ -10,4 +10,3 @@ $CMD > gpurun_out/${TAG}_plain2.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:partials_kernel_v4|nni_prepare_kernel_v2|newton_kernel' -s 3 -c 3 -o gpurun_out/${TAG}_prof -f $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo full rc=$?
 tail -3 gpurun_out/${TAG}_ncu_full.log
-ls -la gpurun_out | tail -8
