@@ -304,10 +304,17 @@ __device__ __forceinline__ void lds256(const double *p, double v[4])
 }
 
 // (a0 b0 + a1 b1) + (a2 b2 + a3 b3), every product and sum rounded separately
+// PT_FMA=1 (experiment only, never the shipped build: scripts/fma_variant.sh): the same tree with
+// the second product of each pair fused into the addition -- 4 instead of 7 FP64 issue slots, but
+// not libpll's bits (SURVEY.md section 7 asked for it to be measured behind the scaler / 1e-9 gates)
 __device__ __forceinline__ double dot4(const double *a, const double b[4])
 {
+#if defined(PT_FMA) && PT_FMA
+  return __dadd_rn(__fma_rn(a[0], b[0], __dmul_rn(a[1], b[1])), __fma_rn(a[2], b[2], __dmul_rn(a[3], b[3])));
+#else
   return __dadd_rn(__dadd_rn(__dmul_rn(a[0], b[0]), __dmul_rn(a[1], b[1])),
                    __dadd_rn(__dmul_rn(a[2], b[2]), __dmul_rn(a[3], b[3])));
+#endif
 }
 
 // One (site, cat) entry of CLV `clv_index`: tips are expanded from their 4-bit
