@@ -324,6 +324,32 @@ def parity_at_full_size(e, tree, aln, cand_rows, plan_rows, scores, n, S, k):
                 seconds=time.perf_counter() - t0)
 
 
+def cpp_partition_leg(tree, aln, n, S, lnl_sum, ms_python):
+    """The same step through the C++ surface a pt build uses: pt_b200/bin/score_neighborhood builds a
+    pt::pll::Partition from files and calls Partition::ScoreNniNeighborhood (what BatchedNeighborhood
+    calls once per tree) on the bench's tree and FULL alignment; outside every timed region."""
+    import tempfile
+    exe = os.path.join(ROOT, "pt_b200", "bin", "score_neighborhood")
+    info = os.path.join(ROOT, "tests", "golden", "data", "ds1", "RAxML_info.DS1")   # DS1's GTR+G4 = FREQS/SUBST/alpha
+    if not os.path.exists(exe):
+        return dict(skipped="pt_b200/bin/score_neighborhood not built (make -C pt_b200/host drivers REF=<pt checkout>)")
+    with tempfile.TemporaryDirectory() as d:
+        with open(os.path.join(d, "t.nwk"), "w") as f:
+            f.write(tree.newick() + "\n")
+        with open(os.path.join(d, "a.fasta"), "wb") as f:
+            for label in tree.labels():
+                f.write(b">" + label.encode() + b"\n" + bytes(aln[label]) + b"\n")
+        r = subprocess.run([exe, os.path.join(d, "t.nwk"), os.path.join(d, "a.fasta"), info, "0", "3"],
+                           capture_output=True, text=True)
+    if r.returncode != 0:
+        return dict(failed=r.stderr[-300:])
+    out = json.loads(r.stdout)
+    rel = abs(out["lnl_sum"] - lnl_sum) / abs(lnl_sum)
+    out.update(call="pt::pll::Partition::ScoreNniNeighborhood (pt_b200/host), incl. P matrices + directional CLVs",
+               lnl_sum_rel_diff_vs_c_abi_path=rel, ms_per_step_c_abi_path=ms_python, passed=bool(rel <= 1e-12))
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -551,6 +577,11 @@ def run_ours(args):
         del host_aln
         sharded = sharded_visit(n, S, rank, world, local, dist, steps=min(max(args.steps, 2), 3), warmup=1,
                                 aln=aln)
+    cpp_leg = None
+    if rank == 0 and world == 1 and args.radius == 0 and weights is None and not args.no_parity_at_size:
+        if sharded is None:
+            e.close()
+        cpp_leg = cpp_partition_leg(tree, aln, n, S, float(np.sum(lnls)), ms / args.steps)
     if rank != 0:
         if dist:
             dist.destroy_process_group()
@@ -630,6 +661,8 @@ def run_ours(args):
         line["parity_at_size"] = parity
     if sharded is not None:
         line["sharded"] = sharded
+    if cpp_leg is not None:
+        line["cpp_partition"] = cpp_leg
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline_single(n, S, aln, tree, min(S, args.cpu_sample_sites), args.radius)
         if cb:

@@ -1,6 +1,9 @@
 // pt_b200/host/ptw/batched_neighborhood.cpp -- see the header.
 #include "batched_neighborhood.hpp"
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 
@@ -17,7 +20,12 @@ BatchedNeighborhood::BatchedNeighborhood(const Options& options)
     throw std::invalid_argument("marginal mode is not available with batched move testing");
 }
 
-BatchedNeighborhood::~BatchedNeighborhood() {}
+BatchedNeighborhood::~BatchedNeighborhood()
+{
+  if (neighborhood_ns_)
+    std::fprintf(stderr, "[ptgpu host] %-28s %10llu calls %10.3f s\n", "neighbourhood (take or score)",
+                 static_cast<unsigned long long>(batches_), neighborhood_ns_ * 1e-9);
+}
 
 // Topology + branch lengths of the tree as the wanderer holds it: who each record
 // is linked to and at which length (FNV-1a over the node array).  The wanderer
@@ -60,7 +68,9 @@ std::pair<bool, double> BatchedNeighborhood::EvaluateMove(pll::Partition& partit
     ++questions_;
   }
   const uint64_t fp = Fingerprint(tree);
+  static const bool stats = std::getenv("PTGPU_HOST_STATS") != nullptr;
   if (scores->tree != tree || scores->fingerprint != fp) {
+    const auto t0 = std::chrono::steady_clock::now();
     // first question about this tree: score its whole NNI neighbourhood.  The
     // partition's per-node CLVs, the tree and its orientation flags stay as they
     // are (the batch works on directional and private buffers), which is the
@@ -72,6 +82,8 @@ std::pair<bool, double> BatchedNeighborhood::EvaluateMove(pll::Partition& partit
     scores->fingerprint = fp;
     std::lock_guard<std::mutex> lock(mutex_);
     ++batches_;
+    if (stats) neighborhood_ns_ += std::chrono::duration_cast<std::chrono::nanoseconds>(
+                                       std::chrono::steady_clock::now() - t0).count();
   }
   for (const pll::Partition::NniScore& m : scores->moves) {
     if (m.node == node && m.type == static_cast<int>(type)) {

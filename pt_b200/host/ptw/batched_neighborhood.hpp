@@ -58,7 +58,7 @@ class BatchedNeighborhood : public MoveTester {
   const int radius_;
   mutable std::mutex mutex_;                                  // guards the map, not the entries:
   mutable std::map<const pll::Partition*, Scores> by_partition_;  // an entry belongs to its wanderer's thread
-  mutable uint64_t batches_ = 0, questions_ = 0;
+  mutable uint64_t batches_ = 0, questions_ = 0, neighborhood_ns_ = 0;
 };
 
 } } // namespace pt::move_tester

@@ -84,6 +84,7 @@ void VisitPrefetcher::Shutdown()
   queue_.clear();
   hoods_.clear();
   hood_order_.clear();
+  speculated_.clear();
   last_tree_.clear();
   pll::Partition::ClearVisits();
 }
@@ -208,6 +209,15 @@ void VisitPrefetcher::WalkAhead(const Task& done, pll::Partition& rep,
     if (m.lnl < threshold) continue;
     // Authority::ProposeMove only reads its tables (and applies + undoes the move on OUR clone)
     if (!const_cast<Authority*>(authority)->ProposeMove(done.tree, m.node, static_cast<MoveType>(m.type))) continue;
+    {
+      // a tree within reach of two good trees is visited from whichever the wanderer meets first:
+      // speculate on it once only (from the first parent a worker sees)
+      pll_utree_nni(m.node, m.type, nullptr);
+      const CompressedTree key = authority->GetKey(done.tree);
+      pll_utree_nni(m.node, m.type, nullptr);
+      std::lock_guard<std::mutex> lock(mutex_);
+      if (!speculated_.insert(key).second) continue;
+    }
     if (Enqueue(done.device, done.model, done.tree, m.node, m.type, done.depth + 1)) ++walked_ahead_;
   }
 }

@@ -32,14 +32,17 @@
 // optimised tree's fingerprint; BatchedNeighborhood takes them from there when the wanderer,
 // having found the tree good, asks about its first move.
 //
-// Walking ahead.  A depth-first walk descends into a tree the moment it has been found good, so
-// the visits of ITS moves would only be asked for when the wanderer gets there.  A worker that
-// has optimised a tree and scored its neighbourhood therefore submits the visits of that tree's
-// promising moves itself (tree good and move score above the authority's present threshold, move
-// not leading to a tree already visited: what QueueMoves will decide, read from the same
-// Authority), PTGPU_PREFETCH_DEPTH levels ahead of the wanderer at most (default 1; measured on
-// DS1: deeper speculation costs more device time than it hides).  A guess that turns out wrong
-// costs device time, never correctness: results are only ever taken by exact start state.
+// Walking ahead (PTGPU_PREFETCH_DEPTH=d, default 0 = off).  A depth-first walk descends into a tree
+// the moment it has been found good, so the visit of its first move is only asked for when the
+// wanderer gets there.  With d > 0 a worker that has optimised a tree and scored its neighbourhood
+// submits the visits of that tree's promising moves itself (tree good and move score above the
+// authority's present threshold, move not leading to a tree already visited or already speculated
+// on: what QueueMoves will decide, read from the same Authority), up to d levels ahead of the
+// wanderer.  A guess that turns out wrong costs device time, never correctness: results are only
+// ever taken by exact start state.  Measured on DS1 and the DS8-shape stand-in
+// (profiles/r2_depth_sweep.log): no gain at any depth -- one level ahead starts a visit only
+// ~0.5 ms before the wanderer would have asked for it, deeper levels spend as much device time on
+// trees reached from another parent as they hide -- hence off by default.
 //
 // On by default in ptw_batched: Start(n) spawns n worker threads (PTGPU_PREFETCH_VISITS=n
 // overrides, 0 = off).  It pays for few wanderers, whose visits otherwise run one after the
@@ -55,6 +58,7 @@
 #include <memory>
 #include <mutex>
 #include <thread>
+#include <unordered_set>
 #include <vector>
 
 #include <libpll/pll.h>
@@ -146,8 +150,9 @@ class VisitPrefetcher
   std::deque<uint64_t> hood_order_;
   std::atomic<unsigned long long> hoods_taken_{0}, walked_ahead_{0};
   std::atomic<const Authority*> authority_{nullptr};
+  std::unordered_set<CompressedTree> speculated_;   // topologies a worker has already walked ahead to
   int radius_ = 0;
-  int max_depth_ = 1;         // PTGPU_PREFETCH_DEPTH
+  int max_depth_ = 0;         // PTGPU_PREFETCH_DEPTH
   bool score_hoods_ = true;   // PTGPU_PREFETCH_NEIGHBORHOODS=0 turns it off
 };
 

@@ -67,27 +67,30 @@ int visit_all(pll_unode_t*) { return 1; }
 // PTGPU_HOST_STATS=1: wall time and call counts of the Partition entry points,
 // printed when a Partition dies (where does a ptw run spend its time?)
 struct HostStat { std::atomic<unsigned long long> ns{0}, calls{0}; };
-enum { kStatTraversal, kStatOptimizeBranch, kStatLogLikelihood, kStatNeighborhood, kStatAllBranches, kStatCount };
+enum { kStatTraversal, kStatOptimizeBranch, kStatLogLikelihood, kStatNeighborhood, kStatAllBranches, kStatVisitWait, kStatCount };
 HostStat g_stats[kStatCount];
 const char* const kStatNames[kStatCount] = {"TraversalUpdate", "OptimizeBranch", "LogLikelihood",
-                                            "ScoreNniNeighborhood", "OptimizeAllBranches(total)"};
+                                            "ScoreNniNeighborhood", "OptimizeAllBranches(total)",
+                                            "  waiting for a prefetched visit"};
 const bool g_stats_on = std::getenv("PTGPU_HOST_STATS") != nullptr;
 
 class StatScope {
  public:
-  explicit StatScope(int which) : which_(which)
+  // `counted` = false for the background replicas: the statistics are the wanderers' own time
+  explicit StatScope(int which, bool counted = true) : which_(which), on_(g_stats_on && counted)
   {
-    if (g_stats_on) t0_ = std::chrono::steady_clock::now();
+    if (on_) t0_ = std::chrono::steady_clock::now();
   }
   ~StatScope()
   {
-    if (!g_stats_on) return;
+    if (!on_) return;
     const auto dt = std::chrono::steady_clock::now() - t0_;
     g_stats[which_].ns += std::chrono::duration_cast<std::chrono::nanoseconds>(dt).count();
     g_stats[which_].calls += 1;
   }
  private:
   int which_;
+  bool on_;
   std::chrono::steady_clock::time_point t0_;
 };
 
@@ -490,6 +493,7 @@ bool Partition::TakePublishedVisit(uint64_t key, pll_unode_t* root)
   }
   VisitResult res;
   try {
+    StatScope wait(kStatVisitWait, !is_replica_);
     res = pending.get();
   } catch (...) {
     return false;   // the background visit failed: compute here, where the caller sees the error
@@ -665,7 +669,7 @@ double Partition::MapLogPrior(pll_unode_t* tree)
 // PTPLL/pll_partition.cpp:309-346
 double Partition::LogLikelihood(pll_unode_t* tree, double* per_site_lnl)
 {
-  StatScope stat(kStatLogLikelihood);
+  StatScope stat(kStatLogLikelihood, !is_replica_);
   double lnl = 0.0;
   OnShards([&](ptgpu_engine* e, unsigned int s) {
     double mine = 0.0;   // the same global sum on every shard
@@ -701,7 +705,7 @@ double Partition::LogMarginalLikelihood(pll_unode_t*)
 // PTPLL/pll_partition.cpp:348-393
 unsigned int Partition::TraversalUpdate(pll_unode_t* root, TraversalType type)
 {
-  StatScope stat(kStatTraversal);
+  StatScope stat(kStatTraversal, !is_replica_);
   unsigned int traversal_size = 0;
   int ok;
   if (type == TraversalType::FULL)
@@ -751,7 +755,7 @@ void Partition::UpdateBranchLength(pll_unode_t* node, double length)
 // device-resident sequence; only the optimised length comes back.
 double Partition::OptimizeBranch(pll_unode_t* node)
 {
-  StatScope stat(kStatOptimizeBranch);
+  StatScope stat(kStatOptimizeBranch, !is_replica_);
   content_id_ = 0;
   pll_unode_t* child = node->back;
   double len = node->length;
@@ -794,7 +798,7 @@ void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
 // PTPLL/pll_partition.cpp:542-582
 void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 {
-  StatScope stat(kStatAllBranches);
+  StatScope stat(kStatAllBranches, !is_replica_);
   if (!use_pllmod && !is_replica_ && g_visits_used.load(std::memory_order_relaxed)) {
     const uint64_t key = VisitKey(tree);
     if (key && TakePublishedVisit(key, tree)) {
@@ -1237,7 +1241,7 @@ void Partition::UpdateDirectionalClvs(pll_utree_t* tree, const std::vector<unsig
 std::vector<Partition::NniScore> Partition::ScoreNniNeighborhood(pll_utree_t* tree, int radius)
 {
   if (radius < 0) throw std::invalid_argument("optimization radius must not be negative");
-  StatScope stat(kStatNeighborhood);
+  StatScope stat(kStatNeighborhood, !is_replica_);
   if (radius > 0) return ScoreNniNeighborhoodLocal(tree, radius);
 
   const unsigned int tips = tip_node_count_;

@@ -26,22 +26,28 @@ def run(label, binary, threads, data, **env):
     print(f"{label:32s} {dt:7.2f} s  rc={r.returncode} | {note[0][22:150] if note else ''}", flush=True)
 
 
-quick = len(sys.argv) > 1 and sys.argv[1] == "quick"
-for rep in range(1 if quick else 2):
-    run("ds1 default (1 wanderer)", B + "ptw_batched", 1, DS1)
-    run("ds1 reference keys", B + "ptw_batched_refkeys", 1, DS1)
-    run("ds1 no prefetch", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_VISITS=0)
-    run("ds1 depth 0", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_DEPTH=0)
-    run("ds1 depth 2", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_DEPTH=2)
-    run("ds1 workers 3", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_VISITS=3)
-    run("ds1 workers 12", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_VISITS=12)
-    run("ds1 no neighbourhoods", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_NEIGHBORHOODS=0)
-run("ds1 4 wanderers", B + "ptw_batched", 4, DS1)
-run("ds1 16 wanderers", B + "ptw_batched", 16, DS1)
-run("ds1 reference, 16 threads", "oracle/_ref/ptw_threads", 16, DS1)
-run("ds8 default (1 wanderer)", B + "ptw_batched", 1, DS8)
-run("ds8 reference keys", B + "ptw_batched_refkeys", 1, DS8)
-run("ds8 no prefetch", B + "ptw_batched", 1, DS8, PTGPU_PREFETCH_VISITS=0)
-run("ds8 depth 0", B + "ptw_batched", 1, DS8, PTGPU_PREFETCH_DEPTH=0)
-run("ds8 16 wanderers", B + "ptw_batched", 16, DS8)
-run("ds8 reference, 16 threads", "oracle/_ref/ptw_threads", 16, DS8)
+def main():
+  quick = len(sys.argv) > 1 and sys.argv[1] == "quick"
+  for rep in range(1 if quick else 2):
+      run("ds1 default (1 wanderer)", B + "ptw_batched", 1, DS1)
+      run("ds1 reference keys", B + "ptw_batched_refkeys", 1, DS1)
+      run("ds1 no prefetch", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_VISITS=0)
+      run("ds1 depth 0", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_DEPTH=0)
+      run("ds1 depth 2", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_DEPTH=2)
+      run("ds1 workers 3", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_VISITS=3)
+      run("ds1 workers 12", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_VISITS=12)
+      run("ds1 no neighbourhoods", B + "ptw_batched", 1, DS1, PTGPU_PREFETCH_NEIGHBORHOODS=0)
+  run("ds1 4 wanderers", B + "ptw_batched", 4, DS1)
+  run("ds1 16 wanderers", B + "ptw_batched", 16, DS1)
+  run("ds1 reference, 16 threads", "oracle/_ref/ptw_threads", 16, DS1)
+  run("ds8 default (1 wanderer)", B + "ptw_batched", 1, DS8)
+  run("ds8 reference keys", B + "ptw_batched_refkeys", 1, DS8)
+  run("ds8 no prefetch", B + "ptw_batched", 1, DS8, PTGPU_PREFETCH_VISITS=0)
+  run("ds8 depth 0", B + "ptw_batched", 1, DS8, PTGPU_PREFETCH_DEPTH=0)
+  run("ds8 16 wanderers", B + "ptw_batched", 16, DS8)
+  run("ds8 reference, 16 threads", "oracle/_ref/ptw_threads", 16, DS8)
+
+
+
+if __name__ == "__main__":
+    main()
