@@ -713,12 +713,39 @@ def run_shape(args):
     for tip in base.nodes[:n]:
         host_aln[tip.clv_index].copy_(torch.from_numpy(aln[tip.label]))
     nbuf = 3 * (n - 2)
-    e = Engine(n, nbuf, S, 4, 2 * n - 3, nbuf, device=local)
+    nmat = 2 * n - 3
+    # P parent trees per engine call: the engine gets P sets of directional CLV / scaler buffers and
+    # P sets of P matrices (plain index spaces of the C ABI: set j's indices are the tree's own
+    # shifted by j x nbuf resp. j x nmat; the tips are shared), so one ptgpu_update_partials walks
+    # the P trees' op lists and ONE ptgpu_score_nni_batch scores all their candidates -- the
+    # Newton kernel's last iterations (a handful of slow candidates) are then shared by P x 122
+    # candidates instead of 122
+    P = 1 if stress else max(1, args.parents_per_call)
+    e = Engine(n, P * nbuf, S, 4, P * nmat, P * nbuf, device=local)
     e.set_model(FREQS, SUBST, rates)
     tip_ids = np.arange(n, dtype=np.uint32)
     tip_ptrs = [host_aln[t].data_ptr() for t in range(n)]
     e.set_tip_states_batch(tip_ids, tip_ptrs)
     st_bytes = 8 * e.batch_sumtable_doubles()
+
+    def shift(arr, j):
+        """the op / candidate / matrix-index arrays of one tree moved into buffer set j"""
+        if j == 0:
+            return arr
+        out = arr.copy()
+        views = [out] if out.dtype.names and "parent_clv_index" in out.dtype.names else (
+            [out["p"], out["q"]] if out.dtype.names else [])
+        for v in views:
+            for side in ("parent", "child1", "child2"):
+                clv = v[side + "_clv_index"]
+                clv[clv >= n] += j * nbuf
+                sc = v[side + "_scaler_index"]
+                sc[sc >= 0] += j * nbuf
+                if side != "parent":
+                    v[side + "_matrix_index"] += j * nmat
+        if not views:
+            out = out + np.uint32(j * nmat)
+        return out
 
     # this rank's parents: descriptors prepared once (host integer work, like the alignment)
     work, bytes_partials, bytes_prepare, ncand_rank, full_bytes = [], 0, 0, 0, 0
@@ -746,6 +773,17 @@ def run_shape(args):
         bytes_prepare += (child + len(rows) * (st_bytes + 4)) * S
         ncand_rank += len(rows)
         work.append(item)
+    if P > 1:
+        # groups of P parents become one item each
+        grouped = []
+        for g0 in range(0, len(work), P):
+            grp = work[g0:g0 + P]
+            grouped.append(dict(midx=np.concatenate([shift(it["midx"], j) for j, it in enumerate(grp)]),
+                                mlen=np.concatenate([it["mlen"] for it in grp]),
+                                plan=np.concatenate([shift(it["plan"], j) for j, it in enumerate(grp)]),
+                                cands=np.concatenate([shift(it["cands"], j) for j, it in enumerate(grp)]),
+                                root=grp[0]["root"]))
+        work = grouped
     results = {}
 
     def step():
@@ -834,12 +872,12 @@ def run_shape(args):
             if stress else
             f"synthetic 64 taxa x 100000 sites GTR+G4 (BASELINE configs[3]): per step a batch of {int(ncand_all)} NNI "
             f"candidates = all 122 of each of {parents_total} parent trees (seeded NNI walk), parents dealt "
-            "round-robin to the GPUs")
+            f"round-robin to the GPUs, {P} parents' candidates per engine call")
     line = dict(metric="nni_candidates_scored_per_s", value=value, unit="candidates/s", n_gpus=world, steps=steps,
                 warmup=args.warmup, ms_per_step=ms / steps, higher_is_better=True,
                 scaling="weak" if stress else "strong", vs_baseline=None, dtype="f64", data="synthetic",
                 config=dict(workload=name, taxa=n, sites=S, rate_cats=4, alpha=args.alpha,
-                            candidates_per_step=int(ncand_all), parents_per_step=parents_total,
+                            candidates_per_step=int(ncand_all), parents_per_step=parents_total, parents_per_call=P,
                             parallelism=f"candidate-parallel x{world}",
                             l2="every parent's CLVs and sumtables (> 1 GB) exceed the 126 MB L2; no flush needed"),
                 clv_site_updates_per_s=site_updates / (ms * 1e-3),
@@ -1181,6 +1219,8 @@ def main():
                     choices=["synthetic", "ptw-ds1", "sharded", "cand100k", "stress1000"])
     ap.add_argument("--parents", type=int, default=0,
                     help="cand100k: parent trees per batch (0 = as many as give 10^5 candidates)")
+    ap.add_argument("--parents-per-call", type=int, default=8,
+                    help="cand100k: parent trees whose candidates are scored by ONE engine call")
     ap.add_argument("--alpha", type=float, default=None,
                     help="cand100k / stress1000: Gamma shape instead of DS1's 0.134946 (0.05: scaler stress)")
     ap.add_argument("--compress-patterns", action="store_true",

@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
 {
   constexpr int T = kSitesPerPass * C;
   extern __shared__ __align__(16) double ring[];
-  __shared__ double red[T / 32 < 1 ? 1 : T / 32];
+  __shared__ double red[2 * (T / 32 < 1 ? 1 : T / 32)];   // two sums per reduction (block_sum_n)
   __shared__ __align__(16) double smat[2 * C * kMatPad];
   __shared__ double sh_len;
   __shared__ int sh_done, sh_status;
@@ -570,12 +570,12 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
         for (unsigned int tile = t0; tile < t1; ++tile)
           blo_sumtable_sweep_tile<C>(a.v, a.m, st.a_clv, st.b_clv, a.sumtables + (size_t)e * a.entry_stride,
                                      tile, dg, out, a.vec_end);
-        const double s1 = block_sum<T>(out[0], red);
-        const double s2 = block_sum<T>(out[1], red);
+        double s12[2] = {out[0], out[1]};
+        block_sum_n<T, 2>(s12, red);   // the same tree per value as block_sum: same bits, half the barriers
         if (threadIdx.x == 0)
         {
-          a.partials[(size_t)w * 3 + 0] = s1;
-          a.partials[(size_t)w * 3 + 1] = s2;
+          a.partials[(size_t)w * 3 + 0] = s12[0];
+          a.partials[(size_t)w * 3 + 1] = s12[1];
         }
       }
       grid.sync();
@@ -609,8 +609,10 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
             a1 = __dadd_rn(a1, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 0));
             a2 = __dadd_rn(a2, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 1));
           }
-          a1 = block_sum<T>(a1, red);
-          a2 = block_sum<T>(a2, red);
+          double a12[2] = {a1, a2};
+          block_sum_n<T, 2>(a12, red);
+          a1 = a12[0];
+          a2 = a12[1];
           if (threadIdx.x == 0)
           {
             shard_put(a.comm, xq, 2 * e, a1);
@@ -644,8 +646,10 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
             a1 = __dadd_rn(a1, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 0));
             a2 = __dadd_rn(a2, __ldcg(prd + ((size_t)e * a.nchunks + t) * 3 + 1));
           }
-          a1 = block_sum<T>(a1, red);
-          a2 = block_sum<T>(a2, red);
+          double a12[2] = {a1, a2};
+          block_sum_n<T, 2>(a12, red);
+          a1 = a12[0];
+          a2 = a12[1];
         }
         NewtonState ns;
         if (threadIdx.x == 0)
@@ -692,12 +696,12 @@ __global__ void __launch_bounds__(kSitesPerPass *C, (C <= 4 && !CLUSTER ? PT_BLO
         const unsigned int t1 = min((chunk + 1) * a.chunk_tiles, a.ntiles);
         sweep_chunk<C, false>(a.m, a.sumtables + (size_t)e * a.entry_stride, nullptr, a.sites,
                               chunk * a.chunk_tiles, t1, dg, ring, out, lp, a.vec_end);
-        const double s1 = block_sum<T>(out[0], red);
-        const double s2 = block_sum<T>(out[1], red);
+        double s12[2] = {out[0], out[1]};
+        block_sum_n<T, 2>(s12, red);
         if (threadIdx.x == 0)
         {
-          pwr[(size_t)w * 3 + 0] = s1;
-          pwr[(size_t)w * 3 + 1] = s2;
+          pwr[(size_t)w * 3 + 0] = s12[0];
+          pwr[(size_t)w * 3 + 1] = s12[1];
         }
       }
       if (sharded) xq += 1;

@@ -336,10 +336,13 @@ int ptgpu_create(unsigned int tips, unsigned int clv_buffers, unsigned int sites
   e->prob_matrices = prob_matrices; e->scale_buffers = scale_buffers;
   e->ntiles = (sites + kTileSites - 1) / kTileSites;
   e->nheavy = (sites + kHeavyTile - 1) / kHeavyTile;
-  // Reduction units of every sum over sites: chunks of <= 8 tiles, at least ~768 of them on a long
-  // alignment, so that ONE branch's sweep (B = 1: OptimizeBranch, every Newton step of a whole-tree
-  // optimisation) still spreads over all SMs with several CTAs each.  A function of `sites` only.
-  e->chunk_tiles = std::min(8u, std::max(1u, e->ntiles / 768u));
+  // Reduction units of every sum over sites: chunks of up to 8 tiles (a tile = 256 sites), about a
+  // hundred of them on a mid-sized alignment and ~490 at 1M sites, so that ONE branch's sweep (B = 1:
+  // OptimizeBranch, every Newton step of a whole-tree optimisation) still spreads over all SMs, while a
+  // chunk stays long enough that the per-chunk reduction does not weigh on the batched sweeps
+  // (measured: 1-tile chunks at 100k sites held the batched Newton kernel at 0.64-0.72 of the HBM
+  // peak).  A function of `sites` only: results do not depend on launch geometry.
+  e->chunk_tiles = std::min(8u, std::max(1u, e->ntiles / 96u));
   e->nchunks = (e->ntiles + e->chunk_tiles - 1) / e->chunk_tiles;
   const size_t clv_stride = (size_t)sites * rate_cats * 4;
 #define CU_NEW(call)                                                                    \

@@ -287,13 +287,13 @@ Partition::Partition(pll_utree_t* tree,
   const bool directional = !std::getenv("PTGPU_NO_DIRECTIONAL");
   const unsigned int extra = directional ? 3 * inner_node_count() : 0;
   directional_base_ = directional ? inner_node_count() : 0;
-  // OptimizeAllBranches as one persistent kernel pays off while the procedure is bound by
-  // launch / barrier latency; from ~0.5M sites on every step is a bandwidth-bound pass over
-  // the alignment and the single-purpose kernels (more CTAs per SM) are ~10 % faster
-  // (measured on B200, 64 taxa: 25 vs 100 ms at 2k sites, 54 vs 113 at 100k, 120 vs 157 at
-  // 300k, 225 vs 219 at 600k, 318 vs 291 at 1M).
+  // OptimizeAllBranches is ONE persistent kernel (ptgpu_optimize_all_branches) at every size: 4 / 54 /
+  // 252 ms per call at 2k / 100k / 1M sites x 64 taxa against 100 / 113 / 364 ms for the reference's
+  // call-by-call sequence (which round 1 preferred above 500k sites, before the reduction tree gave a
+  // single branch's sweep enough CTAs).  PTGPU_STEPWISE_ALL_BRANCHES=1 or a site limit
+  // (PTGPU_FUSED_ALL_BRANCHES_MAX_SITES) bring the call-by-call form back for A/B runs.
   {
-    unsigned long limit = 500000;
+    unsigned long limit = ~0ul;
     if (const char* env = std::getenv("PTGPU_FUSED_ALL_BRANCHES_MAX_SITES")) limit = std::strtoul(env, nullptr, 10);
     stepwise_all_branches_ = std::getenv("PTGPU_STEPWISE_ALL_BRANCHES") != nullptr || site_count_ > limit;
   }
