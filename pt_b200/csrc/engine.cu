@@ -945,6 +945,12 @@ int ptgpu_update_partials(ptgpu_engine *e, const ptgpu_operation_t *ops, unsigne
     LaunchScope ls(e, PTGPU_KERNEL_PARTIALS);
     if (e->partials_version == 3)
     { DISPATCH_CATS(e, (partials_kernel<C><<<e->nheavy, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count))); }
+    else if (e->nheavy < 4u * (unsigned int)e->sm_count)
+    {
+      // too few 128-site tiles to fill the device: 64-site tiles, twice the warps (bit-identical)
+      const unsigned int tiles = (e->sites + 2 * kHeavySites - 1) / (2 * kHeavySites);
+      DISPATCH_CATS(e, (partials_kernel_v4<C, 2><<<tiles, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count)));
+    }
     else
     { DISPATCH_CATS(e, (partials_kernel_v4<C><<<e->nheavy, kHeavySites * C, 0, e->stream>>>(e->dev, e->d_ops, count))); }
   }
@@ -1452,7 +1458,7 @@ int shard_preload()
   PT_LOAD(tip_encode_kernel); PT_LOAD(tip_encode_batch_kernel); PT_LOAD(shard_allreduce_kernel);
   PT_LOAD(sum_partials_kernel); PT_LOAD(newton_update_kernel); PT_LOAD(newton_store_lnl_kernel);
   PT_LOAD(newton_reduce_kernel<false>); PT_LOAD(newton_reduce_kernel<true>);
-  PT_LOAD(pmatrix_kernel<C>); PT_LOAD(partials_kernel<C>); PT_LOAD(partials_kernel_v4<C>);
+  PT_LOAD(pmatrix_kernel<C>); PT_LOAD(partials_kernel<C>); PT_LOAD(partials_kernel_v4<C>); PT_LOAD((partials_kernel_v4<C, 2>));
   PT_LOAD(edge_lnl_kernel<C>); PT_LOAD(sumtable_kernel<C>);
   PT_LOAD(nni_prepare_kernel<C>); PT_LOAD(nni_prepare_kernel_v2<C>);
   PT_LOAD((newton_kernel<C, false>)); PT_LOAD((newton_kernel<C, true>));

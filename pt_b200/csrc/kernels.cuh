@@ -612,7 +612,11 @@ __device__ __forceinline__ void stage_matrices(const DevState &s, const DevOp &o
   cp_async_commit();
 }
 
-template <int C>
+// PASSES = sites per thread and op: 4 (tiles of 128 sites) on long alignments; 2 (tiles of 64) when the
+// alignment has too few 128-site tiles to fill the SMs -- a deep tree on a mid-sized alignment is a
+// chain of dependent L2 round trips per warp, and only more warps hide it.  Per-site arithmetic is
+// the same, so CLVs and scalers are bit-identical either way.
+template <int C, int PASSES = kHeavyPasses>
 __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 6 : 1))
     partials_kernel_v4(DevState s, const DevOp *__restrict__ ops, unsigned int nops)
 {
@@ -620,7 +624,7 @@ __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 6 : 1))
   __shared__ __align__(16) double mats[WARPS][2][2 * C * kMatPad];
   const int cat = threadIdx.x % C;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const unsigned int site0 = blockIdx.x * kHeavyTile + threadIdx.x / C;
+  const unsigned int site0 = blockIdx.x * (kHeavySites * PASSES) + threadIdx.x / C;
 
   DevOp op = ops[0];
   stage_matrices<C>(s, op, mats[warp][0], lane);
@@ -641,7 +645,7 @@ __global__ void __launch_bounds__(kHeavySites *C, (C <= 4 ? 6 : 1))
     const double *rmat = mats[warp][stage] + (C + cat) * kMatPad;
     double *dst = s.clv + (size_t)(op.parent_clv - s.n_tips) * s.clv_stride;
 #pragma unroll 1
-    for (int half = 0; half < kHeavyPasses; half += 2)
+    for (int half = 0; half < PASSES; half += 2)
     {
       double l[2][4], r[2][4], p[2][4];
       unsigned int sc[2];
