@@ -151,6 +151,7 @@ class Partition
   // registered and is computed in place.
   struct VisitResult {
     std::vector<double> lengths;   // by node_index of every record of the tree
+    std::function<void()> taken;   // if set: called (on the taker's thread) when the result is taken
   };
   // `directional`: with the buffers ScoreNniNeighborhood needs (4x the CLV memory)
   std::unique_ptr<Partition> Replica(bool directional = false) const;
@@ -164,6 +165,8 @@ class Partition
   static uint64_t VisitKeyFor(uint64_t content_id, pll_unode_t* root, unsigned int node_count);
   // the same for this partition's present content; 0 when that is not known exactly
   uint64_t VisitKey(pll_unode_t* root) const;
+  // the present content's id (ExactContentId of the tree and root it is exact for); 0 = not known
+  uint64_t ContentId() const { return content_id_; }
   static void PublishVisit(uint64_t key, std::shared_future<VisitResult> result);
   static bool VisitKnown(uint64_t key);
   static void ClearVisits();

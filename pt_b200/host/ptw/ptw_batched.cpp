@@ -89,10 +89,10 @@ int Run(int argc, const char* argv[])
     const auto visits = pt::pll::Partition::VisitStatistics();
     pt::move_tester::VisitPrefetcher& pf = pt::move_tester::VisitPrefetcher::Instance();
     std::fprintf(stderr, "visits ahead of time: %llu submitted (%llu declined), %llu taken by OptimizeAllBranches, "
-                         "%llu computed in place; %llu neighbourhoods scored ahead, %llu visits queued by workers "
-                         "walking ahead\n",
+                         "%llu computed in place; %llu neighbourhoods scored ahead, %llu visits chained after a failed "
+                         "sibling, %llu queued by workers walking ahead\n",
                  pf.submitted(), pf.declined(), visits.first, visits.second, pf.neighborhoods_taken(),
-                 pf.walked_ahead());
+                 pf.chained(), pf.walked_ahead());
   }
   pt::move_tester::VisitPrefetcher::Instance().Shutdown();   // before the partitions and the CUDA runtime go
   if (batched) {

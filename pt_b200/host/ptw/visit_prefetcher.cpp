@@ -37,6 +37,16 @@ bool SameModel(const pll::Model& a, const pll::Model& b)
 
 } // namespace
 
+VisitPrefetcher::Batch::~Batch()
+{
+  if (parent) pll_utree_destroy(parent, pll::cb_erase_data);
+}
+
+VisitPrefetcher::TreeHolder::~TreeHolder()
+{
+  if (t) pll_utree_destroy(t, pll::cb_erase_data);
+}
+
 VisitPrefetcher::Task::~Task()
 {
   if (tree) pll_utree_destroy(tree, pll::cb_erase_data);
@@ -85,7 +95,8 @@ void VisitPrefetcher::Shutdown()
   hoods_.clear();
   hood_order_.clear();
   speculated_.clear();
-  last_tree_.clear();
+  batches_.clear();
+  batch_order_.clear();
   pll::Partition::ClearVisits();
 }
 
@@ -95,6 +106,7 @@ void VisitPrefetcher::Submit(pll::Partition& owner, pll_utree_t* tree, pll_unode
   if (!enabled()) return;
   authority_.store(&authority, std::memory_order_relaxed);
   try {
+    NoteThreshold(authority);
     SubmitOrThrow(owner, tree, node, type);
   } catch (const std::exception& e) {
     // an optional optimisation must never disturb the walk: nothing of the wanderer's has been
@@ -170,21 +182,54 @@ bool VisitPrefetcher::Enqueue(int device, const pll::Model& model, pll_utree_t* 
   const uint64_t content = pll::Partition::ExactContentId(pll::Partition::TreeFingerprint(tree),
                                                           GetVirtualRoot(tree)->node_index);
   const uint64_t key = pll::Partition::VisitKeyFor(content, GetVirtualRoot(task->tree), n_nodes);
-  if (!key || pll::Partition::VisitKnown(key)) return false;
+  if (!key) return false;
   task->device = device;
   task->model = model;
   task->depth = depth;
   task->node_index = node->node_index;
   task->type = type;
+  // the group this move belongs to: the moves one QueueMoves call sends here, in order (depth 0 only)
+  std::shared_ptr<Batch> group;
+  if (depth == 0) {
+    const Authority* authority = authority_.load(std::memory_order_relaxed);
+    std::lock_guard<std::mutex> lock(mutex_);
+    const std::pair<const pll_utree_t*, uint64_t> id(tree, content);
+    std::shared_ptr<Batch>& slot = batches_[id];
+    if (!slot) {
+      slot = std::make_shared<Batch>();
+      slot->id = ++batch_;
+      batch_order_.push_back(id);
+      while (batch_order_.size() > 64) {
+        batches_.erase(batch_order_.front());
+        batch_order_.pop_front();
+      }
+    }
+    group = batches_[id];
+    if (!group->parent) {
+      group->device = device;
+      group->model = model;
+      group->parent_root_index = GetVirtualRoot(tree)->node_index;
+      // the parent tree with the flags a FULL traversal at its root leaves
+      group->parent = pll_utree_clone(tree);
+      if (!group->parent) throw std::runtime_error("pll_utree_clone failed");
+      pll_utree_every(group->parent, pll::cb_copy_clv_traversal);
+      std::vector<pll_unode_t*> buffer(n_nodes, nullptr);
+      unsigned int count = 0;
+      pll_utree_traverse(GetVirtualRoot(group->parent), PLL_TREE_TRAVERSE_POSTORDER, pll::cb_full_traversal,
+                         buffer.data(), &count);
+    }
+    // two moves of a queue can lead to the same topology (the root entry repeats its first child's
+    // edge): the authority grants only the first (src/authority.cpp:139-152), so only that one counts
+    if (authority && !group->topologies.insert(authority->GetKey(task->tree)).second) return false;
+    task->group = group;
+    task->index = task->run_start = group->moves.size();
+    group->moves.emplace_back(node->node_index, type);
+  }
+  if (pll::Partition::VisitKnown(key)) return false;   // (a worker walking ahead got there first)
   pll::Partition::PublishVisit(key, task->result.get_future().share());
   {
     std::lock_guard<std::mutex> lock(mutex_);
-    std::pair<const pll_utree_t*, uint64_t>& last = last_tree_[device];
-    if (last.first != tree || last.second != content) {
-      last = std::make_pair(static_cast<const pll_utree_t*>(tree), content);
-      ++batch_;
-    }
-    task->batch = batch_;
+    task->batch = group ? group->id : ++batch_;
     queue_.push_back(std::move(task));
     ++submitted_;
   }
@@ -224,7 +269,9 @@ void VisitPrefetcher::WalkAhead(const Task& done, pll::Partition& rep,
 
 bool VisitPrefetcher::TakeNeighborhood(pll_utree_t* tree, std::vector<pll::Partition::NniScore>* out)
 {
-  if (!enabled() || !score_hoods_) return false;
+  if (!enabled()) return false;
+  if (const Authority* authority = authority_.load(std::memory_order_relaxed)) NoteThreshold(*authority);
+  if (!score_hoods_) return false;
   const uint64_t fp = pll::Partition::TreeFingerprint(tree);
   std::shared_future<Neighborhood> pending;
   {
@@ -258,88 +305,307 @@ bool VisitPrefetcher::TakeNeighborhood(pll_utree_t* tree, std::vector<pll::Parti
   return true;
 }
 
+void VisitPrefetcher::NoteThreshold(const Authority& authority)
+{
+  const double now = authority.GetThresholdScore();
+  std::lock_guard<std::mutex> lock(mutex_);
+  if (have_threshold_ && now == last_threshold_) return;
+  const bool moved = have_threshold_;
+  have_threshold_ = true;
+  last_threshold_ = now;
+  if (!moved || batches_.empty()) return;
+  rescan_ = true;
+  wake_.notify_one();
+}
+
+double VisitPrefetcher::RunVisit(Task& task, pll::Partition& rep, bool state_on_replica,
+                                 const std::function<void(double)>& before_release)
+{
+  if (!SameModel(rep.GetModel(), task.model)) {
+    rep.SetModel(task.model);
+    state_on_replica = false;
+  }
+  if (!task.previous) {
+    pll_unode_t* moved = RecordByIndex(task.tree, task.node_index);
+    // back to the parent tree: its exact CLVs, oriented at its root, are what the wanderer's
+    // partition holds when it starts this visit
+    pll_utree_nni(moved, task.type, nullptr);
+    rep.TraversalUpdate(RecordByIndex(task.tree, task.parent_root_index), pll::TraversalType::FULL);
+    // the move, as MoveForward applies it
+    pll_utree_nni(moved, task.type, nullptr);
+    pll::InvalidateEdgeClvs(moved);
+  } else if (!state_on_replica ||
+             rep.ContentId() != pll::Partition::ExactContentId(pll::Partition::TreeFingerprint(task.previous->t),
+                                                               GetVirtualRoot(task.previous->t)->node_index)) {
+    // the failed sibling's optimised tree, everything exact and oriented at its root: the state its
+    // visit ended in (Partition::OptimizeAllBranches, TakePublishedVisit)
+    rep.TraversalUpdate(GetVirtualRoot(task.previous->t), pll::TraversalType::FULL);
+  }
+  pll_unode_t* root = GetVirtualRoot(task.tree);
+  rep.OptimizeAllBranches(root);
+  pll::Partition::VisitResult res;
+  const unsigned int n = task.tree->tip_count + task.tree->inner_count;
+  res.lengths.assign(task.tree->tip_count + 3 * task.tree->inner_count, 0.0);
+  for (unsigned int i = 0; i < n; ++i) {
+    pll_unode_t* first = task.tree->nodes[i];
+    pll_unode_t* r = first;
+    do {
+      if (r->node_index < res.lengths.size()) res.lengths[r->node_index] = r->length;
+      r = r->next;
+    } while (r && r != first);
+  }
+  // what the wanderer does next (src/wanderer.cpp:192-198); the CLVs already face the root
+  rep.TraversalUpdate(root, pll::TraversalType::PARTIAL);
+  const double lnl = rep.LogLikelihood(root);
+  before_release(lnl);   // what must be announced before the wanderer can see this visit's result
+  if (task.group) {
+    const std::shared_ptr<Batch> group = task.group;
+    const VisitId id(task.index, task.previous ? task.run_start : task.index);
+    res.taken = [this, group, id, lnl] { Taken(group, id, lnl); };
+  }
+  task.result.set_value(std::move(res));
+  return lnl;
+}
+
+// What the wanderer is about to decide about the tree it has just taken (src/wanderer.cpp:196-207,
+// src/authority.cpp:191-199): final for this queue's path.  If the tree fails, the visit of the next
+// move is registered before this returns -- the wanderer asks for it within microseconds.
+void VisitPrefetcher::Taken(const std::shared_ptr<Batch>& group, VisitId id, double lnl)
+{
+  const Authority* authority = authority_.load(std::memory_order_relaxed);
+  if (!authority || !enabled()) return;
+  const bool good = lnl >= authority->GetThresholdScore();
+  {
+    std::lock_guard<std::mutex> lock(mutex_);
+    if (stop_) return;
+    group->verdict[id] = good;
+  }
+  if (good) return;
+  try {
+    StartJobs(group);
+  } catch (...) {
+  }
+}
+
+void VisitPrefetcher::StartJobs(const std::shared_ptr<Batch>& group)
+{
+  for (const Job& job : Scan(group)) {
+    std::unique_ptr<Task> t = BuildSibling(job);
+    if (!t) continue;
+    std::lock_guard<std::mutex> lock(mutex_);
+    queue_.push_back(std::move(t));
+    wake_.notify_one();
+  }
+}
+
+// The queue of `group` as the wanderer will walk it under the present threshold (see "Sibling
+// chains" in the header): which visit follows which, as far as the finished visits tell.
+std::vector<VisitPrefetcher::Job> VisitPrefetcher::Scan(const std::shared_ptr<Batch>& group)
+{
+  std::vector<Job> jobs;
+  const Authority* authority = authority_.load(std::memory_order_relaxed);
+  if (!group || !authority) return jobs;
+  const double threshold = authority->GetThresholdScore();
+  std::lock_guard<std::mutex> lock(mutex_);
+  bool exact = true;
+  size_t run_start = 0;
+  for (size_t i = 0; i < group->moves.size(); ++i) {
+    const auto it = group->done.find(exact ? VisitId(i, i) : VisitId(i, run_start));
+    if (it == group->done.end()) break;   // not finished yet: its completion scans again
+    const auto v = group->verdict.find(it->first);
+    if (v != group->verdict.end() ? v->second : it->second.lnl >= threshold) {
+      exact = true;   // good (so far): the wanderer descends, and MoveBack restores the exact parent
+      continue;
+    }
+    if (exact) run_start = i;
+    exact = false;
+    if (i + 1 >= group->moves.size()) break;
+    if (!group->started.insert(VisitId(i + 1, run_start)).second) continue;
+    Job job;
+    job.group = group;
+    job.index = i + 1;
+    job.run_start = run_start;
+    job.previous = it->second.tree;
+    job.run.assign(group->moves.begin() + run_start, group->moves.begin() + i + 1);
+    job.move = group->moves[i + 1];
+    jobs.push_back(std::move(job));
+  }
+  return jobs;
+}
+
+// the visit of job.move from the state the failed visit job.previous leaves behind: the parent
+// tree's flags with the invalidated edge ends of every move of the present run of failures
+std::unique_ptr<VisitPrefetcher::Task> VisitPrefetcher::BuildSibling(const Job& job)
+{
+  std::unique_ptr<Task> task(new Task);
+  const pll_utree_t* failed = job.previous->t;
+  const unsigned int n_nodes = failed->tip_count + failed->inner_count;
+  {
+    struct Holder {
+      pll_utree_t* t;
+      ~Holder() { if (t) pll_utree_destroy(t, pll::cb_erase_data); }
+    } parent{pll_utree_clone(job.group->parent)};
+    if (!parent.t) return nullptr;
+    pll_utree_every(parent.t, pll::cb_copy_clv_traversal);
+    // every failed sibling was applied, had its edge ends invalidated and was undone (src/wanderer.cpp:160-176)
+    for (const std::pair<unsigned int, int>& m : job.run) pll::InvalidateEdgeClvs(RecordByIndex(parent.t, m.first));
+    pll_unode_t* moved = RecordByIndex(parent.t, job.move.first);
+    pll_utree_nni(moved, job.move.second, nullptr);
+    pll::InvalidateEdgeClvs(moved);
+    task->tree = pll_utree_clone(parent.t);
+    if (!task->tree) return nullptr;
+    pll_utree_every(task->tree, pll::cb_copy_clv_traversal);
+  }
+  const uint64_t content = pll::Partition::ExactContentId(pll::Partition::TreeFingerprint(failed),
+                                                          GetVirtualRoot(job.previous->t)->node_index);
+  const uint64_t key = pll::Partition::VisitKeyFor(content, GetVirtualRoot(task->tree), n_nodes);
+  if (!key || pll::Partition::VisitKnown(key)) return nullptr;
+  task->group = job.group;
+  task->index = job.index;
+  task->run_start = job.run_start;
+  task->previous = job.previous;
+  task->device = job.group->device;
+  task->model = job.group->model;
+  task->node_index = job.move.first;
+  task->parent_root_index = job.group->parent_root_index;
+  task->type = job.move.second;
+  task->depth = 0;
+  task->batch = job.group->id;
+  pll::Partition::PublishVisit(key, task->result.get_future().share());
+  ++chained_;
+  static const bool debug = std::getenv("PTGPU_PREFETCH_DEBUG") != nullptr;
+  if (debug)
+    std::fprintf(stderr, "[prefetch] chained key %016llx content %016llx batch %llu index %zu run_start %zu\n",
+                 (unsigned long long)key, (unsigned long long)content, task->batch, task->index, task->run_start);
+  return task;
+}
+
 void VisitPrefetcher::Work()
 {
+  static const bool debug = std::getenv("PTGPU_PREFETCH_DEBUG") != nullptr;
   for (;;) {
     std::unique_ptr<Task> task;
     std::unique_ptr<pll::Partition> rep;
+    std::vector<std::shared_ptr<Batch>> rescan;
     {
       std::unique_lock<std::mutex> lock(mutex_);
-      wake_.wait(lock, [this] { return stop_ || !queue_.empty(); });
+      wake_.wait(lock, [this] { return stop_ || rescan_ || !queue_.empty(); });
       if (stop_) break;
-      // The wanderer walks depth first: the queue it fills last is the one it empties first
-      // (move_queues_ is a stack, src/wanderer.cpp:122-131), and each queue from its front
-      // (:157-158).  So: what the wanderer itself asked for before speculation, newest batch
-      // first, oldest submission within it.
-      size_t pick = 0;
-      for (size_t i = 1; i < queue_.size(); ++i) {
-        const Task& a = *queue_[i];
-        const Task& b = *queue_[pick];
-        if (a.depth < b.depth || (a.depth == b.depth && a.batch > b.batch)) pick = i;
+      if (rescan_) {
+        rescan_ = false;
+        for (const auto& b : batches_) rescan.push_back(b.second);
+      } else {
+        // The wanderer walks depth first: the queue it fills last is the one it empties first
+        // (move_queues_ is a stack, src/wanderer.cpp:122-131), and each queue from its front
+        // (:157-158).  So: what the wanderer itself asked for before speculation, newest batch
+        // first, in queue order within it.
+        size_t pick = 0;
+        for (size_t i = 1; i < queue_.size(); ++i) {
+          const Task& a = *queue_[i];
+          const Task& b = *queue_[pick];
+          if (a.depth != b.depth ? a.depth < b.depth
+                                 : (a.batch != b.batch ? a.batch > b.batch : a.index < b.index))
+            pick = i;
+        }
+        task = std::move(queue_[pick]);
+        queue_.erase(queue_.begin() + pick);
+        Pool& pool = pools_[task->device];
+        replica_back_.wait(lock, [&] { return stop_ || !pool.free.empty(); });
+        if (stop_) break;   // the task's promise breaks: the wanderer computes the visit in place
+        rep = std::move(pool.free.back());
+        pool.free.pop_back();
       }
-      task = std::move(queue_[pick]);
-      queue_.erase(queue_.begin() + pick);
-      Pool& pool = pools_[task->device];
-      replica_back_.wait(lock, [&] { return stop_ || !pool.free.empty(); });
-      if (stop_) break;   // the task's promise breaks: the wanderer computes the visit in place
-      rep = std::move(pool.free.back());
-      pool.free.pop_back();
     }
-    try {
-      if (!SameModel(rep->GetModel(), task->model)) rep->SetModel(task->model);
-      pll_unode_t* moved = RecordByIndex(task->tree, task->node_index);
-      // back to the parent tree: its exact CLVs, oriented at its root, are what the wanderer's
-      // partition holds when it starts this visit
-      pll_utree_nni(moved, task->type, nullptr);
-      rep->TraversalUpdate(RecordByIndex(task->tree, task->parent_root_index), pll::TraversalType::FULL);
-      // the move, as MoveForward applies it
-      pll_utree_nni(moved, task->type, nullptr);
-      pll::InvalidateEdgeClvs(moved);
-      rep->OptimizeAllBranches(GetVirtualRoot(task->tree));
-      pll::Partition::VisitResult res;
-      const unsigned int n = task->tree->tip_count + task->tree->inner_count;
-      res.lengths.assign(task->tree->tip_count + 3 * task->tree->inner_count, 0.0);
-      for (unsigned int i = 0; i < n; ++i) {
-        pll_unode_t* first = task->tree->nodes[i];
-        pll_unode_t* r = first;
-        do {
-          if (r->node_index < res.lengths.size()) res.lengths[r->node_index] = r->length;
-          r = r->next;
-        } while (r && r != first);
-      }
-      // the neighbourhood of the optimised tree, for the wanderer's QueueMoves: announced before
-      // the visit's result is released, so the wanderer cannot get ahead of the announcement
-      std::promise<Neighborhood> hood;
-      const bool score = score_hoods_ && radius_ >= 0;
-      if (score) {
-        const uint64_t fp = pll::Partition::TreeFingerprint(task->tree);
-        std::lock_guard<std::mutex> lock(mutex_);
-        if (hoods_.emplace(fp, hood.get_future().share()).second) hood_order_.push_back(fp);
-        while (hood_order_.size() > 4096) {
-          hoods_.erase(hood_order_.front());
-          hood_order_.pop_front();
-        }
-      }
-      task->result.set_value(std::move(res));
-      if (score) {
-        std::vector<pll::Partition::NniScore> moves;
+    if (!rescan.empty()) {
+      // the threshold has moved: visits found good before may have failed since
+      std::sort(rescan.begin(), rescan.end(),
+                [](const std::shared_ptr<Batch>& a, const std::shared_ptr<Batch>& b) { return a->id > b->id; });
+      for (const std::shared_ptr<Batch>& group : rescan) {
         try {
-          moves = rep->ScoreNniNeighborhood(task->tree, radius_);
-          Neighborhood scored;
-          for (const pll::Partition::NniScore& m : moves)
-            scored.push_back(IndexedScore{m.node->node_index, m.type, m.length, m.lnl});
-          hood.set_value(std::move(scored));
+          StartJobs(group);
         } catch (...) {
-          hood.set_exception(std::current_exception());
-          moves.clear();
         }
-        if (!moves.empty()) WalkAhead(*task, *rep, moves);
       }
-    } catch (...) {
+      continue;
+    }
+    // the visit; then, while the optimised tree is not a good one and the wanderer's path goes on
+    // from it, the next move of the same queue on the same replica (whose content is that state)
+    std::shared_ptr<TreeHolder> on_replica;   // the tree whose exact CLVs the replica holds
+    while (task) {
+      std::unique_ptr<Task> next;
       try {
-        task->result.set_exception(std::current_exception());
-      } catch (const std::future_error&) {   // already fulfilled: the failure came after the visit
+        std::promise<Neighborhood> hood;
+        bool good = true, score = false;
+        const bool state_on_replica = task->previous && task->previous == on_replica;
+        const double lnl = RunVisit(*task, *rep, state_on_replica, [&](double value) {
+          const Authority* authority = authority_.load(std::memory_order_relaxed);
+          good = !authority || value >= authority->GetThresholdScore();
+          score = good && score_hoods_ && radius_ >= 0;
+          if (!score) return;
+          // the neighbourhood of the optimised tree, for the wanderer's QueueMoves: announced before
+          // the visit's result is released, so the wanderer cannot get ahead of the announcement
+          const uint64_t fp = pll::Partition::TreeFingerprint(task->tree);
+          std::lock_guard<std::mutex> lock(mutex_);
+          if (hoods_.emplace(fp, hood.get_future().share()).second) hood_order_.push_back(fp);
+          while (hood_order_.size() > 4096) {
+            hoods_.erase(hood_order_.front());
+            hood_order_.pop_front();
+          }
+        });
+        if (debug)
+          std::fprintf(stderr, "[prefetch] visit %s batch %llu index %zu/%zu run_start %zu good %d\n",
+                       !task->previous ? "A" : (state_on_replica ? "B" : "B'"), task->batch, task->index,
+                       task->group ? task->group->moves.size() : 0, task->run_start, (int)good);
+        on_replica.reset();
+        if (score) {
+          std::vector<pll::Partition::NniScore> moves;
+          try {
+            moves = rep->ScoreNniNeighborhood(task->tree, radius_);
+            Neighborhood scored;
+            for (const pll::Partition::NniScore& m : moves)
+              scored.push_back(IndexedScore{m.node->node_index, m.type, m.length, m.lnl});
+            hood.set_value(std::move(scored));
+          } catch (...) {
+            hood.set_exception(std::current_exception());
+            moves.clear();
+          }
+          if (!moves.empty()) WalkAhead(*task, *rep, moves);
+        }
+        if (task->group) {
+          // keep the optimised tree: the next move of the queue may have to start from it
+          std::shared_ptr<TreeHolder> kept = std::make_shared<TreeHolder>(task->tree);
+          task->tree = nullptr;
+          {
+            std::lock_guard<std::mutex> lock(mutex_);
+            task->group->done[VisitId(task->index, task->previous ? task->run_start : task->index)] = Done{lnl, kept};
+          }
+          // (the neighbourhood scoring works on directional buffers and leaves the per-node CLVs alone)
+          on_replica = kept;
+          for (const Job& job : Scan(task->group)) {
+            std::unique_ptr<Task> t = BuildSibling(job);
+            if (!t) continue;
+            if (!next && t->previous == on_replica) {
+              next = std::move(t);
+              continue;
+            }
+            std::lock_guard<std::mutex> lock(mutex_);
+            queue_.push_back(std::move(t));
+            wake_.notify_one();
+          }
+        }
+      } catch (...) {
+        try {
+          task->result.set_exception(std::current_exception());
+        } catch (const std::future_error&) {   // already fulfilled: the failure came after the visit
+        }
       }
+      task = std::move(next);
+      bool stopping;
+      {
+        std::lock_guard<std::mutex> lock(mutex_);
+        stopping = stop_;
+      }
+      if (stopping) task.reset();
     }
     task.reset();
     std::lock_guard<std::mutex> lock(mutex_);

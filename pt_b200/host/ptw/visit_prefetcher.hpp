@@ -32,6 +32,22 @@
 // optimised tree's fingerprint; BatchedNeighborhood takes them from there when the wanderer,
 // having found the tree good, asks about its first move.
 //
+// Sibling chains.  The one start state that is NOT "exact CLVs of the parent" is the visit of a
+// move whose preceding sibling did not lead to a good tree: the partition then still holds THAT
+// tree's CLVs (src/wanderer.cpp:176-186), and the parent tree's flags carry the invalidated edge
+// ends of every sibling tried since its last FULL traversal.  The workers follow each queue the way
+// the wanderer will (Scan): move 0 from the exact parent; after a visit whose optimised tree is
+// below the authority's threshold the next move from the state that visit left (the failed tree's
+// exact CLVs -- still on the replica if the same worker goes on, otherwise put there by one FULL
+// traversal of the kept optimised tree -- and the flags of the run of failures); after a good tree
+// the next move from the exact parent again (MoveBack's FULL traversal, :232-239).  The threshold
+// only ever rises (src/authority.cpp:205-211), so "failed" is final while "good" is not: every
+// queue is followed again whenever the threshold has moved (the wanderer's next question shows
+// it), and the visits a changed verdict calls for are started then -- the wanderer, walking depth
+// first, returns to the later moves of a queue long after.  Both variants of a move may thus be
+// computed; only the one whose start state occurs is ever taken.  Rejected trees get no
+// neighbourhood scores: the wanderer never queues moves from them.
+//
 // Walking ahead (PTGPU_PREFETCH_DEPTH=d, default 0 = off).  A depth-first walk descends into a tree
 // the moment it has been found good, so the visit of its first move is only asked for when the
 // wanderer gets there.  With d > 0 a worker that has optimised a tree and scored its neighbourhood
@@ -53,10 +69,12 @@
 #include <atomic>
 #include <condition_variable>
 #include <deque>
+#include <functional>
 #include <future>
 #include <map>
 #include <memory>
 #include <mutex>
+#include <set>
 #include <thread>
 #include <unordered_set>
 #include <vector>
@@ -98,13 +116,48 @@ class VisitPrefetcher
   unsigned long long declined() const { return declined_; }
   unsigned long long neighborhoods_taken() const { return hoods_taken_; }
   unsigned long long walked_ahead() const { return walked_ahead_; }
+  unsigned long long chained() const { return chained_; }
 
   ~VisitPrefetcher();
 
  private:
   VisitPrefetcher();
 
+  struct TreeHolder {
+    pll_utree_t* t = nullptr;
+    explicit TreeHolder(pll_utree_t* tree) : t(tree) {}
+    TreeHolder(const TreeHolder&) = delete;
+    TreeHolder& operator=(const TreeHolder&) = delete;
+    ~TreeHolder();
+  };
+  // a finished visit: the optimised tree (lengths as OptimizeAllBranches left them) and its lnL
+  struct Done {
+    double lnl;
+    std::shared_ptr<TreeHolder> tree;
+  };
+  typedef std::pair<size_t, size_t> VisitId;   // (index in the queue, first move of the run of failures it
+                                               //  ends; == index for the visit from the exact parent)
+
+  // the moves of one QueueMoves call that reached the prefetcher, in order, and the tree they
+  // are moves of (a private clone carrying the flags a FULL traversal at its root leaves)
+  struct Batch {
+    unsigned long long id = 0;
+    pll_utree_t* parent = nullptr;
+    int device = 0;
+    pll::Model model;
+    unsigned int parent_root_index = 0;
+    std::vector<std::pair<unsigned int, int>> moves;   // (node_index, type), submission order
+    std::unordered_set<CompressedTree> topologies;     // of the trees the moves lead to (duplicates are dropped)
+    std::map<VisitId, Done> done;                      // finished visits of this queue
+    std::map<VisitId, bool> verdict;                   // taken by the wanderer: was the tree good THEN (final)
+    std::set<VisitId> started;                         // visits after a failed sibling already started
+    ~Batch();
+  };
+
   struct Task {
+    std::shared_ptr<Batch> group;     // null for visits queued by workers walking ahead
+    size_t index = 0, run_start = 0;  // position in group->moves; first move of the present run of failed siblings
+    std::shared_ptr<TreeHolder> previous;   // the failed sibling's optimised tree this visit starts from (null: exact parent)
     int device;
     pll::Model model;
     pll_utree_t* tree = nullptr;      // private clone WITH the move applied and the start flags set
@@ -116,6 +169,14 @@ class VisitPrefetcher
     std::promise<pll::Partition::VisitResult> result;
     ~Task();
   };
+  // a visit Scan found missing: move `index` of the queue after the failed visit `previous`
+  struct Job {
+    std::shared_ptr<Batch> group;
+    size_t index, run_start;
+    std::shared_ptr<TreeHolder> previous;
+    std::vector<std::pair<unsigned int, int>> run;   // the failed moves since the last exact state
+    std::pair<unsigned int, int> move;
+  };
   struct IndexedScore { unsigned int node_index; int type; double length, lnl; };
   typedef std::vector<IndexedScore> Neighborhood;
 
@@ -124,6 +185,19 @@ class VisitPrefetcher
   // queues the visit of move (node, type) of `tree`, whose exact CLVs (oriented at its virtual
   // root) the visiting partition will hold; false if that visit is already known
   bool Enqueue(int device, const pll::Model& model, pll_utree_t* tree, pll_unode_t* node, int type, int depth);
+  // one visit on `rep`; returns the optimised tree's lnL.  The start state: task.previous null --
+  // the exact parent (made here); else the failed sibling's exact CLVs, which `rep` already holds
+  // if `state_on_replica`, else made here by a FULL traversal of task.previous
+  double RunVisit(Task& task, pll::Partition& rep, bool state_on_replica,
+                  const std::function<void(double)>& before_release);
+  // follows the queue as the wanderer will under the present threshold; the visits that calls for
+  // and nobody has started yet (marked started here).  Takes mutex_.
+  std::vector<Job> Scan(const std::shared_ptr<Batch>& group);
+  std::unique_ptr<Task> BuildSibling(const Job& job);
+  void NoteThreshold(const Authority& authority);
+  // the wanderer has taken this visit's result (called on its thread, from OptimizeAllBranches)
+  void Taken(const std::shared_ptr<Batch>& group, VisitId id, double lnl);
+  void StartJobs(const std::shared_ptr<Batch>& group);
   void WalkAhead(const Task& done, pll::Partition& rep, const std::vector<pll::Partition::NniScore>& scored);
 
   // One pool of replicas per device, shared by every wanderer on it (all partitions of a ptw
@@ -141,9 +215,14 @@ class VisitPrefetcher
   std::condition_variable wake_, replica_back_;
   std::deque<std::unique_ptr<Task>> queue_;
   bool stop_ = false;
+  bool rescan_ = false;           // the threshold has moved: follow every queue again
+  double last_threshold_ = 0.0;
+  bool have_threshold_ = false;
   std::atomic<bool> disabled_{false};
   unsigned long long batch_ = 0;
-  std::map<int, std::pair<const pll_utree_t*, uint64_t>> last_tree_;   // per device: latest batch's tree
+  std::map<std::pair<const pll_utree_t*, uint64_t>, std::shared_ptr<Batch>> batches_;   // by (tree, content)
+  std::deque<std::pair<const pll_utree_t*, uint64_t>> batch_order_;
+  std::atomic<unsigned long long> chained_{0};
   unsigned long long submitted_ = 0, declined_ = 0;
 
   std::map<uint64_t, std::shared_future<Neighborhood>> hoods_;

@@ -430,6 +430,11 @@ uint64_t Partition::VisitKeyFor(uint64_t content_id, pll_unode_t* root, unsigned
   h ^= flags + 0xc2b2ae3d27d4eb4full + (h << 6) + (h >> 2);
   h ^= 0x165667b19e3779f9ull * (root->node_index + 1) + (h << 6) + (h >> 2);
   h ^= h >> 29; h *= 0xbf58476d1ce4e5b9ull; h ^= h >> 32;
+  static const bool debug = std::getenv("PTGPU_PREFETCH_DEBUG") != nullptr;
+  if (debug)
+    std::fprintf(stderr, "[prefetch] key %016llx = content %016llx tree %016llx flags %016llx root %u\n",
+                 (unsigned long long)(h ? h : 1), (unsigned long long)content_id, (unsigned long long)tree,
+                 (unsigned long long)flags, root->node_index);
   return h ? h : 1;
 }
 
@@ -519,6 +524,7 @@ bool Partition::TakePublishedVisit(uint64_t key, pll_unode_t* root)
     } while (r && r != n);
   }
   TraversalUpdate(root, TraversalType::FULL);
+  if (res.taken) res.taken();
   return true;
 }
 
@@ -801,7 +807,12 @@ void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
   StatScope stat(kStatAllBranches, !is_replica_);
   if (!use_pllmod && !is_replica_ && g_visits_used.load(std::memory_order_relaxed)) {
     const uint64_t key = VisitKey(tree);
-    if (key && TakePublishedVisit(key, tree)) {
+    const bool hit = key && TakePublishedVisit(key, tree);
+    static const bool debug = std::getenv("PTGPU_PREFETCH_DEBUG") != nullptr;
+    if (debug)
+      std::fprintf(stderr, "[prefetch] wanderer key %016llx content %016llx %s\n", (unsigned long long)key,
+                   (unsigned long long)content_id_, hit ? "hit" : "MISS");
+    if (hit) {
       g_visits_served += 1;
       return;
     }

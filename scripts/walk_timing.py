@@ -23,7 +23,7 @@ def run(label, binary, threads, data, **env):
     r = subprocess.run(cmd, capture_output=True, text=True, env=e)
     dt = time.perf_counter() - t0
     note = [l for l in r.stderr.splitlines() if l.startswith("visits")]
-    print(f"{label:32s} {dt:7.2f} s  rc={r.returncode} | {note[0][22:150] if note else ''}", flush=True)
+    print(f"{label:32s} {dt:7.2f} s  rc={r.returncode} | {note[0][22:260] if note else ''}", flush=True)
 
 
 def main():
