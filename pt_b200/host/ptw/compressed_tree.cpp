@@ -27,6 +27,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstdint>
 #include <cstring>
 #include <functional>
 #include <numeric>
@@ -81,8 +82,9 @@ void CompressedTree::Encode(const pll_utree_t* tree)
   const unsigned int tips = tree->tip_count, inner = tree->inner_count;
   const unsigned int records = tips + 3 * inner;
 
-  thread_local TipTable table;
-  const unsigned long long generation = g_generation.load();
+  thread_local TipTable tls_table;
+  TipTable& table = tls_table;   // (one TLS lookup, not one per use)
+  const unsigned long long generation = g_generation.load(std::memory_order_relaxed);
   if (table.generation != generation) {
     table.by_node_index.clear();
     table.generation = generation;
@@ -90,9 +92,11 @@ void CompressedTree::Encode(const pll_utree_t* tree)
   if (table.by_node_index.size() < records) table.by_node_index.resize(records);
 
   // rank (alphabetical position of the smallest label below) per record, dictionary index per tip
-  thread_local std::vector<unsigned int> rank, dict_index;
-  rank.assign(records, 0u);
-  dict_index.assign(records, 0u);
+  thread_local std::vector<unsigned int> tls_rank, tls_dict_index;
+  tls_rank.assign(records, 0u);
+  tls_dict_index.assign(records, 0u);
+  unsigned int* const rank = tls_rank.data();
+  unsigned int* const dict_index = tls_dict_index.data();
   const pll_unode_t* smallest = nullptr;
   for (unsigned int i = 0; i < tips; ++i) {
     const pll_unode_t* tip = tree->nodes[i];
@@ -111,9 +115,59 @@ void CompressedTree::Encode(const pll_utree_t* tree)
   const pll_unode_t* root = smallest->back;
   if (!root || !root->next) throw std::invalid_argument("Encode() requires an internal node");
 
+  // The authority builds the key of the same tree two or three times in a row (ProposeMove,
+  // ReportTestScore, RequestMove on one move: src/authority.cpp:124-183, src/wanderer.cpp:267-278).
+  // What the key depends on -- which record is linked to which, which label sits on which tip --
+  // is summed into two independent 64-bit hashes; the last few keys are kept per thread under them.
+  struct Memo {
+    uint64_t h1 = 0, h2 = 0;
+    unsigned long long generation = 0;
+    std::vector<bool> bits;
+    std::vector<index_type> labels;
+  };
+  constexpr int kMemo = 4;
+  thread_local Memo tls_memo[kMemo];
+  thread_local int tls_memo_next = 0;
+  Memo* const memo = tls_memo;
+  int& memo_next = tls_memo_next;
+  uint64_t h1 = records, h2 = tips;
+  {
+    auto mix = [&h1, &h2](uint64_t a, uint64_t b) {
+      uint64_t x = (a + 1) * 0x9e3779b97f4a7c15ull ^ (b + 1) * 0xc2b2ae3d27d4eb4full;
+      x ^= x >> 29; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 32;
+      h1 += x;
+      uint64_t y = (a + 1) * 0xd6e8feb86659fd93ull + (b + 1) * 0x165667b19e3779f9ull;
+      y ^= y >> 31; y *= 0x94d049bb133111ebull; y ^= y >> 30;
+      h2 += y;
+    };
+    for (unsigned int i = 0; i < tips; ++i) {
+      const pll_unode_t* tip = tree->nodes[i];
+      mix(tip->node_index, tip->back->node_index);
+      mix(records + tip->node_index, dict_index[tip->node_index]);
+    }
+    for (unsigned int i = tips; i < tips + inner; ++i) {
+      const pll_unode_t* r = tree->nodes[i];
+      mix(r->node_index, r->back->node_index);
+      mix(r->next->node_index, r->next->back->node_index);
+      mix(r->next->next->node_index, r->next->next->back->node_index);
+      // the ring itself (which three records form a node)
+      const unsigned int lo = std::min(r->node_index, std::min(r->next->node_index, r->next->next->node_index));
+      mix(2ull * records + r->node_index, lo);
+      mix(2ull * records + r->next->node_index, lo);
+      mix(2ull * records + r->next->next->node_index, lo);
+    }
+    for (int k = 0; k < kMemo; ++k)
+      if (memo[k].generation == generation && memo[k].h1 == h1 && memo[k].h2 == h2) {
+        bits_ = memo[k].bits;
+        label_indices_ = memo[k].labels;
+        return;
+      }
+  }
+
   // post-order: minimum rank below every record that hangs under the new root
   struct Frame { const pll_unode_t* r; bool expanded; };
-  thread_local std::vector<Frame> stack;
+  thread_local std::vector<Frame> tls_stack;
+  std::vector<Frame>& stack = tls_stack;
   stack.clear();
   stack.push_back(Frame{root->next->back, false});
   stack.push_back(Frame{root->next->next->back, false});
@@ -140,7 +194,8 @@ void CompressedTree::Encode(const pll_utree_t* tree)
   bits_.push_back(true);
   bits_.push_back(false);
   label_indices_.push_back(static_cast<index_type>(dict_index[smallest->node_index]));
-  thread_local std::vector<const pll_unode_t*> todo;
+  thread_local std::vector<const pll_unode_t*> tls_todo;
+  std::vector<const pll_unode_t*>& todo = tls_todo;
   todo.clear();
   {
     const pll_unode_t* a = root->next->back;
@@ -164,6 +219,13 @@ void CompressedTree::Encode(const pll_utree_t* tree)
     todo.push_back(b);
     todo.push_back(a);
   }
+  Memo& slot = memo[memo_next];
+  memo_next = (memo_next + 1) % kMemo;
+  slot.h1 = h1;
+  slot.h2 = h2;
+  slot.generation = generation;
+  slot.bits = bits_;
+  slot.labels = label_indices_;
 }
 
 // the Newick string the reference prints for a decoded key (src/ordered_tree.cpp:16-84:
