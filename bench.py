@@ -916,10 +916,12 @@ def run_ptw_ds1(args):
             out = os.path.join(d, "good.tsv")
             tested = os.path.join(d, "tested.tsv")
             cmd = [binary, "--raxml-info", os.path.join(ds1, "RAxML_info.DS1"), "--threads", str(threads),
-                   "--polling-time", "1" if threads > 1 else "100", "--lnl-offset", "-5", "--optimization-radius", "1", "--tested-trees", tested,
+                   "--polling-time", "1", "--lnl-offset", "-5", "--optimization-radius", "1", "--tested-trees", tested,
                    os.path.join(ds1, "RAxML_bestTree.DS1"), os.path.join(ds1, "DS1.fasta"), out]
             t0 = time.perf_counter()
             env = dict(os.environ)
+            if binary == ours:
+                env["PTGPU_HOST_STATS"] = "1"   # the driver's own wall-clock marks of its phases (stderr)
             if binary == ours and args.gpus > 0:
                 # wanderer-parallel over the first N GPUs: every wanderer's Partition takes the next
                 # visible device round-robin (pt_b200/host/src/pll_partition.cpp, pick_device)
@@ -929,10 +931,13 @@ def run_ptw_ds1(args):
             good = sum(1 for _ in open(out))
             ntested = sum(1 for _ in open(tested))
             moves = None
+            phases = {}
             for line in r.stderr.splitlines():
                 if line.startswith("batched move testing:"):
                     moves = int(line.split()[3])
-            return dt, good, ntested, moves
+                if line.startswith("[ptw_batched]"):
+                    phases[line[14:-10].strip()] = float(line.split()[-2])
+            return dt, good, ntested, moves, phases
 
     ours = os.path.join(ROOT, "pt_b200", "bin", "ptw_batched")
     ref = os.path.join(ROOT, "oracle", "_ref", "ptw_threads")
@@ -947,23 +952,28 @@ def run_ptw_ds1(args):
     runs = [walk(ours, W) for _ in range(args.steps)]
     clocks = sampler.stop(wall0, time.time())
     dt = sum(r[0] for r in runs) / len(runs)
-    _, good, ntested, moves = runs[-1]
+    _, good, ntested, moves, _ = runs[-1]
+    # where the process's wall time went, mean over the timed runs (CUDA start-up -- cuInit + the
+    # primary context, 0.5-2.4 s from box to box -- is inside "guru"; the rest of the process's
+    # wall time is the dynamic loader and process exit)
+    phases = {k: round(sum(r[4].get(k, 0.0) for r in runs) / len(runs), 3) for k in runs[-1][4]}
     line = dict(metric="nni_candidates_scored_per_s", value=moves / dt, unit="candidates/s", n_gpus=args.gpus,
                 steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * dt, higher_is_better=True,
                 scaling="strong", vs_baseline=None, dtype="f64", data="DS1 (27 taxa x 1949 sites)",
                 config=dict(workload="BASELINE configs[1] on DS1: ptw topography walk, --lnl-offset -5 "
                                      "--optimization-radius 1, %d wanderer(s) with one engine each, dealt round-robin "
                                      "to %d GPU(s); batched move testing, visits ahead of time (whole process, incl. "
-                                     "~1.1 s CUDA context creation per GPU)" % (W, args.gpus),
+                                     "CUDA start-up: see process_phases_s)" % (W, args.gpus),
                             wanderers=W,
                             taxa=27, sites=1949, rate_cats=4),
                 good_trees=good, tested_trees=ntested, evaluate_move_calls=moves, clocks=clocks,
+                process_phases_s=phases,
                 e2e=dict(value=moves / dt, unit="candidates/s", h2d_bytes_per_step=27 * 1949,
                          d2h_bytes_per_step=8 * moves,
                          note="the run IS end to end: files in, tables out"))
     if os.path.exists(ref) and not args.no_cpu_baseline:
         T = host_cores()
-        rdt, rgood, rtested, _ = walk(ref, T)
+        rdt, rgood, rtested, _, _ = walk(ref, T)
         line["cpu_baseline"] = dict(value=moves / rdt, unit="candidates/s", cores=T, kind="reference",
                                     sample=f"the unmodified ptw_threads --threads {T}, same arguments, "
                                            f"{rdt:.1f} s wall, {rgood} good / {rtested} tested trees "

@@ -27,6 +27,9 @@
 #include "guru.hpp"
 #include "options.hpp"
 
+#include <chrono>
+#include <cstdlib>
+
 namespace {
 
 // one "<lnl>\t<newick>" line per table entry
@@ -47,8 +50,21 @@ struct TreeSet {
   }
 };
 
+// wall-clock marks of the process's phases, printed with PTGPU_HOST_STATS
+struct Phases {
+  std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
+  bool on = std::getenv("PTGPU_HOST_STATS") != nullptr;
+  void mark(const char* what)
+  {
+    const auto now = std::chrono::steady_clock::now();
+    if (on) std::fprintf(stderr, "[ptw_batched] %-34s %8.3f s\n", what, std::chrono::duration<double>(now - last).count());
+    last = now;
+  }
+};
+
 int Run(int argc, const char* argv[])
 {
+  Phases phases;
   pt::Options options = pt::ParseArguments(argc, argv);
 
   std::shared_ptr<const pt::move_tester::BatchedNeighborhood> batched;
@@ -76,14 +92,18 @@ int Run(int argc, const char* argv[])
   pt::CompressedTree::BuildDictionary(labels);
   const pt::pll::Model model = pt::pll::ParseRaxmlInfo(options.raxml_path, options.rate_categories);
 
+  phases.mark("arguments, trees, alignment");
   pt::Guru guru(options, input.trees, model, labels, sequences);
+  phases.mark("guru (first partition, CUDA context)");
   guru.Start();
   guru.Wait(options.poll_ms);
+  phases.mark("the walk");
   if (!options.skip_filtering) guru.FilterGoodTreeTable();
 
   DumpTable(guru.GetGoodTreeTable(), options.good_trees_path);
   DumpTable(guru.GetVisitedTreeTable(), options.visited_trees_path);
   DumpTable(guru.GetTestedTreeTable(), options.tested_trees_path);
+  phases.mark("tables written");
 
   if (pt::move_tester::VisitPrefetcher::Instance().enabled()) {
     const auto visits = pt::pll::Partition::VisitStatistics();
@@ -95,6 +115,7 @@ int Run(int argc, const char* argv[])
                  pf.chained(), pf.walked_ahead());
   }
   pt::move_tester::VisitPrefetcher::Instance().Shutdown();   // before the partitions and the CUDA runtime go
+  phases.mark("workers and their engines released");
   if (batched) {
     const auto stats = batched->Statistics();
     std::fprintf(stderr, "batched move testing: %llu moves answered from %llu engine batches\n",

@@ -322,17 +322,31 @@ Partition::Partition(pll_utree_t* tree,
       tip_sequences = &unique_columns;
     }
   }
+  // (PTGPU_HOST_STATS: where a process's start-up goes)
+  static const bool show = std::getenv("PTGPU_HOST_STATS") != nullptr;
+  auto t_last = std::chrono::steady_clock::now();
+  auto mark = [&](const char* what) {
+    const auto now = std::chrono::steady_clock::now();
+    if (show)
+      std::fprintf(stderr, "[ptgpu host] Partition(): %-24s %8.3f s\n", what,
+                   std::chrono::duration<double>(now - t_last).count());
+    t_last = now;
+  };
   device_ = pick_device();
+  mark("device (CUDA start-up)");
   unsigned int wanted_shards = 1;
   if (const char* env = std::getenv("PTGPU_SITE_SHARDS")) wanted_shards = std::max(1, std::atoi(env));
   CreateEngines(inner_node_count() + extra, inner_node_count() + extra,
                 static_cast<unsigned int>(model.category_rates.size()), wanted_shards);
+  mark("engine");
   // the whole-tree step program on a shard is ONE persistent kernel per GPU; the call-by-call
   // form would pay a launch and an exchange per Newton step
   if (shards_.size() > 1 && !std::getenv("PTGPU_STEPWISE_ALL_BRANCHES")) stepwise_all_branches_ = false;
   try {
     SetModel(model);
+    mark("model");
     SetTipStates(tree, labels, *tip_sequences);
+    mark("tips");
     if (!weights.empty())
       OnShards([&](ptgpu_engine* e, unsigned int s) {
         return ptgpu_set_pattern_weights(e, weights.data() + shard_begin_[s]);

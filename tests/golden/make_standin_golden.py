@@ -77,7 +77,13 @@ def run(binary, name, extra, threads=1, env=None):
 if __name__ == "__main__":
     ref = os.path.join(ROOT, "oracle", "_ref", "ptw_threads")
     only = sys.argv[1:]
-    path = os.path.join(HERE, "standin_golden.json")
+    # STANDIN_GOLDEN_OUT: another file to write (several sets can be generated side by side and
+    # merged afterwards); STANDIN_OFFSET: another --lnl-offset for the sets named on the command line
+    path = os.environ.get("STANDIN_GOLDEN_OUT", os.path.join(HERE, "standin_golden.json"))
+    if only and os.environ.get("STANDIN_OFFSET"):
+        for name in only:
+            taxa, sites, extra = SETS[name]
+            SETS[name] = (taxa, sites, ["--lnl-offset", os.environ["STANDIN_OFFSET"]] + extra[2:])
     g = json.load(open(path)) if os.path.exists(path) else {}
     for name, (taxa, sites, extra) in SETS.items():
         if only and name not in only:
