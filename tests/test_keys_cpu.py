@@ -60,3 +60,114 @@ def test_key_construction_is_faster_than_the_reference_s(tmp_path):
           f"({t['ours_twice']:.2f} when each tree is asked for twice running)")
     assert t["ours"] < t["ref"]
     assert t["ours_twice"] < t["ours"]
+
+
+# ---- the 16-bit label index (pt_b200/host/ptw/wide_label_dictionary.hpp) ----------------------
+WIDE = os.path.join(ROOT, "oracle", "_ref", "keys_wide")
+
+
+def splits_of(newick):
+    """the non-trivial bipartitions of a Newick tree, each as the frozenset of tip labels on the
+    side that does not hold the alphabetically smallest label"""
+    from pt_b200.pytree import Tree
+    t = Tree(newick)
+    labels = sorted(t.labels())
+    anchor = labels[0]
+    out = set()
+
+    def below(n):   # tip labels behind record n (iterative post-order: 1000-taxon trees are deep)
+        stack, seen = [(n, False)], {}
+        while stack:
+            r, done = stack.pop()
+            if r.is_tip:
+                seen[id(r)] = frozenset([r.label])
+            elif done:
+                seen[id(r)] = seen[id(r.next.back)] | seen[id(r.next.next.back)]
+                side = seen[id(r)]
+                side = side if anchor not in side else frozenset(labels) - side
+                if 1 < len(side) < len(labels) - 1:
+                    out.add(side)
+            else:
+                stack += [(r, True), (r.next.back, False), (r.next.next.back, False)]
+        return seen[id(n)]
+
+    r = t.root
+    for x in (r, r.next, r.next.next):
+        below(x.back)
+    return out
+
+
+def rotated_newick(tree, rng):
+    """the same unrooted tree written from another inner node, children in random order"""
+    inner = [n for n in tree.nodes[tree.tip_count:]]
+    root = inner[int(rng.integers(len(inner)))]
+
+    def rec(n):
+        stack, text = [(n, 0)], {}
+        while stack:
+            r, state = stack.pop()
+            if r.is_tip:
+                text[id(r)] = f"{r.label}:{r.length!r}"
+            elif state == 0:
+                stack += [(r, 1), (r.next.back, 0), (r.next.next.back, 0)]
+            else:
+                kids = [text[id(r.next.back)], text[id(r.next.next.back)]]
+                if rng.integers(2):
+                    kids.reverse()
+                text[id(r)] = "(" + ",".join(kids) + f"):{r.length!r}"
+        return text[id(n)]
+
+    parts = [rec(x.back) for x in (root, root.next, root.next.next)]
+    rng.shuffle(parts)
+    return "(" + ",".join(parts) + ");"
+
+
+def key_blocks(stdout, count):
+    """keys_dump prints 4 lines per key (bits, label indices, hash, decoded Newick), every tree
+    twice in a row and then all once more: the first key of each tree"""
+    lines = stdout.splitlines()
+    assert len(lines) == 4 * 3 * count
+    return [tuple(lines[8 * i: 8 * i + 4]) for i in range(count)]
+
+
+@pytest.mark.parametrize("taxa,count", [(27, 60), (200, 40), (256, 20)])
+def test_wide_label_index_changes_nothing_up_to_256_taxa(tmp_path, taxa, count):
+    """built with the 16-bit dictionary, the keys of trees the reference can handle are the
+    reference's: bits, indices, hash and decoded Newick"""
+    need_binaries()
+    if not os.path.exists(WIDE):
+        pytest.skip("oracle/_ref/keys_wide not built")
+    path = trees_file(tmp_path, taxa, count, 4000 + taxa)
+    a = subprocess.run([REF, path], capture_output=True, text=True, check=True).stdout
+    b = subprocess.run([WIDE, path], capture_output=True, text=True, check=True).stdout
+    assert a == b
+
+
+@pytest.mark.parametrize("taxa", [257, 300, 1000])
+def test_wide_label_index_beyond_256_taxa(tmp_path, taxa):
+    """more taxa than pt's uint8_t index allows (the reference throws std::length_error: no
+    reference output exists): the key is a function of the unrooted topology alone -- equal for
+    the same tree written from another node with its children in another order, different for
+    NNI neighbours -- and decodes to that topology"""
+    from pt_b200.pytree import Tree
+    if not os.path.exists(WIDE):
+        pytest.skip("oracle/_ref/keys_wide not built")
+    count = 24
+    path = trees_file(tmp_path, taxa, count, 9000 + taxa)
+    rng = np.random.default_rng(taxa)
+    originals = open(path).read().splitlines()
+    # the first tree stays first (its tip order defines the dictionary); rotations appended
+    rotated = [rotated_newick(Tree(nw), rng) for nw in originals]
+    both = tmp_path / "both.nwk"
+    both.write_text("\n".join(originals + rotated) + "\n")
+    r = subprocess.run([WIDE, str(both)], capture_output=True, text=True, check=True)
+    keys = key_blocks(r.stdout, 2 * count)
+    for i in range(count):
+        assert keys[i] == keys[count + i], f"tree {i}: another rotation, another key"
+        assert splits_of(keys[i][3]) == splits_of(originals[i]), f"tree {i}: decoded topology differs"
+    distinct = {frozenset(splits_of(nw)) for nw in originals}
+    assert len({k[:2] for k in keys[:count]}) == len(distinct)
+    assert max(int(x) for x in keys[0][1].strip("[]").split(",")) == taxa - 1   # indices beyond 255 in use
+    if os.path.exists(REF):
+        ref = subprocess.run([REF, path], capture_output=True, text=True)
+        assert ref.returncode != 0   # "index type is not large enough"
