@@ -167,7 +167,8 @@ class Partition
   uint64_t VisitKey(pll_unode_t* root) const;
   // the present content's id (ExactContentId of the tree and root it is exact for); 0 = not known
   uint64_t ContentId() const { return content_id_; }
-  static void PublishVisit(uint64_t key, std::shared_future<VisitResult> result);
+  // (`bytes`: about how much the result will hold, for the registry's memory budget)
+  static void PublishVisit(uint64_t key, std::shared_future<VisitResult> result, size_t bytes = 0);
   static bool VisitKnown(uint64_t key);
   static void ClearVisits();
   // (visits served from the registry, visits computed here) since process start

@@ -199,7 +199,7 @@ bool VisitPrefetcher::Enqueue(int device, const pll::Model& model, pll_utree_t* 
       slot = std::make_shared<Batch>();
       slot->id = ++batch_;
       batch_order_.push_back(id);
-      while (batch_order_.size() > 64) {
+      while (batch_order_.size() > 4096) {
         batches_.erase(batch_order_.front());
         batch_order_.pop_front();
       }
@@ -226,7 +226,8 @@ bool VisitPrefetcher::Enqueue(int device, const pll::Model& model, pll_utree_t* 
     group->moves.emplace_back(node->node_index, type);
   }
   if (pll::Partition::VisitKnown(key)) return false;   // (a worker walking ahead got there first)
-  pll::Partition::PublishVisit(key, task->result.get_future().share());
+  pll::Partition::PublishVisit(key, task->result.get_future().share(),
+                               sizeof(double) * (task->tree->tip_count + 3 * task->tree->inner_count));
   {
     std::lock_guard<std::mutex> lock(mutex_);
     task->batch = group ? group->id : ++batch_;
@@ -471,7 +472,8 @@ std::unique_ptr<VisitPrefetcher::Task> VisitPrefetcher::BuildSibling(const Job& 
   task->type = job.move.second;
   task->depth = 0;
   task->batch = job.group->id;
-  pll::Partition::PublishVisit(key, task->result.get_future().share());
+  pll::Partition::PublishVisit(key, task->result.get_future().share(),
+                               sizeof(double) * (task->tree->tip_count + 3 * task->tree->inner_count));
   ++chained_;
   static const bool debug = std::getenv("PTGPU_PREFETCH_DEBUG") != nullptr;
   if (debug)
@@ -547,7 +549,7 @@ void VisitPrefetcher::Work()
           const uint64_t fp = pll::Partition::TreeFingerprint(task->tree);
           std::lock_guard<std::mutex> lock(mutex_);
           if (hoods_.emplace(fp, hood.get_future().share()).second) hood_order_.push_back(fp);
-          while (hood_order_.size() > 4096) {
+          while (hood_order_.size() > 65536) {
             hoods_.erase(hood_order_.front());
             hood_order_.pop_front();
           }

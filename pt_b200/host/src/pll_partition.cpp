@@ -18,6 +18,7 @@
 #include <cstring>
 #include <deque>
 #include <exception>
+#include <functional>
 #include <future>
 #include <map>
 #include <mutex>
@@ -363,6 +364,8 @@ namespace {
 
 std::mutex g_visit_mutex;
 std::unordered_map<uint64_t, std::shared_future<Partition::VisitResult>> g_visits;
+std::deque<std::pair<uint64_t, size_t>> g_visit_order;   // publication order with each entry's bytes
+size_t g_visit_bytes = 0;                                 // sum over g_visit_order (taken entries leave it late)
 std::atomic<bool> g_visits_used{false};
 std::atomic<unsigned long long> g_visits_served{0}, g_visits_computed{0};
 
@@ -457,14 +460,27 @@ uint64_t Partition::VisitKey(pll_unode_t* root) const
   return VisitKeyFor(content_id_, root, node_count());
 }
 
-void Partition::PublishVisit(uint64_t key, std::shared_future<VisitResult> result)
+void Partition::PublishVisit(uint64_t key, std::shared_future<VisitResult> result, size_t bytes)
 {
   std::lock_guard<std::mutex> lock(g_visit_mutex);
-  // results nobody came for (a predicted start state that did not occur) are dropped oldest first
-  static std::deque<uint64_t> order;
-  if (g_visits.emplace(key, std::move(result)).second) order.push_back(key);
-  while (order.size() > 4096) {
-    g_visits.erase(order.front());
+  // Results nobody came for (a predicted start state that did not occur) are dropped oldest first
+  // once the registry holds more than its budget: a depth-first walk returns to the later moves of
+  // an early queue only after everything below it, so the budget is large (256 MB of lengths;
+  // PTGPU_VISIT_REGISTRY_MB) -- results dropped too early are simply computed in place again.
+  std::deque<std::pair<uint64_t, size_t>>& order = g_visit_order;
+  size_t& held = g_visit_bytes;
+  static const size_t budget = [] {
+    const char* env = std::getenv("PTGPU_VISIT_REGISTRY_MB");
+    return (env ? std::strtoull(env, nullptr, 10) : 256ull) << 20;
+  }();
+  bytes += 256;   // the entry itself
+  if (g_visits.emplace(key, std::move(result)).second) {
+    order.emplace_back(key, bytes);
+    held += bytes;
+  }
+  while (order.size() > 1 && (held > budget || order.size() > (1u << 20))) {
+    g_visits.erase(order.front().first);
+    held -= order.front().second;
     order.pop_front();
   }
   g_visits_used = true;
@@ -480,6 +496,8 @@ void Partition::ClearVisits()
 {
   std::lock_guard<std::mutex> lock(g_visit_mutex);
   g_visits.clear();
+  g_visit_order.clear();
+  g_visit_bytes = 0;
 }
 
 std::pair<unsigned long long, unsigned long long> Partition::VisitStatistics()
@@ -1614,6 +1632,60 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhoodLocal(pll_utree_
                                       s == 0 ? lnl.data() : v2.data(), s == 0 ? status.data() : s2.data(),
                                       nullptr);
   });
+  // PTGPU_DUMP_LOCAL_TESTS=<file>: every candidate whose optimisation ended with a failure status (and
+  // every 997th other one; PTGPU_DUMP_LOCAL_EVERY=n: every nth) as "<status> <score> <newick of the moved tree, written from the move's node,
+  // lengths with 17 digits>" -- to replay single cases on the reference (tests/golden tooling)
+  if (const char* path = std::getenv("PTGPU_DUMP_LOCAL_TESTS")) {
+    static std::mutex dump_mutex;
+    static unsigned long long seen = 0;
+    std::lock_guard<std::mutex> lock(dump_mutex);
+    FILE* f = nullptr;
+    for (unsigned int i = 0; i < count; ++i) {
+      static const unsigned long long every = [] {
+        const char* env = std::getenv("PTGPU_DUMP_LOCAL_EVERY");
+        return env ? std::max(1ull, std::strtoull(env, nullptr, 10)) : 997ull;
+      }();
+      if (status[i] == 0 && (++seen % every) != 0) continue;
+      if (!f) f = std::fopen(path, "a");
+      if (!f) break;
+      pll_utree_t* moved = pll_utree_clone(tree);
+      if (!moved) continue;
+      pll_unode_t* at = nullptr;
+      for (unsigned int k = 0; k < moved->tip_count + moved->inner_count && !at; ++k) {
+        pll_unode_t* first = moved->nodes[k];
+        pll_unode_t* r = first;
+        do {
+          if (r->node_index == out[i].node->node_index) { at = r; break; }
+          r = r->next;
+        } while (r && r != first);
+      }
+      if (at) {
+        pll_utree_nni(at, out[i].type, nullptr);
+        std::string text;
+        std::function<void(const pll_unode_t*)> sub = [&](const pll_unode_t* r) {
+          char len[40];
+          std::snprintf(len, sizeof len, ":%.17g", r->length);
+          if (!r->next) { text += r->label; text += len; return; }
+          text += "(";
+          sub(r->next->back);
+          text += ",";
+          sub(r->next->next->back);
+          text += ")";
+          text += len;
+        };
+        text += "(";
+        sub(at->back);
+        text += ",";
+        sub(at->next->back);
+        text += ",";
+        sub(at->next->next->back);
+        text += ");";
+        std::fprintf(f, "%d %.17g %s\n", status[i], lnl[i], text.c_str());
+      }
+      pll_utree_destroy(moved, nullptr);
+    }
+    if (f) std::fclose(f);
+  }
   double prior = 0.0;
   if (map_mode_) prior = MapLogPrior(GetVirtualRoot(tree));
   for (unsigned int i = 0; i < count; ++i) {

@@ -37,8 +37,21 @@ def digest(lines):
     return hashlib.sha256("\n".join(lines).encode()).hexdigest()
 
 
+def score_buckets(lines, n=256):
+    """per-bucket sums of the printed scores, trees dealt to n buckets by a hash of their Newick string:
+    a table of several 10^5 scores printed with 6 significant digits is expected to hold a few that sit
+    on a rounding edge (a 1e-12 relative difference in lnL then flips the last printed digit); such a
+    flip moves ONE bucket by ONE unit of the last digit, anything systematic moves them all"""
+    sums = [0.0] * n
+    for l in lines:
+        score, newick = l.split("\t", 1)
+        sums[int.from_bytes(hashlib.sha1(newick.encode()).digest()[:4], "little") % n] += float(score)
+    return [round(x, 6) for x in sums]
+
+
 def summarise(tables):
     return dict(good=tables["good"], counts={k: len(v) for k, v in tables.items()},
+                visited_buckets=score_buckets(tables["visited"]), tested_buckets=score_buckets(tables["tested"]),
                 visited_sha=digest(tables["visited"]), tested_sha=digest(tables["tested"]),
                 # topologies only (lnl column dropped): what "identical good_trees" pins even
                 # if a printed 6-significant-digit lnl sat on a rounding edge

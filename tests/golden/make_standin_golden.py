@@ -26,7 +26,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, HERE)
 
-from make_ptw_golden import summarise  # noqa: E402
+from make_ptw_golden import digest, score_buckets, summarise  # noqa: E402
 from pt_b200.pytree import Tree, random_tree_newick  # noqa: E402
 from pt_b200 import synth  # noqa: E402
 
@@ -39,7 +39,7 @@ SETS = {
     "DS4": (41, 1137, CONFIG2),
     "DS5": (50, 378, ["--lnl-offset", "-0.25", "--optimization-radius", "1"]),
     "DS6": (50, 1133, ["--lnl-offset", "-2", "--optimization-radius", "0"]),
-    "DS7": (59, 1824, CONFIG2),
+    "DS7": (59, 1824, ["--lnl-offset", "-2", "--optimization-radius", "1"]),   # offset -5: > 3 h on one core, given up
     "DS8": (64, 1008, ["--lnl-offset", "-1.5", "--optimization-radius", "0"]),
 }
 
@@ -91,6 +91,11 @@ if __name__ == "__main__":
         make_inputs(name, taxa, sites)
         t0 = time.time()
         g[name] = dict(taxa=taxa, sites=sites, args=extra, **summarise(run(ref, name, extra)))
+        g[name]["score_scale"] = max(abs(float(l.split("\t")[0])) for l in g[name]["good"])
+        if len(g[name]["good"]) > 1000:   # keep the fixture small: digest + per-bucket score sums
+            g[name]["good_sha"] = digest(g[name]["good"])
+            g[name]["good_buckets"] = score_buckets(g[name]["good"])
+            del g[name]["good"]
         print(name, taxa, sites, extra, g[name]["counts"], "%.1f s" % (time.time() - t0), flush=True)
         with open(path, "w") as f:
             json.dump(g, f, indent=0)
