@@ -167,6 +167,23 @@ class Partition
   uint64_t VisitKey(pll_unode_t* root) const;
   // the present content's id (ExactContentId of the tree and root it is exact for); 0 = not known
   uint64_t ContentId() const { return content_id_; }
+
+  // The state the reference's move testers leave behind.  BranchNeighborhoodOptimizer ends every test
+  // with TraversalUpdate(tested node, FULL) on the wanderer's tree
+  // (src/move_tester/branch_neighborhood_optimizer.cpp:71-73); SingleBranchOptimizer leaves the tree
+  // oriented at the tested node with the two ends of its edge invalid (single_branch_optimizer.cpp:33-60).
+  // After QueueMoves the tree is therefore oriented at the LAST node tested, and the visit that follows
+  // (src/wanderer.cpp:150-190) starts from those validity flags -- which decide which stale CLVs its
+  // first branches reuse.  A tester that scores the neighbourhood in one call and leaves the partition
+  // alone registers that state here after every test; it is produced -- one FULL traversal at `tested`
+  // on `tree`, the edge invalidated if asked, the invalidations this thread has made since replayed
+  // (pll_util.hpp InvalidationLog), the flags copied onto the clone being visited -- when the next
+  // OptimizeAllBranches starts, and forgotten if a FULL traversal comes first (MoveBack,
+  // src/wanderer.cpp:232-239).  `tree` must still be alive then: it is, the wanderer visits clones of it.
+  void DeferTesterOrientation(pll_utree_t* tree, pll_unode_t* tested, bool invalidate_edge);
+  // called (on the visiting thread) right after a deferred orientation has been produced, before the
+  // visit looks for a registered result: (partition, tree, node it is now oriented at, edge invalidated)
+  static void SetOrientationHook(std::function<void(Partition&, pll_utree_t*, pll_unode_t*, bool)> hook);
   // (`bytes`: about how much the result will hold, for the registry's memory budget)
   static void PublishVisit(uint64_t key, std::shared_future<VisitResult> result, size_t bytes = 0);
   static bool VisitKnown(uint64_t key);
@@ -183,6 +200,10 @@ class Partition
   bool is_replica_ = false;
   // what the per-node CLVs and the P matrices hold, when that is known exactly
   // (ExactContentId); 0 = unknown
+  void ProduceTesterOrientation(pll_unode_t* visit_root);
+  pll_utree_t* pending_tree_ = nullptr;      // DeferTesterOrientation
+  pll_unode_t* pending_node_ = nullptr;
+  bool pending_invalidate_ = false;
   uint64_t content_id_ = 0;
   uint64_t content_fp_ = 0;   // TreeFingerprint of the tree content_id_ was formed from
 

@@ -59,6 +59,8 @@ pll_unode_t* GetVirtualRoot(pll_utree_t* tree);
 
 // an NNI across node's edge changes what both of its end nodes summarise (:353-366)
 void InvalidateEdgeClvs(pll_unode_t* node);
+// the nodes this thread has passed to InvalidateEdgeClvs lately, oldest first (at most 64 are kept)
+std::vector<pll_unode_t*>& InvalidationLog();
 
 // copies node / clv / scaler / pmatrix indices of equally labelled tips from src to dest so
 // that one engine (one set of tip buffers) serves both trees (:368-411)

@@ -18,6 +18,11 @@ BatchedNeighborhood::BatchedNeighborhood(const Options& options)
   if (radius_ < 0) throw std::invalid_argument("optimization radius must not be negative");
   if (options.marginal_mode)
     throw std::invalid_argument("marginal mode is not available with batched move testing");
+  // once the partition has produced the state the reference's tester would have left (below), the
+  // visits of the moves that passed their test are queued from exactly that state
+  pll::Partition::SetOrientationHook([](pll::Partition& partition, pll_utree_t* tree, pll_unode_t* at, bool edge_invalid) {
+    VisitPrefetcher::Instance().Flush(partition, tree, at, edge_invalid);
+  });
 }
 
 BatchedNeighborhood::~BatchedNeighborhood()
@@ -92,6 +97,11 @@ std::pair<bool, double> BatchedNeighborhood::EvaluateMove(pll::Partition& partit
       // the wanderer will visit this move if the authority grants it (src/wanderer.cpp:262-272):
       // start that visit now, on another engine (the wanderer's tree is not touched; never throws)
       if (accept) VisitPrefetcher::Instance().Submit(partition, tree, node, static_cast<int>(type), authority);
+      // The reference's testers leave the wanderer's tree oriented at the node of the move they have
+      // just tested (BranchNeighborhoodOptimizer: FULL traversal there; SingleBranchOptimizer: oriented
+      // there, the edge's two ends invalid): the next visit starts from that.  Nothing is touched here;
+      // the partition produces the state when -- if -- a visit follows (Partition::DeferTesterOrientation).
+      partition.DeferTesterOrientation(tree, node, radius_ == 0);
       return std::make_pair(accept, m.lnl);
     }
   }

@@ -40,6 +40,7 @@ bool SameModel(const pll::Model& a, const pll::Model& b)
 VisitPrefetcher::Batch::~Batch()
 {
   if (parent) pll_utree_destroy(parent, pll::cb_erase_data);
+  if (parent_first) pll_utree_destroy(parent_first, pll::cb_erase_data);
 }
 
 VisitPrefetcher::TreeHolder::~TreeHolder()
@@ -97,6 +98,7 @@ void VisitPrefetcher::Shutdown()
   speculated_.clear();
   batches_.clear();
   batch_order_.clear();
+  noted_.clear();
   pll::Partition::ClearVisits();
 }
 
@@ -145,55 +147,48 @@ void VisitPrefetcher::SubmitOrThrow(pll::Partition& owner, pll_utree_t* tree, pl
     ++declined_;
     return;
   }
-  Enqueue(device, owner.GetModel(), tree, node, type, 0);
+  std::lock_guard<std::mutex> lock(mutex_);
+  Noted& noted = noted_[&owner];
+  if (noted.tree != tree) {   // moves of an earlier tree whose queue was never visited (nothing was granted)
+    noted.tree = tree;
+    noted.moves.clear();
+  }
+  noted.moves.emplace_back(node->node_index, type);
+}
+
+void VisitPrefetcher::Flush(pll::Partition& owner, pll_utree_t* tree, pll_unode_t* at, bool edge_invalid) noexcept
+{
+  if (!enabled()) return;
+  std::vector<std::pair<unsigned int, int>> moves;
+  {
+    std::lock_guard<std::mutex> lock(mutex_);
+    auto it = noted_.find(&owner);
+    if (it == noted_.end() || it->second.tree != tree) return;
+    moves.swap(it->second.moves);
+    it->second.tree = nullptr;
+  }
+  try {
+    for (const std::pair<unsigned int, int>& m : moves)
+      Enqueue(owner.device(), owner.GetModel(), tree, RecordByIndex(tree, m.first), m.second, 0, at, edge_invalid);
+  } catch (const std::exception& e) {
+    disabled_ = true;
+    std::fprintf(stderr, "visit prefetcher: turned off (%s)\n", e.what());
+  } catch (...) {
+    disabled_ = true;
+  }
 }
 
 bool VisitPrefetcher::Enqueue(int device, const pll::Model& model, pll_utree_t* tree, pll_unode_t* node, int type,
-                              int depth)
+                              int depth, const pll_unode_t* at, bool edge_invalid)
 {
   const unsigned int n_nodes = tree->tip_count + tree->inner_count;
-  // The start state of the visit as Wanderer::MoveForward will produce it (src/wanderer.cpp:160-166)
-  // when the partition holds the exact CLVs of `tree` oriented at its virtual root: the tree's
-  // flags are then those a FULL traversal leaves, plus the two invalid ends of the NNI edge.
-  // The clone is made the way the wanderer makes it -- NNI on (a copy of) its tree, THEN the clone
-  // that is visited -- because pll_utree_clone rebuilds the node array from the topology it
-  // finds: the candidates of the visited tree's neighbourhood are enumerated in that order.
-  std::unique_ptr<Task> task(new Task);
-  {
-    struct Holder {
-      pll_utree_t* t;
-      ~Holder() { if (t) pll_utree_destroy(t, pll::cb_erase_data); }
-    } parent{pll_utree_clone(tree)};
-    if (!parent.t) throw std::runtime_error("pll_utree_clone failed");
-    pll_utree_every(parent.t, pll::cb_copy_clv_traversal);
-    std::vector<pll_unode_t*> buffer(n_nodes, nullptr);
-    unsigned int count = 0;
-    if (!pll_utree_traverse(GetVirtualRoot(parent.t), PLL_TREE_TRAVERSE_POSTORDER, pll::cb_full_traversal,
-                            buffer.data(), &count))
-      throw std::runtime_error("the tree's virtual root is not an inner node");
-    pll_unode_t* moved = RecordByIndex(parent.t, node->node_index);
-    pll_utree_nni(moved, type, nullptr);
-    pll::InvalidateEdgeClvs(moved);
-    task->tree = pll_utree_clone(parent.t);
-    if (!task->tree) throw std::runtime_error("pll_utree_clone failed");
-    pll_utree_every(task->tree, pll::cb_copy_clv_traversal);
-  }
-  task->parent_root_index = GetVirtualRoot(tree)->node_index;
-  const uint64_t content = pll::Partition::ExactContentId(pll::Partition::TreeFingerprint(tree),
-                                                          GetVirtualRoot(tree)->node_index);
-  const uint64_t key = pll::Partition::VisitKeyFor(content, GetVirtualRoot(task->tree), n_nodes);
-  if (!key) return false;
-  task->device = device;
-  task->model = model;
-  task->depth = depth;
-  task->node_index = node->node_index;
-  task->type = type;
-  // the group this move belongs to: the moves one QueueMoves call sends here, in order (depth 0 only)
+  // Which state the visit starts from: the FIRST move of a queue is visited with the tree as the move
+  // tester left it (oriented at the last node tested: `at`), every later one either after MoveBack's
+  // FULL traversal at the virtual root (this task) or after a failed sibling (BuildSibling).
   std::shared_ptr<Batch> group;
+  const std::pair<const pll_utree_t*, uint64_t> id(tree, pll::Partition::TreeFingerprint(tree));
   if (depth == 0) {
-    const Authority* authority = authority_.load(std::memory_order_relaxed);
     std::lock_guard<std::mutex> lock(mutex_);
-    const std::pair<const pll_utree_t*, uint64_t> id(tree, content);
     std::shared_ptr<Batch>& slot = batches_[id];
     if (!slot) {
       slot = std::make_shared<Batch>();
@@ -205,18 +200,65 @@ bool VisitPrefetcher::Enqueue(int device, const pll::Model& model, pll_utree_t* 
       }
     }
     group = batches_[id];
+  }
+  const bool first = group && group->moves.empty() && at != nullptr;
+  const unsigned int orient_index = first ? at->node_index : GetVirtualRoot(tree)->node_index;
+  const bool orient_invalid = first && edge_invalid;
+  // a clone of `tree` with the flags of that state
+  auto oriented_clone = [&](unsigned int index, bool invalid) -> pll_utree_t* {
+    pll_utree_t* c = pll_utree_clone(tree);
+    if (!c) throw std::runtime_error("pll_utree_clone failed");
+    pll_utree_every(c, pll::cb_copy_clv_traversal);
+    std::vector<pll_unode_t*> buffer(n_nodes, nullptr);
+    unsigned int count = 0;
+    pll_unode_t* r = RecordByIndex(c, index);
+    if (!pll_utree_traverse(r, PLL_TREE_TRAVERSE_POSTORDER, pll::cb_full_traversal, buffer.data(), &count)) {
+      pll_utree_destroy(c, pll::cb_erase_data);
+      throw std::runtime_error("the tree's orientation node is not an inner node");
+    }
+    if (invalid) pll::InvalidateEdgeClvs(r);
+    return c;
+  };
+  // The start state of the visit as Wanderer::MoveForward will produce it (src/wanderer.cpp:160-166)
+  // when the partition holds the exact CLVs of `tree` oriented at its virtual root: the tree's
+  // flags are then those a FULL traversal leaves, plus the two invalid ends of the NNI edge.
+  // The clone is made the way the wanderer makes it -- NNI on (a copy of) its tree, THEN the clone
+  // that is visited -- because pll_utree_clone rebuilds the node array from the topology it
+  // finds: the candidates of the visited tree's neighbourhood are enumerated in that order.
+  std::unique_ptr<Task> task(new Task);
+  {
+    struct Holder {
+      pll_utree_t* t;
+      ~Holder() { if (t) pll_utree_destroy(t, pll::cb_erase_data); }
+    } parent{oriented_clone(orient_index, orient_invalid)};
+    pll_unode_t* moved = RecordByIndex(parent.t, node->node_index);
+    pll_utree_nni(moved, type, nullptr);
+    pll::InvalidateEdgeClvs(moved);
+    task->tree = pll_utree_clone(parent.t);
+    if (!task->tree) throw std::runtime_error("pll_utree_clone failed");
+    pll_utree_every(task->tree, pll::cb_copy_clv_traversal);
+  }
+  task->parent_root_index = orient_index;
+  task->parent_edge_invalid = orient_invalid;
+  const uint64_t content = pll::Partition::ExactContentId(id.second, orient_index);
+  const uint64_t key = pll::Partition::VisitKeyFor(content, GetVirtualRoot(task->tree), n_nodes);
+  if (!key) return false;
+  task->device = device;
+  task->model = model;
+  task->depth = depth;
+  task->node_index = node->node_index;
+  task->type = type;
+  // the group this move belongs to: the moves one QueueMoves call sends here, in order (depth 0 only)
+  if (group) {
+    const Authority* authority = authority_.load(std::memory_order_relaxed);
+    std::lock_guard<std::mutex> lock(mutex_);
     if (!group->parent) {
       group->device = device;
       group->model = model;
       group->parent_root_index = GetVirtualRoot(tree)->node_index;
-      // the parent tree with the flags a FULL traversal at its root leaves
-      group->parent = pll_utree_clone(tree);
-      if (!group->parent) throw std::runtime_error("pll_utree_clone failed");
-      pll_utree_every(group->parent, pll::cb_copy_clv_traversal);
-      std::vector<pll_unode_t*> buffer(n_nodes, nullptr);
-      unsigned int count = 0;
-      pll_utree_traverse(GetVirtualRoot(group->parent), PLL_TREE_TRAVERSE_POSTORDER, pll::cb_full_traversal,
-                         buffer.data(), &count);
+      // the parent tree with the flags a FULL traversal at its root leaves, and with the tester's
+      group->parent = oriented_clone(group->parent_root_index, false);
+      if (first) group->parent_first = oriented_clone(orient_index, orient_invalid);
     }
     // two moves of a queue can lead to the same topology (the root entry repeats its first child's
     // edge): the authority grants only the first (src/authority.cpp:139-152), so only that one counts
@@ -331,7 +373,9 @@ double VisitPrefetcher::RunVisit(Task& task, pll::Partition& rep, bool state_on_
     // back to the parent tree: its exact CLVs, oriented at its root, are what the wanderer's
     // partition holds when it starts this visit
     pll_utree_nni(moved, task.type, nullptr);
-    rep.TraversalUpdate(RecordByIndex(task.tree, task.parent_root_index), pll::TraversalType::FULL);
+    pll_unode_t* oriented_at = RecordByIndex(task.tree, task.parent_root_index);
+    rep.TraversalUpdate(oriented_at, pll::TraversalType::FULL);
+    if (task.parent_edge_invalid) pll::InvalidateEdgeClvs(oriented_at);   // (the radius-0 tester's last state)
     // the move, as MoveForward applies it
     pll_utree_nni(moved, task.type, nullptr);
     pll::InvalidateEdgeClvs(moved);
@@ -445,7 +489,10 @@ std::unique_ptr<VisitPrefetcher::Task> VisitPrefetcher::BuildSibling(const Job& 
     struct Holder {
       pll_utree_t* t;
       ~Holder() { if (t) pll_utree_destroy(t, pll::cb_erase_data); }
-    } parent{pll_utree_clone(job.group->parent)};
+    // (a run of failures that starts with the queue's first visit still sees the tester's orientation;
+    //  any later run starts after a good tree, i.e. after MoveBack's FULL traversal at the root)
+    } parent{pll_utree_clone(job.run_start == 0 && job.group->parent_first ? job.group->parent_first
+                                                                           : job.group->parent)};
     if (!parent.t) return nullptr;
     pll_utree_every(parent.t, pll::cb_copy_clv_traversal);
     // every failed sibling was applied, had its edge ends invalidated and was undone (src/wanderer.cpp:160-176)

@@ -102,8 +102,15 @@ class VisitPrefetcher
   // wanderer's partition, whose content is exact for `tree` (it has just been visited).
   // Nothing the wanderer owns is modified; returns at once.  Never throws: a failure turns
   // prefetching off for the rest of the run and the visit is computed in place.
+  // The move is only NOTED: the start state of the queue's first visit depends on the node the
+  // move tester tests LAST (the tree is left oriented at it: Partition::DeferTesterOrientation), so
+  // the visits are queued by Flush, which the partition calls when that state has been produced.
   void Submit(pll::Partition& owner, pll_utree_t* tree, pll_unode_t* node, int type,
               const Authority& authority) noexcept;
+  // `tree` is now oriented at `at` (its edge ends invalid if `edge_invalid`), the partition exact for
+  // it: queue the noted moves of `tree` -- the first from this state, the others from the exact
+  // tree at its virtual root (where MoveBack leaves it); sibling chains follow as visits finish
+  void Flush(pll::Partition& owner, pll_utree_t* tree, pll_unode_t* at, bool edge_invalid) noexcept;
 
   // the scores of `tree`'s NNI neighbourhood if a worker has computed (or is computing) them:
   // node pointers are those of `tree`.  false = not registered (or the computation failed).
@@ -142,7 +149,9 @@ class VisitPrefetcher
   // are moves of (a private clone carrying the flags a FULL traversal at its root leaves)
   struct Batch {
     unsigned long long id = 0;
-    pll_utree_t* parent = nullptr;
+    pll_utree_t* parent = nullptr;         // flags: FULL traversal at the virtual root
+    pll_utree_t* parent_first = nullptr;   // flags: as the move tester left them (what the queue's first visit,
+                                           // and a run of failures that starts with it, sees)
     int device = 0;
     pll::Model model;
     unsigned int parent_root_index = 0;
@@ -162,7 +171,8 @@ class VisitPrefetcher
     pll::Model model;
     pll_utree_t* tree = nullptr;      // private clone WITH the move applied and the start flags set
     unsigned int node_index;          // the move, by record index
-    unsigned int parent_root_index;   // virtual root of the parent tree (the content's orientation)
+    unsigned int parent_root_index;   // where the parent tree's exact CLVs are oriented when the visit starts
+    bool parent_edge_invalid = false; // ... with the two ends of that node's edge invalid (radius-0 tester)
     int type;
     int depth = 0;                    // levels ahead of the wanderer (0: submitted by the wanderer)
     unsigned long long batch;         // moves queued by the same QueueMoves share a batch
@@ -184,7 +194,9 @@ class VisitPrefetcher
   void SubmitOrThrow(pll::Partition& owner, pll_utree_t* tree, pll_unode_t* node, int type);
   // queues the visit of move (node, type) of `tree`, whose exact CLVs (oriented at its virtual
   // root) the visiting partition will hold; false if that visit is already known
-  bool Enqueue(int device, const pll::Model& model, pll_utree_t* tree, pll_unode_t* node, int type, int depth);
+  // (`at` / `edge_invalid`: the orientation of the queue's first visit, null = the virtual root)
+  bool Enqueue(int device, const pll::Model& model, pll_utree_t* tree, pll_unode_t* node, int type, int depth,
+               const pll_unode_t* at = nullptr, bool edge_invalid = false);
   // one visit on `rep`; returns the optimised tree's lnL.  The start state: task.previous null --
   // the exact parent (made here); else the failed sibling's exact CLVs, which `rep` already holds
   // if `state_on_replica`, else made here by a FULL traversal of task.previous
@@ -210,6 +222,13 @@ class VisitPrefetcher
   };
   std::map<int, Pool> pools_;
 
+  // moves that have passed their test, waiting for Flush: per owner, of one tree
+  struct Noted {
+    const pll_utree_t* tree = nullptr;
+    std::vector<std::pair<unsigned int, int>> moves;   // (node_index, type)
+  };
+  std::map<const pll::Partition*, Noted> noted_;
+
   std::vector<std::thread> workers_;
   std::mutex mutex_;
   std::condition_variable wake_, replica_back_;
@@ -220,7 +239,7 @@ class VisitPrefetcher
   bool have_threshold_ = false;
   std::atomic<bool> disabled_{false};
   unsigned long long batch_ = 0;
-  std::map<std::pair<const pll_utree_t*, uint64_t>, std::shared_ptr<Batch>> batches_;   // by (tree, content)
+  std::map<std::pair<const pll_utree_t*, uint64_t>, std::shared_ptr<Batch>> batches_;   // by (tree, its fingerprint)
   std::deque<std::pair<const pll_utree_t*, uint64_t>> batch_order_;
   std::atomic<unsigned long long> chained_{0};
   unsigned long long submitted_ = 0, declined_ = 0;

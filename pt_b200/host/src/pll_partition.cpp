@@ -743,6 +743,8 @@ double Partition::LogMarginalLikelihood(pll_unode_t*)
 // PTPLL/pll_partition.cpp:348-393
 unsigned int Partition::TraversalUpdate(pll_unode_t* root, TraversalType type)
 {
+  if (type == TraversalType::FULL) pending_tree_ = nullptr;   // whatever a tester left is overwritten
+
   StatScope stat(kStatTraversal, !is_replica_);
   unsigned int traversal_size = 0;
   int ok;
@@ -834,9 +836,67 @@ void Partition::OptimizeAllBranchesOnce(pll_unode_t* tree, bool use_pllmod)
 }
 
 // PTPLL/pll_partition.cpp:542-582
+namespace {
+std::function<void(Partition&, pll_utree_t*, pll_unode_t*, bool)> g_orientation_hook;
+}
+
+void Partition::SetOrientationHook(std::function<void(Partition&, pll_utree_t*, pll_unode_t*, bool)> hook)
+{
+  g_orientation_hook = std::move(hook);
+}
+
+void Partition::DeferTesterOrientation(pll_utree_t* tree, pll_unode_t* tested, bool invalidate_edge)
+{
+  if (is_replica_) return;
+  pending_tree_ = tree;
+  pending_node_ = tested;
+  pending_invalidate_ = invalidate_edge;
+  InvalidationLog().clear();   // what is invalidated from here on happens after the tester's last state
+}
+
+// see DeferTesterOrientation in the header
+void Partition::ProduceTesterOrientation(pll_unode_t* visit_root)
+{
+  pll_utree_t* tree = pending_tree_;
+  pll_unode_t* tested = pending_node_;
+  const bool invalidate = pending_invalidate_;
+  pending_tree_ = nullptr;
+  const std::vector<pll_unode_t*> since = InvalidationLog();   // (copy: the calls below log too)
+  TraversalUpdate(tested, TraversalType::FULL);
+  if (invalidate) InvalidateEdgeClvs(tested);
+  for (pll_unode_t* n : since) InvalidateEdgeClvs(n);
+  // the tree being visited was cloned from `tree` (records keep their indices under an NNI) with the
+  // flags it had then (src/wanderer.cpp:160-166): give it the ones it would have had
+  const unsigned int records = tree->tip_count + 3 * tree->inner_count;
+  std::vector<signed char> valid(records, -1);
+  for (unsigned int i = 0; i < tree->tip_count + tree->inner_count; ++i) {
+    pll_unode_t* first = tree->nodes[i];
+    pll_unode_t* r = first;
+    do {
+      if (r->data && r->node_index < records) valid[r->node_index] = static_cast<node_info_t*>(r->data)->clv_valid ? 1 : 0;
+      r = r->next;
+    } while (r && r != first);
+  }
+  unsigned int found = 0;
+  if (pll_utree_traverse(visit_root, PLL_TREE_TRAVERSE_POSTORDER, visit_all, travbuffer_.data(), &found) &&
+      found == node_count()) {
+    for (unsigned int i = 0; i < found; ++i) {
+      pll_unode_t* first = travbuffer_[i];
+      pll_unode_t* r = first;
+      do {
+        if (r->data && r->node_index < records && valid[r->node_index] >= 0)
+          static_cast<node_info_t*>(r->data)->clv_valid = valid[r->node_index];
+        r = r->next;
+      } while (r && r != first);
+    }
+  }
+  if (g_orientation_hook) g_orientation_hook(*this, tree, tested, invalidate);
+}
+
 void Partition::OptimizeAllBranches(pll_unode_t* tree, bool use_pllmod)
 {
   StatScope stat(kStatAllBranches, !is_replica_);
+  if (pending_tree_ && !use_pllmod && !is_replica_) ProduceTesterOrientation(tree);
   if (!use_pllmod && !is_replica_ && g_visits_used.load(std::memory_order_relaxed)) {
     const uint64_t key = VisitKey(tree);
     const bool hit = key && TakePublishedVisit(key, tree);

@@ -157,6 +157,16 @@ void InvalidateEdgeClvs(pll_unode_t* node)
 {
   if (node->data) info(node)->clv_valid = 0;
   if (node->back->data) info(node->back)->clv_valid = 0;
+  // (this thread's latest invalidations: Partition::DeferTesterOrientation replays them)
+  std::vector<pll_unode_t*>& log = InvalidationLog();
+  if (log.size() >= 64) log.erase(log.begin(), log.begin() + 32);
+  log.push_back(node);
+}
+
+std::vector<pll_unode_t*>& InvalidationLog()
+{
+  thread_local std::vector<pll_unode_t*> log;
+  return log;
 }
 
 // PTPLL/pll_util.cpp:368-411

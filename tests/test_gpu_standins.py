@@ -51,13 +51,5 @@ def test_walk_tables_equal_the_reference_s(name):
         # (make_ptw_golden.score_buckets): at most a handful of buckets may differ, by one last-digit unit.
         assert table + "_buckets" in gold, f"{table} scores differ"
         unit = 10.0 ** (math.floor(math.log10(gold["score_scale"])) - 5)
-        if table + "_buckets_fine" in gold:
-            # DS5 only (see its "tested_note" in the golden file and DESIGN.md 6): at most 0.1 % of the
-            # entries, each by at most 5 units of the last printed digit (two may share a bucket); 4096
-            # buckets of ~80 scores
-            fine = score_buckets(tables[table], 4096)
-            off = [abs(a - b) for a, b in zip(fine, gold[table + "_buckets_fine"]) if abs(a - b) > 1e-6]
-            assert len(off) <= 0.001 * gold["counts"][table] and max(off) <= 10.5 * unit, (table, len(off), max(off))
-            continue
         off = [abs(a - b) for a, b in zip(got[table + "_buckets"], gold[table + "_buckets"]) if abs(a - b) > 1e-6]
         assert len(off) <= 5 and max(off) <= 1.5 * unit, (table, len(off), max(off), unit)
