@@ -17,10 +17,13 @@
 // (PTPLL/pll_util.cpp:353-366), so the CLVs between that edge and the root are stale when the
 // first branches are optimised, and the optimum found (to OptimizeAllBranches' own 1e-6
 // tolerance) depends on it in the last digits.  A worker therefore reproduces that very start
-// state -- FULL traversal of the parent tree T at its root (the partition's content whenever the
-// wanderer visits the first move of T's queue, or returns to T by MoveBack), then the NNI and
-// the two invalid flags -- and runs the identical procedure: same kernels, same inputs, same
-// bits.  The result is registered under a key that names the start state (content, tree,
+// state -- FULL traversal of the parent tree T at the node the tree is oriented at when the visit
+// starts, then the NNI and the two invalid flags -- and runs the identical procedure: same
+// kernels, same inputs, same bits.  That node is T's virtual root when the wanderer returns to T
+// by MoveBack (src/wanderer.cpp:232-239); for the FIRST move of T's queue it is the node the move
+// tester tested last (the reference's testers leave the tree oriented there; the batched tester
+// registers it with Partition::DeferTesterOrientation, the partition produces the state when the
+// visit starts and hands the moves noted so far to Flush).  The result is registered under a key that names the start state (content, tree,
 // flags: Partition::VisitKey); a visit whose actual start state is another one -- the move
 // after a visit that did NOT lead to a good tree starts from that tree's CLVs instead -- finds
 // nothing under its key and is computed in place, as before.  tests/test_gpu_dropin.py requires
