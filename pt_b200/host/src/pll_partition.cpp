@@ -1694,7 +1694,7 @@ std::vector<Partition::NniScore> Partition::ScoreNniNeighborhoodLocal(pll_utree_
   });
   // PTGPU_DUMP_LOCAL_TESTS=<file>: every candidate whose optimisation ended with a failure status (and
   // every 997th other one; PTGPU_DUMP_LOCAL_EVERY=n: every nth) as "<status> <score> <newick of the moved tree, written from the move's node,
-  // lengths with 17 digits>" -- to replay single cases on the reference (tests/golden tooling)
+  // lengths with 17 digits>" -- to replay single cases on the reference (tests/golden/ds5_replay_local_tests.py)
   if (const char* path = std::getenv("PTGPU_DUMP_LOCAL_TESTS")) {
     static std::mutex dump_mutex;
     static unsigned long long seen = 0;

@@ -1,7 +1,7 @@
 """pt's OptimizeBranch restated in the oracle against the compiled reference on the branches of DS5
 stand-in trees (many optima at zero length), every branch in OptimizeAllBranchesOnce order; prints
 (#optimisations, #results below 1e-5, #results that differ bitwise).  Needs the dump of
-scripts/ds5_replay_local_tests.py.  (round 2: 13 328 optimisations, 1390 near zero, 0 differ)"""
+tests/golden/ds5_replay_local_tests.py.  (round 2: 13 328 optimisations, 1390 near zero, 0 differ)"""
 import gzip,sys,os,tempfile
 import numpy as np
 sys.path.insert(0,'/root/repo')

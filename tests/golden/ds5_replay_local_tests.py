@@ -2,7 +2,7 @@
 [PTGPU_DUMP_LOCAL_EVERY=n]: "<status> <score> <moved tree, written from the move's node, 17-digit lengths>")
 on the compiled reference here: FULL traversal at the move's node, OptimizeBranchNeighborhood(node, 1),
 LogLikelihood -- what BranchNeighborhoodOptimizer::EvaluateMove computes -- and lists the cases whose
-score differs by more than 1e-9 relative.  usage: python scripts/ds5_replay_local_tests.py <part> <parts>
+score differs by more than 1e-9 relative.  usage: python tests/golden/ds5_replay_local_tests.py <part> <parts>
 (round 2: 33 803 sampled tests of the DS5 stand-in walk, 0 differ: profiles/r2_ds5_replay.txt)"""
 import gzip,sys,os,tempfile
 sys.path.insert(0,'/root/repo')
